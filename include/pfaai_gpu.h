@@ -1,0 +1,121 @@
+/*
+ * pfaai_gpu.h -- C-ABI of the B200-native AJI hot path (libpfaai_gpu.so).
+ *
+ * This is the drop-in boundary for the one path of AluruLab/ParFastAAI that runs on the GPU:
+ *
+ *   tetramer inverted index (Lc, F [, T])  ->  genome-major postings (device radix sort + histograms)
+ *       ->  per-(genome pair, SCP) intersection counts (on-chip, never materialised)
+ *       ->  Jaccard  ->  (S, N)  ->  AJI matrix.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo):
+ *   - DataStructInterface::construct()  = constructL/F/T/E   include/pfaai/interface.hpp:306-327,
+ *     implemented by DataStructHelper::constructLc / parallelPrefixSum / constructF / constructT /
+ *     constructE  include/pfaai/ds_helper.hpp:46-162,362-421 and parallelMergeSort psort.hpp:27-53;
+ *   - ParFAAIImpl::computeJAC / computeAJI / run  include/pfaai/algorithm_impl.hpp:281-329;
+ *   - the id maps / predicates of ParFAAIData, ParFAAIQSubData, ParFAAIQryTgtData
+ *     include/pfaai/ds_impl.hpp:39-151,159-337,344-490;
+ *   - printOutput's dense matrix fill  src/main.cpp:143-154.
+ * The reference has no FFI of its own (header-only C++ templates); INTEGRATION.md shows the binding a
+ * maintainer adds (a DataStructInterface subclass + ParFAAIImpl replacement that call these functions).
+ *
+ * Conventions: plain C, host pointers unless a name ends in `_dev`; the caller owns every host buffer,
+ * the context owns all device memory.  Every function returns a pfaai_status (the reference's
+ * PFAAI_ERROR_CODE values, interface.hpp:39-44); text for the last failure via pfaai_gpu_last_error().
+ * One host thread per context; one context drives one CUDA device.  There is NO CPU fallback: without a
+ * CUDA device pfaai_gpu_create() fails with PFAAI_ERR_CONSTRUCT.
+ */
+#ifndef PFAAI_GPU_H
+#define PFAAI_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PFAAI_NTETRAMERS 160000 /* 20^4, interface.hpp:233 */
+
+typedef struct pfaai_gpu_ctx pfaai_gpu_ctx; /* opaque */
+
+/* == DPair<int,int> (utils.hpp:204-225): one posting of F */
+typedef struct { int32_t protein, genome; } pfaai_pg_t;
+/* == JACTuple<int,double> fields (interface.hpp:61-75), natural C alignment (24 B) */
+typedef struct { int32_t gA, gB; double S; int32_t N; int32_t pad_; } pfaai_jac_t;
+
+/* == PFAAI_ERROR_CODE (interface.hpp:39-44) */
+enum pfaai_status { PFAAI_OK = 0, PFAAI_ERR_SQLITE_DB = 1, PFAAI_ERR_SQLITE_MEM_ALLOC = 2, PFAAI_ERR_CONSTRUCT = 3 };
+
+/* the three drivers of src/main.cpp:177,234,302 */
+enum pfaai_mode { PFAAI_ALL_VS_ALL = 0, PFAAI_QUERY_SUBSET = 1, PFAAI_QUERY_DB = 2 };
+
+/* flags for pfaai_gpu_compute* */
+#define PFAAI_FLAG_REF_COMPAT_QT 1u /* query-DB mode: reproduce the reference's T-lookup labels (q, nQ+t),
+                                       ds_impl.hpp:434-436; needed to match xdb_qt_{jac,aji}.bin */
+
+/* timings of the last build/compute, milliseconds, CUDA events on the context's stream */
+typedef struct {
+    float h2d_ms;        /* pfaai_gpu_upload_index                                       */
+    float build_ms;      /* pfaai_gpu_build total                                        */
+    float sort_ms;       /*   of which: radix sort passes                                */
+    float pack_ms;       /* row-slice packing inside compute                             */
+    float tile_ms;       /* the core tile kernel (aji_tile_kernel)                       */
+    float d2h_ms;        /* result download                                              */
+    int32_t n_launches;  /* kernels launched by the last build + compute                 */
+    int32_t n_tiles;     /* tiles the core kernel processed                              */
+    int64_t tile_alg_bytes; /* algorithmic bytes of the core kernel   */
+} pfaai_timings_t;
+
+/* ---- life cycle ------------------------------------------------------------------------------ */
+int  pfaai_gpu_create(pfaai_gpu_ctx **out, int device, unsigned flags);
+void pfaai_gpu_destroy(pfaai_gpu_ctx *ctx);
+const char *pfaai_gpu_last_error(const pfaai_gpu_ctx *ctx); /* ctx may be NULL: error of the last create */
+/* run on this cudaStream_t (e.g. torch's current stream); default = a stream the context creates */
+int  pfaai_gpu_set_stream(pfaai_gpu_ctx *ctx, void *cuda_stream);
+/* multi-GPU row-block sharding: this context computes tiles t with t % n_shards == shard (no collective:
+ * row blocks are independent); cells owned by other shards are left untouched (zero). */
+int  pfaai_gpu_set_shard(pfaai_gpu_ctx *ctx, int shard, int n_shards);
+
+/* ---- phase 1/2: index --------------------------------------------------------------------------
+ * Upload the reference's arrays exactly as DataBaseInterface delivers them (interface.hpp:153-196):
+ *   F  [nF]      postings (protein, genome) in (tetramer, protein, genome) order  -- proteinSetGPPairs
+ *   Lc [160000]  postings per tetramer                                           -- tetramerOccCounts
+ *   T  [P x G]   row-major tetramer counts, or NULL to derive T on the device as the (p,g) histogram of
+ *                F (exact in the single-DB modes; query-DB mode must pass the host T) -- proteinTetramerCounts
+ * n_genomes is the TOTAL number of genome ids (query-DB mode: nT + nQ, targets first). */
+int  pfaai_gpu_upload_index(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes,
+                            const pfaai_pg_t *F, const int32_t *Lc, int64_t nF, const int32_t *T);
+/* Device build: Lp (exclusive scan), per-(genome,SCP) segment histogram, T, and the genome-major
+ * postings by a stable LSD radix sort of the postings on (genome, SCP). */
+int  pfaai_gpu_build(pfaai_gpu_ctx *ctx);
+/* Parity hooks (any pointer may be NULL): Lc/Lp [160000], T [P x G], and the genome-major index:
+ * seg_off [G*P+1] (int64, segment g*P+p) and seg_vals [nF] (tetramers, ascending inside a segment). */
+int  pfaai_gpu_get_arrays(pfaai_gpu_ctx *ctx, int32_t *Lc, int32_t *Lp, int32_t *T,
+                          int64_t *seg_off, int32_t *seg_vals);
+
+/* ---- phase 3/4: AJI ----------------------------------------------------------------------------
+ * Computes the output matrix of the mode on the device (it stays there):
+ *   ALL_VS_ALL    G x G, symmetric, zero diagonal            (n_qry, qry_ids ignored)
+ *   QUERY_SUBSET  n_qry x G, rows in qry_ids order, self cell 0
+ *   QUERY_DB      n_qry x (G - n_qry): rows = query ids G-n_qry.., cols = target ids 0..G-n_qry-1
+ * A pair without any shared tetramer gets AJI 0 (N = 0). */
+int  pfaai_gpu_compute_device(pfaai_gpu_ctx *ctx, int mode, const int32_t *qry_ids, int n_qry, unsigned flags);
+/* shape of the matrix of the last compute */
+int  pfaai_gpu_matrix_shape(const pfaai_gpu_ctx *ctx, int64_t *rows, int64_t *cols);
+/* device pointer of the row-major fp64 matrix of the last compute (valid until the next compute/destroy) */
+const double *pfaai_gpu_matrix_dev(const pfaai_gpu_ctx *ctx);
+/* copy the matrix to host memory [rows x cols] */
+int  pfaai_gpu_download_matrix(pfaai_gpu_ctx *ctx, double *aji_matrix);
+/* One call with host buffers: compute_device + download, plus the optional small-N outputs in the
+ * reference's JAC order (initJAC of the mode): jac [n_pairs] (labels, S, N), aji [n_pairs],
+ * counts [n_pairs x P] per-SCP intersection counts.  Any output pointer may be NULL. */
+int  pfaai_gpu_compute(pfaai_gpu_ctx *ctx, int mode, const int32_t *qry_ids, int n_qry, unsigned flags,
+                       double *aji_matrix, pfaai_jac_t *jac, double *aji, int32_t *counts);
+/* number of JAC entries of a mode (nGenomePairs of the three classes) */
+int64_t pfaai_gpu_n_pairs(int mode, int n_genomes, int n_qry);
+
+int  pfaai_gpu_get_timings(const pfaai_gpu_ctx *ctx, pfaai_timings_t *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PFAAI_GPU_H */

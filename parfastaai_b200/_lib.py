@@ -1,0 +1,187 @@
+"""ctypes binding of libpfaai_gpu.so (the C-ABI declared in include/pfaai_gpu.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` (nvcc, sm_100a).  There is no CPU
+fallback anywhere in this package: if the shared library is missing or no CUDA device is present,
+the calls below raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpfaai_gpu.so")
+
+PG_DTYPE = np.dtype([("protein", "<i4"), ("genome", "<i4")])
+JAC_DTYPE = np.dtype([("gA", "<i4"), ("gB", "<i4"), ("S", "<f8"), ("N", "<i4"), ("pad_", "<i4")])
+assert JAC_DTYPE.itemsize == 24
+
+ALL_VS_ALL, QUERY_SUBSET, QUERY_DB = 0, 1, 2
+FLAG_REF_COMPAT_QT = 1
+NTETRA = 160000
+
+EXPORTS = [
+    "pfaai_gpu_create", "pfaai_gpu_destroy", "pfaai_gpu_last_error", "pfaai_gpu_set_stream", "pfaai_gpu_set_shard",
+    "pfaai_gpu_upload_index", "pfaai_gpu_build", "pfaai_gpu_get_arrays", "pfaai_gpu_compute_device",
+    "pfaai_gpu_matrix_shape", "pfaai_gpu_matrix_dev", "pfaai_gpu_download_matrix", "pfaai_gpu_compute",
+    "pfaai_gpu_n_pairs", "pfaai_gpu_get_timings",
+]
+
+
+class Timings(C.Structure):
+    _fields_ = [("h2d_ms", C.c_float), ("build_ms", C.c_float), ("sort_ms", C.c_float), ("pack_ms", C.c_float),
+                ("tile_ms", C.c_float), ("d2h_ms", C.c_float), ("n_launches", C.c_int32), ("n_tiles", C.c_int32),
+                ("tile_alg_bytes", C.c_int64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+_lib = None
+
+
+def load():
+    """dlopen the C-ABI library; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(nvcc, sm_100a). There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, u32 = C.c_void_p, C.c_int, C.c_int64, C.c_uint
+    L.pfaai_gpu_create.argtypes = [C.POINTER(vp), i32, u32]
+    L.pfaai_gpu_destroy.argtypes = [vp]
+    L.pfaai_gpu_destroy.restype = None
+    L.pfaai_gpu_last_error.argtypes = [vp]
+    L.pfaai_gpu_last_error.restype = C.c_char_p
+    L.pfaai_gpu_set_stream.argtypes = [vp, vp]
+    L.pfaai_gpu_set_shard.argtypes = [vp, i32, i32]
+    L.pfaai_gpu_upload_index.argtypes = [vp, i32, i32, vp, vp, i64, vp]
+    L.pfaai_gpu_build.argtypes = [vp]
+    L.pfaai_gpu_get_arrays.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.pfaai_gpu_compute_device.argtypes = [vp, i32, vp, i32, u32]
+    L.pfaai_gpu_matrix_shape.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
+    L.pfaai_gpu_matrix_dev.argtypes = [vp]
+    L.pfaai_gpu_matrix_dev.restype = vp
+    L.pfaai_gpu_download_matrix.argtypes = [vp, vp]
+    L.pfaai_gpu_compute.argtypes = [vp, i32, vp, i32, u32, vp, vp, vp, vp]
+    L.pfaai_gpu_n_pairs.argtypes = [i32, i32, i32]
+    L.pfaai_gpu_n_pairs.restype = i64
+    L.pfaai_gpu_get_timings.argtypes = [vp, C.POINTER(Timings)]
+    _lib = L
+    return L
+
+
+def _p(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+class PfaaiError(RuntimeError):
+    pass
+
+
+class PfaaiGpu:
+    """Thin object wrapper over one pfaai_gpu_ctx (one CUDA device)."""
+
+    def __init__(self, device=0):
+        self._L = load()
+        h = C.c_void_p()
+        rc = self._L.pfaai_gpu_create(C.byref(h), device, 0)
+        if rc != 0:
+            raise PfaaiError(f"pfaai_gpu_create rc={rc}: {self._L.pfaai_gpu_last_error(None).decode()}")
+        self._h = h
+        self.P = self.G = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pfaai_gpu_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise PfaaiError(f"{what} rc={rc}: {self._L.pfaai_gpu_last_error(self._h).decode()}")
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self._L.pfaai_gpu_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "set_stream")
+
+    def set_shard(self, shard, n_shards):
+        self._check(self._L.pfaai_gpu_set_shard(self._h, shard, n_shards), "set_shard")
+
+    def upload_index(self, P, G, F, Lc, T=None):
+        F = np.ascontiguousarray(F, dtype=PG_DTYPE)
+        Lc = np.ascontiguousarray(Lc, dtype=np.int32)
+        if Lc.shape[0] != NTETRA:
+            raise ValueError("Lc must have 160000 entries")
+        if T is not None:
+            T = np.ascontiguousarray(T, dtype=np.int32)
+            if T.shape != (P, G):
+                raise ValueError("T must be P x G")
+        self.P, self.G, self.nF = P, G, F.shape[0]
+        self._check(self._L.pfaai_gpu_upload_index(self._h, P, G, _p(F), _p(Lc), F.shape[0], _p(T)), "upload_index")
+
+    def build(self):
+        self._check(self._L.pfaai_gpu_build(self._h), "build")
+
+    def get_arrays(self, want_lists=True):
+        Lc = np.zeros(NTETRA, np.int32)
+        Lp = np.zeros(NTETRA, np.int32)
+        T = np.zeros((self.P, self.G), np.int32)
+        off = np.zeros(self.P * self.G + 1, np.int64) if want_lists else None
+        vals = np.zeros(self.nF, np.int32) if want_lists else None
+        self._check(self._L.pfaai_gpu_get_arrays(self._h, _p(Lc), _p(Lp), _p(T), _p(off), _p(vals)), "get_arrays")
+        return {"Lc": Lc, "Lp": Lp, "T": T, "seg_off": off, "seg_vals": vals}
+
+    def n_pairs(self, mode, n_qry=0):
+        return int(self._L.pfaai_gpu_n_pairs(mode, self.G, n_qry))
+
+    def compute_device(self, mode, qry_ids=None, flags=0):
+        q = None if qry_ids is None else np.ascontiguousarray(qry_ids, dtype=np.int32)
+        nq = 0 if q is None else q.shape[0]
+        self._check(self._L.pfaai_gpu_compute_device(self._h, mode, _p(q), nq, flags), "compute_device")
+
+    def matrix_shape(self):
+        r, c = C.c_int64(), C.c_int64()
+        self._check(self._L.pfaai_gpu_matrix_shape(self._h, C.byref(r), C.byref(c)), "matrix_shape")
+        return int(r.value), int(c.value)
+
+    def matrix_dev_ptr(self):
+        return self._L.pfaai_gpu_matrix_dev(self._h)
+
+    def download_matrix(self, out=None):
+        r, c = self.matrix_shape()
+        if out is None:
+            out = np.empty((r, c), np.float64)
+        self._check(self._L.pfaai_gpu_download_matrix(self._h, _p(out)), "download_matrix")
+        return out
+
+    def compute(self, mode, qry_ids=None, n_qry=None, flags=0, want_jac=True, want_counts=False, matrix_out=None):
+        """Host-buffer call. Returns dict(matrix, jac, aji, counts)."""
+        q = None if qry_ids is None else np.ascontiguousarray(qry_ids, dtype=np.int32)
+        nq = (0 if q is None else q.shape[0]) if n_qry is None else n_qry
+        if mode == ALL_VS_ALL:
+            shape = (self.G, self.G)
+        elif mode == QUERY_SUBSET:
+            shape = (nq, self.G)
+        else:
+            shape = (nq, self.G - nq)
+        M = matrix_out if matrix_out is not None else np.empty(shape, np.float64)
+        npairs = self.n_pairs(mode, nq)
+        jac = np.zeros(npairs, JAC_DTYPE) if want_jac else None
+        aji = np.zeros(npairs, np.float64) if want_jac else None
+        cnt = np.zeros((npairs, self.P), np.int32) if want_counts else None
+        self._check(self._L.pfaai_gpu_compute(self._h, mode, _p(q), nq, flags, _p(M), _p(jac), _p(aji), _p(cnt)), "compute")
+        return {"matrix": M, "jac": jac, "aji": aji, "counts": cnt}
+
+    def timings(self):
+        t = Timings()
+        self._check(self._L.pfaai_gpu_get_timings(self._h, C.byref(t)), "get_timings")
+        return t.as_dict()

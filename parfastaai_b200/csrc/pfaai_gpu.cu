@@ -1,0 +1,548 @@
+// pfaai_gpu.cu -- C-ABI (include/pfaai_gpu.h) and host orchestration of the sm_100a AJI path.
+// No CPU fallback: every entry point either runs the CUDA kernels or returns PFAAI_ERR_CONSTRUCT.
+#include <algorithm>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "aji_tile.cuh"
+#include "common.cuh"
+#include "index_build.cuh"
+
+namespace pfaai {
+
+static std::string g_create_error;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct Ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    int shard = 0, n_shards = 1;
+    // index
+    int P = 0, G = 0;
+    int64_t nF = 0;
+    bool host_T = false, uploaded = false, built = false;
+    int max_len = 0;
+    DevBuf F, Lc, Lp64, Lp32, T, seg_len, seg_off, itemsA, itemsB, vals, tile_sums, block_hist, block_base, flags;
+    // compute
+    DevBuf rows, row_t, cols, col_t, ell_nch, ell_off, ell, tiles, out, S_out, N_out, counts_out;
+    int64_t out_rows = 0, out_cols = 0;
+    int last_mode = -1;
+    // events / stats
+    cudaEvent_t ev[12] = {};
+    pfaai_timings_t tm = {};
+    int launches = 0;
+};
+
+void set_error(Ctx *ctx, const std::string &msg) {
+    if (ctx) ctx->err = msg; else g_create_error = msg;
+}
+
+static int ensure(Ctx *c, DevBuf &b, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    if (b.cap >= bytes) return PFAAI_OK;
+    if (b.p) { PF_CUDA(c, cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+    // grow with a little slack so that steady-state calls never reallocate
+    size_t want = bytes + bytes / 16 + 256;
+    PF_CUDA(c, cudaMalloc(&b.p, want));
+    b.cap = want;
+    return PFAAI_OK;
+}
+static void release(DevBuf &b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr; b.cap = 0;
+}
+template <typename T> static inline T *ptr(DevBuf &b) { return reinterpret_cast<T *>(b.p); }
+
+#define PF_TRY(call) do { int rc__ = (call); if (rc__ != PFAAI_OK) return rc__; } while (0)
+#define PF_LAUNCH_CHECK(c) do { (c)->launches++; PF_CUDA((c), cudaGetLastError()); } while (0)
+
+enum { EV_H2D0, EV_H2D1, EV_B0, EV_S0, EV_S1, EV_B1, EV_P0, EV_P1, EV_T0, EV_T1, EV_D0, EV_D1 };
+
+static float ev_ms(Ctx *c, int a, int b) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]) != cudaSuccess) { cudaGetLastError(); return 0.f; }
+    return ms;
+}
+
+// int32 -> int64 exclusive scan with n+1 outputs
+static int launch_scan(Ctx *c, const int32_t *in, int64_t n, int64_t *out, int32_t *out32) {
+    if (n <= 0) { PF_CUDA(c, cudaMemsetAsync(out, 0, sizeof(int64_t), c->stream)); return PFAAI_OK; }
+    const int64_t ntiles = ceil_div64(n, SCAN_TILE);
+    PF_TRY(ensure(c, c->tile_sums, sizeof(int64_t) * (size_t)ntiles));
+    k_scan_tile_sums<<<(unsigned)ntiles, SCAN_THREADS, 0, c->stream>>>(in, n, ptr<int64_t>(c->tile_sums));
+    PF_LAUNCH_CHECK(c);
+    k_scan_small_i64<<<1, 1024, 0, c->stream>>>(ptr<int64_t>(c->tile_sums), ntiles);
+    PF_LAUNCH_CHECK(c);
+    k_scan_final<<<(unsigned)ntiles, SCAN_THREADS, 0, c->stream>>>(in, n, ptr<int64_t>(c->tile_sums), out, out32);
+    PF_LAUNCH_CHECK(c);
+    return PFAAI_OK;
+}
+
+static int read_flags(Ctx *c, int *flags_host /*[4]*/) {
+    PF_CUDA(c, cudaMemcpyAsync(flags_host, c->flags.p, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PFAAI_OK;
+}
+
+}  // namespace pfaai
+
+using namespace pfaai;
+
+extern "C" {
+
+int pfaai_gpu_create(pfaai_gpu_ctx **out, int device, unsigned /*flags*/) {
+    if (!out) return PFAAI_ERR_CONSTRUCT;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (this library has no CPU fallback)";
+        cudaGetLastError();
+        return PFAAI_ERR_CONSTRUCT;
+    }
+    if (device < 0 || device >= ndev) { g_create_error = "bad device ordinal"; return PFAAI_ERR_CONSTRUCT; }
+    Ctx *c = new Ctx();
+    c->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { g_create_error = "cudaSetDevice failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { g_create_error = "cudaGetDeviceProperties failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
+    if (prop.major < 10) {
+        g_create_error = std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) + std::to_string(prop.minor) +
+                         "; this library is built for sm_100a only";
+        delete c; return PFAAI_ERR_CONSTRUCT;
+    }
+    c->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { g_create_error = "cudaStreamCreate failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
+    c->own_stream = true;
+    for (auto &ev : c->ev)
+        if (cudaEventCreate(&ev) != cudaSuccess) { g_create_error = "cudaEventCreate failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
+    if (cudaMalloc(&c->flags.p, 64) != cudaSuccess) { g_create_error = "cudaMalloc failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
+    c->flags.cap = 64;
+    *out = reinterpret_cast<pfaai_gpu_ctx *>(c);
+    return PFAAI_OK;
+}
+
+void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf *all[] = {&c->F, &c->Lc, &c->Lp64, &c->Lp32, &c->T, &c->seg_len, &c->seg_off, &c->itemsA, &c->itemsB, &c->vals,
+                     &c->tile_sums, &c->block_hist, &c->block_base, &c->flags, &c->rows, &c->row_t, &c->cols, &c->col_t,
+                     &c->ell_nch, &c->ell_off, &c->ell, &c->tiles, &c->out, &c->S_out, &c->N_out, &c->counts_out};
+    for (DevBuf *b : all) release(*b);
+    for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char *pfaai_gpu_last_error(const pfaai_gpu_ctx *h) {
+    const Ctx *c = reinterpret_cast<const Ctx *>(h);
+    return c ? c->err.c_str() : g_create_error.c_str();
+}
+
+int pfaai_gpu_set_stream(pfaai_gpu_ctx *h, void *s) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    PF_CUDA(c, cudaSetDevice(c->device));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    c->own_stream = false;
+    c->stream = reinterpret_cast<cudaStream_t>(s);
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_set_shard(pfaai_gpu_ctx *h, int shard, int n_shards) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || n_shards < 1 || shard < 0 || shard >= n_shards) { set_error(c, "bad shard"); return PFAAI_ERR_CONSTRUCT; }
+    c->shard = shard; c->n_shards = n_shards;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_upload_index(pfaai_gpu_ctx *h, int P, int G, const pfaai_pg_t *F, const int32_t *Lc, int64_t nF,
+                           const int32_t *T) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (P <= 0 || G <= 0 || nF < 0 || !Lc || (nF > 0 && !F)) { set_error(c, "upload_index: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
+    if ((int64_t)P * G >= (1ll << 31)) { set_error(c, "upload_index: P*G too large"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false;
+    PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
+    PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D0], c->stream));
+    if (nF > 0) PF_CUDA(c, cudaMemcpyAsync(c->F.p, F, sizeof(pfaai_pg_t) * (size_t)nF, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(c->Lc.p, Lc, sizeof(int32_t) * NTETRA, cudaMemcpyHostToDevice, c->stream));
+    if (T) PF_CUDA(c, cudaMemcpyAsync(c->T.p, T, sizeof(int32_t) * (size_t)P * G, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D1], c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));   // the caller may reuse its buffers
+    c->tm.h2d_ms = ev_ms(c, EV_H2D0, EV_H2D1);
+    c->uploaded = true;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_build(pfaai_gpu_ctx *h) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (!c->uploaded) { set_error(c, "build: no index uploaded"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    const int P = c->P, G = c->G;
+    const int64_t nF = c->nF, nseg = (int64_t)P * G;
+    c->launches = 0;
+    PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
+    PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->seg_len, sizeof(uint32_t) * (size_t)nseg));
+    PF_TRY(ensure(c, c->seg_off, sizeof(int64_t) * (size_t)(nseg + 1)));
+    PF_TRY(ensure(c, c->itemsA, sizeof(uint64_t) * (size_t)nF));
+    PF_TRY(ensure(c, c->itemsB, sizeof(uint64_t) * (size_t)nF));
+    PF_TRY(ensure(c, c->vals, sizeof(uint32_t) * (size_t)nF));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B0], c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->flags.p, 0, 64, c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->seg_len.p, 0, sizeof(uint32_t) * (size_t)nseg, c->stream));
+    // K1: Lp = exclusive scan of Lc (parallelPrefixSum)
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->Lc), NTETRA, ptr<int64_t>(c->Lp64), ptr<int32_t>(c->Lp32)));
+    // K2a + K3: sort items and the (genome, SCP) histogram
+    if (nF > 0) {
+        const int64_t nthreads = ceil_div64(nF, MI_ITEMS);
+        k_make_items<<<(unsigned)ceil_div64(nthreads, MI_THREADS), MI_THREADS, 0, c->stream>>>(
+            ptr<pfaai_pg_t>(c->F), ptr<int64_t>(c->Lp64), nF, P, G, ptr<uint64_t>(c->itemsA), ptr<uint32_t>(c->seg_len),
+            ptr<int>(c->flags));
+        PF_LAUNCH_CHECK(c);
+    }
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->seg_len), nseg, ptr<int64_t>(c->seg_off), nullptr));
+    k_transpose_t<<<(unsigned)ceil_div64(nseg, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->seg_len), P, G,
+                                                                          c->host_T ? nullptr : ptr<int32_t>(c->T),
+                                                                          ptr<int>(c->flags) + 1);
+    PF_LAUNCH_CHECK(c);
+    // K2b: stable LSD radix sort on (genome*P + protein); the last pass emits the tetramers only
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_S0], c->stream));
+    if (nF > 0) {
+        int keybits = 1;
+        while (keybits < 31 && ((int64_t)1 << keybits) < nseg) keybits++;
+        const int passes = (keybits + 7) / 8;
+        int64_t nb = std::min<int64_t>((int64_t)c->sm_count * 4, ceil_div64(nF, RS_TILE));
+        int64_t chunk = ceil_div64(ceil_div64(nF, nb), RS_TILE) * RS_TILE;
+        nb = ceil_div64(nF, chunk);
+        PF_TRY(ensure(c, c->block_hist, sizeof(uint32_t) * (size_t)(RS_RADIX * nb)));
+        PF_TRY(ensure(c, c->block_base, sizeof(int64_t) * (size_t)(RS_RADIX * nb)));
+        uint64_t *src = ptr<uint64_t>(c->itemsA), *dst = ptr<uint64_t>(c->itemsB);
+        for (int pass = 0; pass < passes; pass++) {
+            const int shift = TET_BITS + 8 * pass;
+            k_radix_hist<<<(unsigned)nb, RS_THREADS, 0, c->stream>>>(src, nF, shift, chunk, ptr<uint32_t>(c->block_hist));
+            PF_LAUNCH_CHECK(c);
+            k_radix_scan<<<1, 1024, 0, c->stream>>>(ptr<uint32_t>(c->block_hist), RS_RADIX * nb, ptr<int64_t>(c->block_base));
+            PF_LAUNCH_CHECK(c);
+            if (pass == passes - 1)
+                k_radix_scatter<true><<<(unsigned)nb, RS_THREADS, 0, c->stream>>>(src, nF, shift, chunk, ptr<int64_t>(c->block_base),
+                                                                                  nullptr, ptr<uint32_t>(c->vals));
+            else
+                k_radix_scatter<false><<<(unsigned)nb, RS_THREADS, 0, c->stream>>>(src, nF, shift, chunk, ptr<int64_t>(c->block_base),
+                                                                                   dst, nullptr);
+            PF_LAUNCH_CHECK(c);
+            std::swap(src, dst);
+        }
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_S1], c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B1], c->stream));
+    int fl[4];
+    PF_TRY(read_flags(c, fl));
+    if (fl[0] == 2) { set_error(c, "build: sum(Lc) != |F|"); return PFAAI_ERR_CONSTRUCT; }
+    if (fl[0]) { set_error(c, "build: posting with protein/genome id out of range"); return PFAAI_ERR_CONSTRUCT; }
+    c->max_len = fl[1];
+    c->tm.build_ms = ev_ms(c, EV_B0, EV_B1);
+    c->tm.sort_ms = ev_ms(c, EV_S0, EV_S1);
+    c->tm.n_launches = c->launches;
+    c->built = true;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_get_arrays(pfaai_gpu_ctx *h, int32_t *Lc, int32_t *Lp, int32_t *T, int64_t *seg_off, int32_t *seg_vals) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !c->built) { set_error(c, "get_arrays: index not built"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    const size_t nseg = (size_t)c->P * c->G;
+    if (Lc) PF_CUDA(c, cudaMemcpyAsync(Lc, c->Lc.p, sizeof(int32_t) * NTETRA, cudaMemcpyDeviceToHost, c->stream));
+    if (Lp) PF_CUDA(c, cudaMemcpyAsync(Lp, c->Lp32.p, sizeof(int32_t) * NTETRA, cudaMemcpyDeviceToHost, c->stream));
+    if (T) PF_CUDA(c, cudaMemcpyAsync(T, c->T.p, sizeof(int32_t) * nseg, cudaMemcpyDeviceToHost, c->stream));
+    if (seg_off) PF_CUDA(c, cudaMemcpyAsync(seg_off, c->seg_off.p, sizeof(int64_t) * (nseg + 1), cudaMemcpyDeviceToHost, c->stream));
+    if (seg_vals && c->nF > 0)
+        PF_CUDA(c, cudaMemcpyAsync(seg_vals, c->vals.p, sizeof(int32_t) * (size_t)c->nF, cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PFAAI_OK;
+}
+
+int64_t pfaai_gpu_n_pairs(int mode, int G, int nQ) {
+    switch (mode) {
+    case PFAAI_ALL_VS_ALL: return (int64_t)G * (G - 1) / 2;                                   // ds_impl.hpp:79-81
+    case PFAAI_QUERY_SUBSET: return (int64_t)nQ * (G - nQ) + (int64_t)nQ * (nQ - 1) / 2;     // ds_impl.hpp:244-249
+    case PFAAI_QUERY_DB: return (int64_t)nQ * (G - nQ);                                       // ds_impl.hpp:403
+    default: return -1;
+    }
+}
+
+}  // extern "C"
+
+// =====================================================================================================
+// Phase 3/4: AJI
+// =====================================================================================================
+namespace pfaai {
+
+constexpr int TILE_WARPS = 12;                               // 384 threads, <= 168 registers each
+constexpr int TILE_ROWS = TILE_WARPS * ROWS_PER_WARP;        // 192 rows x 64 cols per CTA
+constexpr int SMEM_FIXED = ((BM_WORDS + 3) & ~3) * 4 + COLS_PER_TILE * (8 + 4 + 4 + 4) + 36 * 4;
+constexpr int SMEM_TOTAL = 227 * 1024;
+constexpr int MASK_CAP = (SMEM_TOTAL - SMEM_FIXED) / 8 - 1;
+
+struct ModePlan {
+    std::vector<int32_t> rows, row_t, cols, col_t;
+    int64_t out_rows = 0, out_cols = 0, rs = 0, cs = 0;
+    int symmetric = 0;
+};
+
+// The id maps of the three reference mode classes (ds_impl.hpp:39-151,159-337,344-490) turned into the
+// kernel's row / column genome lists, T-column labels and output strides.
+static int plan_mode(Ctx *c, int mode, const int32_t *qry_ids, int nQ, unsigned flags, ModePlan &m) {
+    const int G = c->G;
+    if (mode == PFAAI_ALL_VS_ALL) {
+        m.rows.resize(G);
+        for (int g = 0; g < G; g++) m.rows[g] = g;
+        m.cols = m.rows; m.row_t = m.rows; m.col_t = m.rows;
+        m.out_rows = G; m.out_cols = G; m.rs = G; m.cs = 1; m.symmetric = 1;
+    } else if (mode == PFAAI_QUERY_SUBSET) {
+        if (nQ <= 0 || nQ > G || !qry_ids) { set_error(c, "compute: bad query subset"); return PFAAI_ERR_CONSTRUCT; }
+        std::vector<char> seen(G, 0);
+        for (int q = 0; q < nQ; q++) {
+            if (qry_ids[q] < 0 || qry_ids[q] >= G || seen[qry_ids[q]]) { set_error(c, "compute: query id out of range or repeated"); return PFAAI_ERR_CONSTRUCT; }
+            seen[qry_ids[q]] = 1;
+        }
+        // output is nQ x G (rows in query-file order, main.cpp:143-154); the kernel streams all genomes as
+        // rows against the (few) query genomes as dictionary columns and writes the transpose
+        m.rows.resize(G);
+        for (int g = 0; g < G; g++) m.rows[g] = g;
+        m.row_t = m.rows;
+        m.cols.assign(qry_ids, qry_ids + nQ); m.col_t = m.cols;
+        m.out_rows = nQ; m.out_cols = G; m.rs = 1; m.cs = G; m.symmetric = 0;
+    } else if (mode == PFAAI_QUERY_DB) {
+        const int nT = G - nQ;
+        if (nQ <= 0 || nT <= 0) { set_error(c, "compute: bad query-DB split"); return PFAAI_ERR_CONSTRUCT; }
+        m.rows.resize(nT); m.row_t.resize(nT); m.cols.resize(nQ); m.col_t.resize(nQ);
+        const bool quirk = (flags & PFAAI_FLAG_REF_COMPAT_QT) != 0;
+        for (int t = 0; t < nT; t++) { m.rows[t] = t; m.row_t[t] = quirk ? nQ + t : t; }            // ds_impl.hpp:434-436
+        for (int q = 0; q < nQ; q++) { m.cols[q] = nT + q; m.col_t[q] = quirk ? q : nT + q; }
+        m.out_rows = nQ; m.out_cols = nT; m.rs = 1; m.cs = nT; m.symmetric = 0;
+    } else { set_error(c, "compute: unknown mode"); return PFAAI_ERR_CONSTRUCT; }
+    return PFAAI_OK;
+}
+
+static int upload_i32(Ctx *c, DevBuf &b, const std::vector<int32_t> &v) {
+    PF_TRY(ensure(c, b, sizeof(int32_t) * v.size()));
+    if (!v.empty()) PF_CUDA(c, cudaMemcpyAsync(b.p, v.data(), sizeof(int32_t) * v.size(), cudaMemcpyHostToDevice, c->stream));
+    return PFAAI_OK;
+}
+
+template <int NPL>
+static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles) {
+    auto kern = aji_tile_kernel<TILE_WARPS, NPL>;
+    PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
+    kern<<<(unsigned)n_tiles, TILE_WARPS * 32, SMEM_TOTAL, c->stream>>>(prm);
+    PF_LAUNCH_CHECK(c);
+    return PFAAI_OK;
+}
+
+static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, unsigned flags, bool want_sn, bool want_counts,
+                            ModePlan &m) {
+    if (!c->built) { set_error(c, "compute: index not built"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    PF_TRY(plan_mode(c, mode, qry_ids, nQ, flags, m));
+    const int P = c->P;
+    const int n_rows = (int)m.rows.size(), n_cols = (int)m.cols.size();
+    const int n_groups = (n_rows + ROWS_PER_WARP - 1) / ROWS_PER_WARP;
+    const int launches_before = c->launches;
+    // plane capacity: a lane performs 4*ceil(max_len/8) lookups per SCP
+    const int lane_lookups = 4 * ((c->max_len + 7) / 8);
+    if (lane_lookups > 4095) { set_error(c, "compute: a (SCP, genome) tetramer list exceeds 8184 entries"); return PFAAI_ERR_CONSTRUCT; }
+
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_P0], c->stream));
+    PF_TRY(upload_i32(c, c->rows, m.rows)); PF_TRY(upload_i32(c, c->row_t, m.row_t));
+    PF_TRY(upload_i32(c, c->cols, m.cols)); PF_TRY(upload_i32(c, c->col_t, m.col_t));
+    // ---- pack the row slices ----
+    const int64_t ngp = (int64_t)n_groups * P;
+    PF_TRY(ensure(c, c->ell_nch, sizeof(int32_t) * (size_t)ngp));
+    PF_TRY(ensure(c, c->ell_off, sizeof(int64_t) * (size_t)(ngp + 1)));
+    k_pack_count<<<(unsigned)ceil_div64(ngp, 256), 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), ptr<int32_t>(c->rows), n_rows,
+                                                                        n_groups, P, ptr<int32_t>(c->ell_nch));
+    PF_LAUNCH_CHECK(c);
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->ell_nch), ngp, ptr<int64_t>(c->ell_off), nullptr));
+    int64_t total_chunks = 0;
+    PF_CUDA(c, cudaMemcpyAsync(&total_chunks, ptr<int64_t>(c->ell_off) + ngp, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    PF_TRY(ensure(c, c->ell, sizeof(uint4) * 32 * (size_t)total_chunks));
+    if (total_chunks > 0) {
+        k_pack_fill<<<(unsigned)std::min<int64_t>(ceil_div64(ngp, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
+            ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), ptr<int32_t>(c->rows), n_rows, n_groups, P, ptr<int64_t>(c->ell_off),
+            ptr<int32_t>(c->ell_nch), ptr<uint4>(c->ell));
+        PF_LAUNCH_CHECK(c);
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_P1], c->stream));
+    // ---- tile list: row block x column block, I-major so that concurrently resident CTAs share the row
+    //      block's slices in L2; symmetric mode keeps only tiles that contain a cell with row < col ----
+    const int nrb = (n_groups + TILE_WARPS - 1) / TILE_WARPS, ncb = (n_cols + COLS_PER_TILE - 1) / COLS_PER_TILE;
+    std::vector<int2> tiles;
+    int64_t t_index = 0;
+    for (int I = 0; I < nrb; I++)
+        for (int J = 0; J < ncb; J++) {
+            if (m.symmetric) {
+                const int row_min = I * TILE_ROWS, col_max = std::min((J + 1) * COLS_PER_TILE, n_cols) - 1;
+                if (row_min >= col_max) continue;
+            }
+            if (t_index++ % c->n_shards == c->shard) tiles.push_back(make_int2(I, J));
+        }
+    PF_TRY(ensure(c, c->tiles, sizeof(int2) * tiles.size()));
+    if (!tiles.empty()) PF_CUDA(c, cudaMemcpyAsync(c->tiles.p, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, c->stream));
+    // ---- outputs ----
+    c->out_rows = m.out_rows; c->out_cols = m.out_cols;
+    const size_t ncell = (size_t)m.out_rows * m.out_cols, nk = (size_t)n_rows * n_cols;
+    PF_TRY(ensure(c, c->out, sizeof(double) * ncell));
+    PF_CUDA(c, cudaMemsetAsync(c->out.p, 0, sizeof(double) * ncell, c->stream));
+    if (want_sn) {
+        PF_TRY(ensure(c, c->S_out, sizeof(double) * nk)); PF_TRY(ensure(c, c->N_out, sizeof(int32_t) * nk));
+        PF_CUDA(c, cudaMemsetAsync(c->S_out.p, 0, sizeof(double) * nk, c->stream));
+        PF_CUDA(c, cudaMemsetAsync(c->N_out.p, 0, sizeof(int32_t) * nk, c->stream));
+    }
+    if (want_counts) {
+        if ((double)nk * P > 1.0e9) { set_error(c, "compute: counts output is a small-N hook (n_rows*n_cols*P <= 1e9)"); return PFAAI_ERR_CONSTRUCT; }
+        PF_TRY(ensure(c, c->counts_out, sizeof(int32_t) * nk * P));
+        PF_CUDA(c, cudaMemsetAsync(c->counts_out.p, 0, sizeof(int32_t) * nk * P, c->stream));
+    }
+    PF_CUDA(c, cudaMemsetAsync(ptr<int>(c->flags) + 2, 0, sizeof(int), c->stream));
+    TileParams prm;
+    prm.ell = ptr<uint4>(c->ell); prm.ell_off = ptr<int64_t>(c->ell_off); prm.ell_nch = ptr<int32_t>(c->ell_nch);
+    prm.rows = ptr<int32_t>(c->rows); prm.row_t = ptr<int32_t>(c->row_t); prm.n_rows = n_rows; prm.n_groups = n_groups;
+    prm.cols = ptr<int32_t>(c->cols); prm.col_t = ptr<int32_t>(c->col_t); prm.n_cols = n_cols;
+    prm.seg_off = ptr<int64_t>(c->seg_off); prm.vals = ptr<uint32_t>(c->vals);
+    prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
+    prm.out = ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric;
+    prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
+    prm.N_out = want_sn ? ptr<int32_t>(c->N_out) : nullptr;
+    prm.counts_out = want_counts ? ptr<int32_t>(c->counts_out) : nullptr;
+    prm.tiles = ptr<int2>(c->tiles); prm.err = ptr<int>(c->flags) + 2; prm.mask_cap = MASK_CAP;
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
+    if (!tiles.empty() && c->nF > 0) {
+        if (lane_lookups <= 511) PF_TRY(launch_tiles<9>(c, prm, (int)tiles.size()));
+        else PF_TRY(launch_tiles<12>(c, prm, (int)tiles.size()));
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
+    int fl[4];
+    PF_TRY(read_flags(c, fl));
+    if (fl[2]) { set_error(c, "compute: a single (SCP, genome) tetramer list overflows the shared-memory dictionary"); return PFAAI_ERR_CONSTRUCT; }
+    c->tm.pack_ms = ev_ms(c, EV_P0, EV_P1);
+    c->tm.tile_ms = ev_ms(c, EV_T0, EV_T1);
+    c->tm.n_tiles = (int32_t)tiles.size();
+    c->tm.n_launches = c->launches;   // build + this compute
+    (void)launches_before;
+    // algorithmic bytes of the tile kernel: postings once, segment offsets, T, output once
+    c->tm.tile_alg_bytes = 4 * c->nF + 8 * ((int64_t)P * c->G + 1) + 4 * (int64_t)P * c->G +
+                           (int64_t)(8 * (double)ncell / c->n_shards);
+    c->last_mode = mode;
+    return PFAAI_OK;
+}
+
+}  // namespace pfaai
+
+extern "C" {
+
+int pfaai_gpu_compute_device(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_qry, unsigned flags) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    ModePlan m;
+    return compute_internal(c, mode, qry_ids, n_qry, flags, false, false, m);
+}
+
+int pfaai_gpu_matrix_shape(const pfaai_gpu_ctx *h, int64_t *rows, int64_t *cols) {
+    const Ctx *c = reinterpret_cast<const Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (rows) *rows = c->out_rows;
+    if (cols) *cols = c->out_cols;
+    return PFAAI_OK;
+}
+
+const double *pfaai_gpu_matrix_dev(const pfaai_gpu_ctx *h) {
+    const Ctx *c = reinterpret_cast<const Ctx *>(h);
+    return c ? reinterpret_cast<const double *>(c->out.p) : nullptr;
+}
+
+int pfaai_gpu_download_matrix(pfaai_gpu_ctx *h, double *M) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !M || c->last_mode < 0) { set_error(c, "download_matrix: nothing computed"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_D0], c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(M, c->out.p, sizeof(double) * (size_t)c->out_rows * c->out_cols, cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_D1], c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->tm.d2h_ms = ev_ms(c, EV_D0, EV_D1);
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_compute(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_qry, unsigned flags, double *aji_matrix,
+                      pfaai_jac_t *jac, double *aji, int32_t *counts) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    ModePlan m;
+    const bool want_sn = jac || aji;
+    PF_TRY(compute_internal(c, mode, qry_ids, n_qry, flags, want_sn, counts != nullptr, m));
+    if (aji_matrix) PF_TRY(pfaai_gpu_download_matrix(h, aji_matrix));
+    if (!want_sn && !counts) return PFAAI_OK;
+    // ---- small-N outputs in the reference's JAC order (initJAC of the mode) ----
+    const int G = c->G, P = c->P;
+    const int n_rows = (int)m.rows.size(), n_cols = (int)m.cols.size();
+    const size_t nk = (size_t)n_rows * n_cols;
+    std::vector<double> S; std::vector<int32_t> N, C;
+    if (want_sn) {
+        S.resize(nk); N.resize(nk);
+        PF_CUDA(c, cudaMemcpyAsync(S.data(), c->S_out.p, sizeof(double) * nk, cudaMemcpyDeviceToHost, c->stream));
+        PF_CUDA(c, cudaMemcpyAsync(N.data(), c->N_out.p, sizeof(int32_t) * nk, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (counts) {
+        C.resize(nk * P);
+        PF_CUDA(c, cudaMemcpyAsync(C.data(), c->counts_out.p, sizeof(int32_t) * nk * P, cudaMemcpyDeviceToHost, c->stream));
+    }
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    int64_t k = 0;
+    auto emit = [&](int labA, int labB, size_t cell) {
+        if (jac) { jac[k].gA = labA; jac[k].gB = labB; jac[k].S = S[cell]; jac[k].N = N[cell]; jac[k].pad_ = 0; }
+        if (aji) aji[k] = (N[cell] > 0) ? S[cell] / (double)N[cell] : 0.0;   // computeAJI, algorithm_impl.hpp:318
+        if (counts) std::memcpy(counts + k * P, C.data() + cell * P, sizeof(int32_t) * P);
+        k++;
+    };
+    if (mode == PFAAI_ALL_VS_ALL) {                       // ds_impl.hpp:99-114
+        for (int a = 0; a < G; a++) for (int b = a + 1; b < G; b++) emit(a, b, (size_t)a * n_cols + b);
+    } else if (mode == PFAAI_QUERY_SUBSET) {              // ds_impl.hpp:278-305; kernel rows = genomes, cols = queries
+        std::vector<char> isq(G, 0);
+        for (int q = 0; q < n_qry; q++) isq[qry_ids[q]] = 1;
+        for (int q = 0; q < n_qry; q++) for (int g = 0; g < G; g++) if (!isq[g]) emit(qry_ids[q], g, (size_t)g * n_cols + q);
+        for (int a = 0; a < n_qry; a++) for (int b = a + 1; b < n_qry; b++) emit(qry_ids[a], qry_ids[b], (size_t)qry_ids[b] * n_cols + a);
+    } else {                                              // ds_impl.hpp:426-438; kernel rows = targets, cols = queries
+        const int nT = G - n_qry;
+        const bool quirk = (flags & PFAAI_FLAG_REF_COMPAT_QT) != 0;
+        for (int q = 0; q < n_qry; q++) for (int t = 0; t < nT; t++)
+            emit(quirk ? q : nT + q, quirk ? n_qry + t : t, (size_t)t * n_cols + q);
+    }
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_get_timings(const pfaai_gpu_ctx *h, pfaai_timings_t *out) {
+    const Ctx *c = reinterpret_cast<const Ctx *>(h);
+    if (!c || !out) return PFAAI_ERR_CONSTRUCT;
+    *out = c->tm;
+    return PFAAI_OK;
+}
+
+}  // extern "C"

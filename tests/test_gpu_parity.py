@@ -1,0 +1,191 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the C-ABI
+(libpfaai_gpu.so via ctypes) and is compared with the reference's goldens and the CPU oracle.
+
+Bars (BASELINE.json north_star): Lc/Lp/T and per-(pair, SCP) intersection counts bit-exact; N exact;
+S within 1e-7 (JACTuple::operator==, interface.hpp:67-70); AJI within 1e-6 absolute -- in practice the
+kernel sums Jaccards in the reference's order (ascending SCP) with IEEE fp64 division, so the tests
+also assert bit-equality of AJI where the reference's own tests do (pfaai_tests.cpp:383,417,450).
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+pytestmark = pytest.mark.gpu
+
+AJI_TOL = 1e-6   # north_star tolerance (absolute)
+S_TOL = 1e-7
+
+
+@pytest.fixture(scope="module")
+def pf():
+    import __graft_entry__ as ge
+    ge.build()
+    import parfastaai_b200 as pf
+    return pf
+
+
+@pytest.fixture(scope="module")
+def orc():
+    from oracle import pfaai_oracle as orc
+    return orc
+
+
+from tests import golden_util as gu  # noqa: E402
+
+
+def _ctx_for(pf, g, host_T=False):
+    P, G = g["t"].shape
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, G, g["f"], g["lc"], g["t"] if host_T else None)
+    ctx.build()
+    return ctx, P, G
+
+
+def _check_jac(res, gold_jac, gold_aji):
+    assert np.array_equal(res["jac"]["gA"], gold_jac["gA"]) and np.array_equal(res["jac"]["gB"], gold_jac["gB"])
+    assert np.array_equal(res["jac"]["N"], gold_jac["N"])
+    assert np.abs(res["jac"]["S"] - gold_jac["S"]).max() < S_TOL
+    assert np.abs(res["aji"] - gold_aji).max() <= AJI_TOL
+    assert np.array_equal(res["aji"], gold_aji), "AJI not bit-identical to the reference golden"
+
+
+@pytest.mark.parametrize("name", ["xanthodb", "xdb_subset1", "xdb_subset2"])
+def test_index_build_golden(pf, orc, name):
+    g = gu.load(name)
+    ctx, P, G = _ctx_for(pf, g)
+    a = ctx.get_arrays()
+    assert np.array_equal(a["Lc"], g["lc"])
+    assert np.array_equal(a["Lp"], g["lp"])            # *_lp_array.bin
+    assert np.array_equal(a["T"], g["t"])              # *_t_matrix.bin, built on device as histogram of F
+    off, vals = orc.genome_major(P, G, g["lc"], g["f"])
+    assert np.array_equal(a["seg_off"], off)
+    assert np.array_equal(a["seg_vals"], vals)          # stable radix sort == stable re-sort of *_f_array.bin
+    ctx.close()
+
+
+@pytest.mark.parametrize("name", ["xanthodb", "xdb_subset1", "xdb_subset2"])
+def test_all_vs_all_golden(pf, orc, name):
+    g = gu.load(name)
+    ctx, P, G = _ctx_for(pf, g)
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, G, P, g["lc"], g["f"], g["t"])
+    assert np.array_equal(res["counts"], ref["counts"])
+    if "sorted_e" in g:   # run lengths of the reference's sorted E
+        idx = lambda a, b: G * a + b - (a + 2) * (a + 1) // 2
+        assert np.array_equal(res["counts"], gu.run_lengths_from_sorted_e(g["sorted_e"], idx, G * (G - 1) // 2, P))
+    else:                 # xantho: per-pair block extents of sorted E
+        assert np.array_equal(res["counts"].sum(axis=1), g["gpe_ends"] - g["gpe_starts"] + 1)
+    _check_jac(res, g["jac"], g["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    assert np.array_equal(res["matrix"], res["matrix"].T) and np.all(np.diag(res["matrix"]) == 0)
+    ctx.close()
+
+
+def test_query_subset_golden(pf, orc):
+    g = gu.load("xanthodb")
+    q = gu.load("xdb_qry_subset")
+    qids = gu.query_subset_ids()
+    ctx, P, G = _ctx_for(pf, g)
+    res = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.QUERY_SUBSET, G, P, g["lc"], g["f"], g["t"], nQ=len(qids), qry_ids=qids)
+    assert np.array_equal(res["counts"], ref["counts"])
+    _check_jac(res, q["jac"], q["aji"])
+    assert res["matrix"].shape == (5, 20)
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    lines = gu.csv_bytes("qsub_test_output_matrix_wheader.csv").decode().strip().split("\n")
+    M = np.array([[float(x) for x in line.split(",")[1:]] for line in lines[1:]])
+    assert np.array_equal(res["matrix"], M)
+    ctx.close()
+
+
+def test_query_db_golden_with_quirk(pf, orc):
+    g = gu.load("xdb_qt")
+    ctx, P, Gu = _ctx_for(pf, g, host_T=True)
+    a = ctx.get_arrays(want_lists=False)
+    assert np.array_equal(a["T"], g["t"]) and np.array_equal(a["Lp"], g["lp"])
+    nQ = 4
+    qids = np.arange(Gu - nQ, Gu, dtype=np.int32)
+    res = ctx.compute(pf.QUERY_DB, qry_ids=qids, flags=pf.FLAG_REF_COMPAT_QT, want_jac=True, want_counts=True)
+    idx = lambda a, b: (a - (Gu - nQ)) * (Gu - nQ) + b
+    assert np.array_equal(res["counts"], gu.run_lengths_from_sorted_e(g["sorted_e"], idx, 16, P))
+    _check_jac(res, g["jac"], g["aji"])
+    ref = orc.full_pipeline(orc.QUERY_DB, Gu, P, g["lc"], g["f"], g["t"], nQ=nQ, quirk=True)
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    # corrected labels (flag off) == oracle without the quirk
+    res2 = ctx.compute(pf.QUERY_DB, qry_ids=qids, flags=0, want_jac=True)
+    ref2 = orc.full_pipeline(orc.QUERY_DB, Gu, P, g["lc"], g["f"], g["t"], nQ=nQ, quirk=False)
+    assert np.array_equal(res2["aji"], ref2["aji"]) and res2["aji"].max() <= 1.0
+    ctx.close()
+
+
+@pytest.mark.parametrize("N,P,seed,dense", [(70, 12, 1, False), (200, 9, 2, False), (333, 7, 3, True), (450, 5, 4, False)])
+def test_synthetic_all_vs_all_vs_oracle(pf, orc, N, P, seed, dense):
+    """Multiple row blocks (192 rows) and column blocks (64 cols), ragged edges, triangular tile skipping."""
+    from parfastaai_b200 import synth
+    off, vals = synth.generate(N, P, seed=seed, dense=dense)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    a = ctx.get_arrays()
+    assert np.array_equal(a["T"], T) and np.array_equal(a["seg_off"], off) and np.array_equal(a["seg_vals"], vals)
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, N, P, Lc, F, T)
+    assert np.array_equal(res["counts"], ref["counts"])
+    assert np.array_equal(res["jac"]["N"], ref["jac"]["N"])
+    assert np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    ctx.close()
+
+
+def test_synthetic_subset_and_query_db_vs_oracle(pf, orc):
+    from parfastaai_b200 import synth
+    N, P = 260, 8
+    off, vals = synth.generate(N, P, seed=11)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    qids = np.array(sorted(np.random.default_rng(5).choice(N, 70, replace=False)), np.int32)
+    res = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.QUERY_SUBSET, N, P, Lc, F, T, nQ=len(qids), qry_ids=qids)
+    assert np.array_equal(res["counts"], ref["counts"]) and np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    # query-DB split of the same genomes: last 100 are "queries" (nQ != nT: corrected labels only)
+    nQ = 100
+    q2 = np.arange(N - nQ, N, dtype=np.int32)
+    res = ctx.compute(pf.QUERY_DB, qry_ids=q2, flags=0, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.QUERY_DB, N, P, Lc, F, T, nQ=nQ, quirk=False)
+    assert np.array_equal(res["counts"], ref["counts"]) and np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    ctx.close()
+
+
+def test_sharded_tiles_cover_matrix_exactly_once(pf, orc):
+    """Row-block sharding: the union of the shards' matrices is the full matrix, bit for bit."""
+    from parfastaai_b200 import synth
+    N, P = 500, 4
+    off, vals = synth.generate(N, P, seed=21)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    full = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
+    acc = np.zeros_like(full)
+    hits = np.zeros(full.shape, np.int32)
+    for s in range(3):
+        ctx.set_shard(s, 3)
+        part = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+        hits += part != 0
+        acc += part
+    ctx.set_shard(0, 1)
+    assert hits.max() == 1
+    assert np.array_equal(acc, full)
+    ctx.close()
