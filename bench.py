@@ -384,7 +384,7 @@ def main():
                    "genomes": G, "scps": P, "postings": nF, "pairs": pairs_total, "mode": "all-vs-all",
                    "parallelism": f"row-block tiles sharded over {world} rank(s), index replicated, no collective",
                    "l2_policy": "inputs larger than L2 (F = %.2f GB, matrix = %.2f GB vs 126 MB L2)" % (8 * nF / 1e9, d2h / 1e9),
-                   "step": "index build (scan + histogram + radix sort) + row-slice packing + tile kernel"},
+                   "step": "index build (scan + histogram + radix sort) + row-slab packing + column dictionaries + tile kernel"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
@@ -394,7 +394,7 @@ def main():
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "alg_bytes_per_launch": alg_bytes, "kernel_ms": tile_avg_ms,
                      "note": "the tile kernel is on-chip (shared-memory lookup / LOP3 issue) bound at this size; see DESIGN.md section 4"},
-        "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "tile": tile_avg_ms,
+        "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
                       "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"]},
     }
 

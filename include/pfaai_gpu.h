@@ -57,12 +57,14 @@ typedef struct {
     float h2d_ms;        /* pfaai_gpu_upload_index                                       */
     float build_ms;      /* pfaai_gpu_build total                                        */
     float sort_ms;       /*   of which: radix sort passes                                */
-    float pack_ms;       /* row-slice packing inside compute                             */
+    float pack_ms;       /* row-slab packing inside compute                              */
     float tile_ms;       /* the core tile kernel (aji_tile_kernel)                       */
     float d2h_ms;        /* result download                                              */
     int32_t n_launches;  /* kernels launched by the last build + compute                 */
     int32_t n_tiles;     /* tiles the core kernel processed                              */
     int64_t tile_alg_bytes; /* algorithmic bytes of the core kernel   */
+    float dict_ms;       /* column-block dictionary build inside compute                 */
+    int32_t reserved_;
 } pfaai_timings_t;
 
 /* ---- life cycle ------------------------------------------------------------------------------ */

@@ -33,7 +33,7 @@ EXPORTS = [
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("build_ms", C.c_float), ("sort_ms", C.c_float), ("pack_ms", C.c_float),
                 ("tile_ms", C.c_float), ("d2h_ms", C.c_float), ("n_launches", C.c_int32), ("n_tiles", C.c_int32),
-                ("tile_alg_bytes", C.c_int64)]
+                ("tile_alg_bytes", C.c_int64), ("dict_ms", C.c_float), ("reserved_", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

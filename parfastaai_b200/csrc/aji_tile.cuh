@@ -9,18 +9,22 @@
 //   computeAJI                include/pfaai/algorithm_impl.hpp:309-322  (AJI = S/N)
 //   printOutput matrix fill   src/main.cpp:143-154                   (mirror across the diagonal, zero diagonal)
 //
-// Formulation.  One CTA owns a tile of (NW*16 rows) x (64 columns) genome pairs and loops over the SCPs in
-// ascending index (same summation order as the reference).  Per SCP:
-//   build : the 64 column genomes' tetramer lists are scattered into a shared-memory dictionary
-//           tetramer -> 64-bit column mask: a 160k-bit presence bitmap with interleaved 16-bit ranks
-//           (40 KB) + one uint2 mask per distinct tetramer (warp-aggregation-free: smem atomicOr only
-//           in this build step, |cols|*len operations, amortised over NW*16 rows).
-//   walk  : lane (row r, half h) streams its half of row r's sorted list (coalesced LDG.128 from the packed
-//           slices), looks every tetramer up (1 LDS.32 + 1 LDS.64) and adds the 64-bit mask into BIT-SLICED
-//           counters (carry-save adders, LOP3 only): one mask add advances 64 pair counters at once.
-//           No atomics, no E array, no per-pair memory traffic.
-//   epilogue: the two half-lanes exchange halves (SHFL), each lane expands 32 counters, forms
-//           J = c / (T(p,a) + T(p,b) - c) in fp64, S += J, N += (c > 0)  -- registers only.
+// Formulation.  A persistent CTA (one per SM, 16 walker warps) owns tiles of 256 rows x 64 columns of genome
+// pairs and, per tile, walks the column block's STAGE LIST: for every SCP in ascending index (the reference's
+// summation order) and every tetramer range, one dictionary blob
+//        [presence/rank bitmap over the range | one 64-bit column mask per distinct tetramer]
+// built once per compute call by k_dict_build (tile_index.cuh).
+//   pipeline : blobs arrive in a 2-slot shared-memory ring by cp.async.bulk (TMA, SASS UBLKCP) completing on
+//              an mbarrier; a slot is refilled by whichever warp is the LAST to finish walking it (an
+//              acq_rel shared-memory counter), so there is no producer warp and no block-wide barrier inside
+//              a tile: warps drift up to one stage apart and the LDS-bound walk of one warp overlaps the
+//              ALU/FP64-bound epilogue of another.
+//   walk     : lane (row r, half h) streams its half of row r's sorted list (coalesced LDG.128 from the packed
+//              slabs, prefetched one step ahead), looks every tetramer up (1 LDS.32 + 1 LDS.64) and adds the
+//              64-bit mask into BIT-SLICED counters (carry-save adders, LOP3 only): one mask add advances
+//              64 pair counters at once.  No atomics, no E array, no per-pair memory traffic.
+//   epilogue : after the last stage of an SCP the two half-lanes exchange halves (SHFL), each lane expands 32
+//              counters, forms J = c / (T(p,a) + T(p,b) - c) in fp64, S += J, N += (c > 0) -- registers only.
 // After the last SCP: AJI = S/N written to the dense output (both triangles in symmetric mode).
 #pragma once
 #include "common.cuh"
@@ -28,19 +32,19 @@
 namespace pfaai {
 
 struct TileParams {
-    // row side: packed slices (k_pack_fill)
+    // row side: packed slabs (k_pack_fill)
     const uint4 *ell;
-    const int64_t *ell_off;    // [n_groups * P] in 512-byte chunks
-    const int32_t *ell_nch;    // [n_groups * P]
+    const int64_t *ell_off;    // [n_groups * P * NRANGE + 1] in 512-byte chunks
     const int32_t *rows;       // [n_rows] genome id of kernel row i
     const int32_t *row_t;      // [n_rows] T column used for row i
     int n_rows, n_groups;
-    // column side: genome-major lists
+    // column side: dictionaries (k_dict_build / k_stage_fill)
     const int32_t *cols;       // [n_cols]
-    const int32_t *col_t;      // [n_cols]
     int n_cols;
-    const int64_t *seg_off;    // [G*P + 1]
-    const uint32_t *vals;      // [nF]
+    const StageDesc *stages;
+    const int64_t *stage_begin;   // [n_col_blocks + 1]
+    const unsigned char *blob;
+    const int32_t *colT;       // [n_col_blocks * P * 64]
     const int32_t *T;          // [P x t_ld]
     int t_ld, P;
     // output
@@ -50,10 +54,39 @@ struct TileParams {
     double *S_out;             // optional hooks, [n_rows x n_cols]
     int32_t *N_out;
     int32_t *counts_out;       // optional, [n_rows x n_cols x P]
-    const int2 *tiles;         // (row block, col block) per CTA
-    int *err;                  // device error flag: 1 = a single column list overflows the dictionary
-    int mask_cap;              // capacity (entries) of the mask array in shared memory
+    const int2 *tiles;         // (row block, col block)
+    int n_tiles;
 };
+
+// ---- PTX wrappers: mbarrier + bulk async copy (TMA) ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ uint32_t atom_add_acq_rel_smem(uint32_t *p, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(smem_u32(p)), "r"(v) : "memory");
+    return old;
+}
 
 // carry-save adder on one 32-bit slice: (h, l) = a + b + c
 #define PF_CSA(h, l, a, b, c)                       \
@@ -66,262 +99,285 @@ struct TileParams {
 
 struct Mask64 { uint32_t lo, hi; };
 
-__device__ __forceinline__ Mask64 dict_lookup(const uint32_t *__restrict__ bm, const uint2 *__restrict__ masks, uint32_t v) {
-    const uint32_t w = bm[v >> 4];
-    const uint32_t b = v & 15u;
-    const uint32_t below = w & ((1u << b) - 1u);          // presence bits of smaller tetramers in this word
-    const uint32_t idx = (w >> 16) + __popc(below) + 1u;    // slot 0 is the all-zero "miss" slot
-    const uint32_t slot = ((w >> b) & 1u) ? idx : 0u;
+// x = slab_encode(v): bitmap word at byte offset x>>5; shifting it left by x&31 puts v's presence bit in
+// bit 31 and the presence bits of smaller tetramers below it (the rank half-word falls off the top).
+__device__ __forceinline__ Mask64 dict_lookup(const unsigned char *__restrict__ bm, const uint2 *__restrict__ masks, uint32_t x) {
+    const uint32_t w = *reinterpret_cast<const uint32_t *>(bm + (x >> 5));
+    const uint32_t t = __funnelshift_l(0u, w, x);                  // w << (x & 31)
+    const uint32_t idx = (w >> 16) + __popc(t);                     // rank of the word + #present <= v  (>= 1 on a hit)
+    const uint32_t slot = ((int32_t)t < 0) ? idx : 0u;              // slot 0 is the all-zero "miss" mask
     const uint2 m = masks[slot];
     Mask64 r; r.lo = m.x; r.hi = m.y;
     return r;
 }
 
-template <int NW, int NPL>
-__global__ void __launch_bounds__(NW * 32, 1) aji_tile_kernel(const TileParams prm) {
-    constexpr int NT = NW * 32;
-    extern __shared__ __align__(16) uint32_t smem[];
-    // ---- shared memory carve-up ----
-    uint32_t *bm = smem;                                          // [BM_WORDS] (+pad)
-    constexpr int BM_PAD = (BM_WORDS + 3) & ~3;
-    int64_t *col_seg = reinterpret_cast<int64_t *>(smem + BM_PAD); // [64] start of the column's list
-    int32_t *col_len = reinterpret_cast<int32_t *>(col_seg + COLS_PER_TILE);  // [64]
-    int32_t *col_tv = col_len + COLS_PER_TILE;                    // [64] T(p, col)
-    int32_t *col_g = col_tv + COLS_PER_TILE;                      // [64] genome id (-1 = none)
-    uint32_t *wsum = reinterpret_cast<uint32_t *>(col_g + COLS_PER_TILE);  // [34] scan scratch
-    uint2 *masks = reinterpret_cast<uint2 *>(wsum + 36);          // [mask_cap + 1]
+// a StageDesc travels through the kernel as the raw uint4 {off.lo, off.hi, bytes, p | q<<16 | flags<<24}
+__device__ __forceinline__ uint4 load_stage(const StageDesc *p) { return __ldg(reinterpret_cast<const uint4 *>(p)); }
+__device__ __forceinline__ int st_p(uint32_t w) { return (int)(w & 0xffffu); }
+__device__ __forceinline__ int st_q(uint32_t w) { return (int)((w >> 16) & 0xffu); }
+__device__ __forceinline__ bool st_first(uint32_t w) { return (w >> 24) & 1u; }
+__device__ __forceinline__ bool st_last(uint32_t w) { return (w >> 25) & 1u; }
+
+constexpr int N_PLANES_N = 10;   // bit-sliced N counter: up to 1023 SCPs
+
+template <int NPL>
+__global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TileParams prm) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    // ---- shared memory carve-up: [misc SMEM_MISC][stage 0][stage 1] ----
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem);               // [2] mbarriers: blob landed
+    uint32_t *done = reinterpret_cast<uint32_t *>(smem + 16);          // [2] warps that finished walking the slot
+    int32_t *col_g = reinterpret_cast<int32_t *>(smem + 64);           // [64] genome id of the tile's columns (-1 = none)
+    int32_t *colT = reinterpret_cast<int32_t *>(smem + 64 + 256);      // [4][64] ring of T(p, column), slot p & 3
+    unsigned char *stage_mem = smem + SMEM_MISC;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int2 tile = prm.tiles[blockIdx.x];
     const int P = prm.P;
-    const int group = tile.x * NW + warp;
-    const bool group_ok = group < prm.n_groups;
     const int r = lane >> 1, h = lane & 1;
-    const int row = group * ROWS_PER_WARP + r;
-    const bool row_ok = row < prm.n_rows;
-    const int gi = row_ok ? prm.rows[row] : -1;
-    const int ti = row_ok ? prm.row_t[row] : 0;
-    const int j0 = tile.y * COLS_PER_TILE;
-    const int ncol = min(COLS_PER_TILE, prm.n_cols - j0);
+    const int cbase = 32 * h;
 
-    if (tid < COLS_PER_TILE) col_g[tid] = (tid < ncol) ? prm.cols[j0 + tid] : -1;
+    if (tid == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        done[0] = 0u; done[1] = 0u;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t use[2] = {0u, 0u};     // completed fills of each slot (wait parity), identical in every thread
 
-    double S[32];
-    uint32_t n16[16];
-#pragma unroll
-    for (int j = 0; j < 32; j++) S[j] = 0.0;
-#pragma unroll
-    for (int j = 0; j < 16; j++) n16[j] = 0u;
+    auto issue = [&](const uint4 st, int slot, int cb) {
+        // runs in ONE thread: refill `slot` with the blob of stage `st` (+ the column T values on an SCP's first stage)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const uint32_t extra = st_first(st.w) ? COLS_PER_TILE * 4u : 0u;
+        const int64_t off = (int64_t)(((uint64_t)st.y << 32) | st.x);
+        mbar_expect_tx(&full[slot], st.z + extra);
+        bulk_g2s(stage_mem + (size_t)slot * STAGE_BYTES, prm.blob + off, st.z, &full[slot]);
+        if (extra)
+            bulk_g2s(colT + (st_p(st.w) & 3) * COLS_PER_TILE, prm.colT + ((int64_t)cb * P + st_p(st.w)) * COLS_PER_TILE, extra,
+                     &full[slot]);
+    };
 
-    // words of the bitmap each thread scans; odd so that consecutive lanes hit distinct banks
-    constexpr int WPT = ((BM_WORDS + NT - 1) / NT) | 1;
+    for (int t = blockIdx.x; t < prm.n_tiles; t += gridDim.x) {
+        const int2 tile = prm.tiles[t];
+        const int cb = tile.y;
+        const int64_t sb = prm.stage_begin[cb];
+        const int nst = (int)(prm.stage_begin[cb + 1] - sb);
+        const int group = tile.x * TILE_WARPS + warp;
+        const bool group_ok = group < prm.n_groups;
+        const int row = group * ROWS_PER_WARP + r;
+        const bool row_ok = row < prm.n_rows;
+        const int gi = row_ok ? prm.rows[row] : -1;
+        const int ti = row_ok ? prm.row_t[row] : 0;
+        const int j0 = cb * COLS_PER_TILE;
+        const int ncol = min(COLS_PER_TILE, prm.n_cols - j0);
 
-    for (int p = 0; p < P; p++) {
-        const int ta = row_ok ? prm.T[(int64_t)p * prm.t_ld + ti] : 0;
-        int c0 = 0;
-        while (c0 < ncol) {
-            int c1 = ncol;
-            uint32_t n_distinct = 0;
-            // ================= build the dictionary for columns [c0, c1) =================
-            for (;;) {
-                __syncthreads();   // previous users of bm / masks / col_* are done
-                for (int i = tid; i < BM_PAD; i += NT) bm[i] = 0u;
-                if (tid < COLS_PER_TILE) {
-                    int len = 0; int64_t so = 0; int tv = 0;
-                    if (tid >= c0 && tid < c1) {
-                        const int64_t s = (int64_t)col_g[tid] * P + p;
-                        so = prm.seg_off[s];
-                        len = (int)(prm.seg_off[s + 1] - so);
-                        tv = prm.T[(int64_t)p * prm.t_ld + prm.col_t[j0 + tid]];
-                    }
-                    col_seg[tid] = so; col_len[tid] = len; col_tv[tid] = tv;
-                }
-                __syncthreads();
-                // presence bits: task = (32-entry chunk, column); columns of one SCP have similar lengths
-                int maxlen = 0;
-                for (int c = c0; c < c1; c++) maxlen = max(maxlen, col_len[c]);   // smem broadcast reads
-                const int nchunk = (maxlen + 31) >> 5, ncs = c1 - c0;
-                for (int t = warp; t < nchunk * ncs; t += NW) {
-                    const int c = c0 + t % ncs, k = (t / ncs) * 32 + lane;
-                    if (k < col_len[c]) {
-                        const uint32_t v = prm.vals[col_seg[c] + k];
-                        atomicOr(&bm[v >> 4], 1u << (v & 15u));
-                    }
-                }
-                __syncthreads();
-                // ranks: exclusive scan of popc(presence) over the words, stored in the high half-words
-                {
-                    const int w0 = tid * WPT, w1 = min(w0 + WPT, BM_WORDS);
-                    uint32_t s = 0;
-                    for (int i = w0; i < w1; i++) s += __popc(bm[i]);
-                    uint32_t inc = s;
-#pragma unroll
-                    for (int d = 1; d < 32; d <<= 1) {
-                        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-                        if (lane >= d) inc += o;
-                    }
-                    if (lane == 31) wsum[warp] = inc;
-                    __syncthreads();
-                    if (warp == 0) {
-                        const uint32_t wv = (lane < NW) ? wsum[lane] : 0u;
-                        uint32_t winc = wv;
-#pragma unroll
-                        for (int d = 1; d < 32; d <<= 1) {
-                            const uint32_t o = __shfl_up_sync(0xffffffffu, winc, d);
-                            if (lane >= d) winc += o;
-                        }
-                        wsum[lane] = winc - wv;
-                        if (lane == 31) wsum[32] = winc;
-                    }
-                    __syncthreads();
-                    uint32_t run = wsum[warp] + inc - s;
-                    n_distinct = wsum[32];
-                    if (n_distinct <= (uint32_t)prm.mask_cap) {
-                        for (int i = w0; i < w1; i++) { const uint32_t w = bm[i]; bm[i] = w | (run << 16); run += __popc(w); }
-                    }
-                }
-                if (n_distinct <= (uint32_t)prm.mask_cap) break;
-                if (c1 - c0 == 1) {           // a single list does not fit: give up on this tile, flag it
-                    if (tid == 0) *prm.err = 1;
-                    return;                   // uniform: n_distinct is the same in every thread
-                }
-                c1 = c0 + ((c1 - c0) >> 1);   // halve the column range and rebuild
-            }
-            // zero the masks (slot 0 = miss), then OR every column's bit into its tetramers' masks
-            for (uint32_t i = tid; i <= n_distinct; i += NT) masks[i] = make_uint2(0u, 0u);
-            __syncthreads();
-            {
-                int maxlen = 0;
-                for (int c = c0; c < c1; c++) maxlen = max(maxlen, col_len[c]);
-                const int nchunk = (maxlen + 31) >> 5, ncs = c1 - c0;
-                uint32_t *m32 = reinterpret_cast<uint32_t *>(masks);
-                for (int t = warp; t < nchunk * ncs; t += NW) {
-                    const int c = c0 + t % ncs, k = (t / ncs) * 32 + lane;
-                    if (k < col_len[c]) {
-                        const uint32_t v = prm.vals[col_seg[c] + k];
-                        const uint32_t w = bm[v >> 4];
-                        const uint32_t idx = (w >> 16) + __popc(w & ((1u << (v & 15u)) - 1u)) + 1u;
-                        atomicOr(&m32[2 * idx + (c >> 5)], 1u << (c & 31));
-                    }
-                }
-            }
-            __syncthreads();
+        if (tid == 0) {
+            if (nst > 0) issue(load_stage(prm.stages + sb), 0, cb);
+            if (nst > 1) issue(load_stage(prm.stages + sb + 1), 1, cb);
+        }
+        if (tid < COLS_PER_TILE) col_g[tid] = (tid < ncol) ? prm.cols[j0 + tid] : -1;
+        __syncthreads();
 
-            // ================= walk: bit-sliced accumulation of the row half-lists =================
-            uint32_t plo[NPL], phi[NPL];
-#pragma unroll
-            for (int k = 0; k < NPL; k++) { plo[k] = 0u; phi[k] = 0u; }
-            if (group_ok) {
-                const int64_t gp = (int64_t)group * P + p;
-                const int nch = prm.ell_nch[gp];
-                const uint4 *src = prm.ell + prm.ell_off[gp] * 32 + lane;
-                int c = 0;
-                for (; c + 4 <= nch; c += 4) {       // 16 lookups per iteration
-                    uint4 q[4];
-#pragma unroll
-                    for (int u = 0; u < 4; u++) q[u] = __ldg(src + (int64_t)(c + u) * 32);
-                    uint32_t e_lo[2], e_hi[2];       // two "eights" carries
-#pragma unroll
-                    for (int half = 0; half < 2; half++) {
-                        uint32_t f_lo[2], f_hi[2];   // two "fours" carries
-#pragma unroll
-                        for (int qq = 0; qq < 2; qq++) {
-                            const uint4 v = q[half * 2 + qq];
-                            const Mask64 m0 = dict_lookup(bm, masks, v.x), m1 = dict_lookup(bm, masks, v.y);
-                            const Mask64 m2 = dict_lookup(bm, masks, v.z), m3 = dict_lookup(bm, masks, v.w);
-                            uint32_t ta_lo, ta_hi, tb_lo, tb_hi;
-                            PF_CSA(ta_lo, plo[0], plo[0], m0.lo, m1.lo); PF_CSA(ta_hi, phi[0], phi[0], m0.hi, m1.hi);
-                            PF_CSA(tb_lo, plo[0], plo[0], m2.lo, m3.lo); PF_CSA(tb_hi, phi[0], phi[0], m2.hi, m3.hi);
-                            PF_CSA(f_lo[qq], plo[1], plo[1], ta_lo, tb_lo); PF_CSA(f_hi[qq], phi[1], phi[1], ta_hi, tb_hi);
-                        }
-                        PF_CSA(e_lo[half], plo[2], plo[2], f_lo[0], f_lo[1]); PF_CSA(e_hi[half], phi[2], phi[2], f_hi[0], f_hi[1]);
-                    }
-                    uint32_t cl, ch;                 // "sixteens" carry, rippled into planes 4..
-                    PF_CSA(cl, plo[3], plo[3], e_lo[0], e_lo[1]); PF_CSA(ch, phi[3], phi[3], e_hi[0], e_hi[1]);
-#pragma unroll
-                    for (int k = 4; k < NPL; k++) {
-                        const uint32_t tl = plo[k] & cl, th = phi[k] & ch;
-                        plo[k] ^= cl; phi[k] ^= ch; cl = tl; ch = th;
-                    }
-                }
-                for (; c < nch; c++) {               // tail: 4 lookups per iteration
-                    const uint4 v = __ldg(src + (int64_t)c * 32);
-                    const Mask64 m0 = dict_lookup(bm, masks, v.x), m1 = dict_lookup(bm, masks, v.y);
-                    const Mask64 m2 = dict_lookup(bm, masks, v.z), m3 = dict_lookup(bm, masks, v.w);
-                    uint32_t ta_lo, ta_hi, tb_lo, tb_hi, cl, ch;
-                    PF_CSA(ta_lo, plo[0], plo[0], m0.lo, m1.lo); PF_CSA(ta_hi, phi[0], phi[0], m0.hi, m1.hi);
-                    PF_CSA(tb_lo, plo[0], plo[0], m2.lo, m3.lo); PF_CSA(tb_hi, phi[0], phi[0], m2.hi, m3.hi);
-                    PF_CSA(cl, plo[1], plo[1], ta_lo, tb_lo); PF_CSA(ch, phi[1], phi[1], ta_hi, tb_hi);
-#pragma unroll
-                    for (int k = 2; k < NPL; k++) {
-                        const uint32_t tl = plo[k] & cl, th = phi[k] & ch;
-                        plo[k] ^= cl; phi[k] ^= ch; cl = tl; ch = th;
-                    }
-                }
-            }
-            // ================= pair reduce: lane h keeps columns [32h, 32h+32) of both halves =================
-            uint32_t R[NPL + 1];
-            {
-                uint32_t carry = 0u;
-#pragma unroll
-                for (int k = 0; k < NPL; k++) {
-                    const uint32_t mine = h ? phi[k] : plo[k];
-                    const uint32_t send = h ? plo[k] : phi[k];
-                    const uint32_t theirs = __shfl_xor_sync(0xffffffffu, send, 1);
-                    const uint32_t u = mine ^ theirs;
-                    R[k] = u ^ carry;
-                    carry = (mine & theirs) | (u & carry);
-                }
-                R[NPL] = carry;
-            }
-            // ================= epilogue: counts -> Jaccard -> S, N (registers) =================
-            const int cbase = 32 * h;
+        // columns of this lane that are real pairs: inside the block and not the row's own genome (isValidPair)
+        uint32_t valid = 0u;
+        if (row_ok) {
 #pragma unroll
             for (int jj = 0; jj < 32; jj++) {
-                const int col = cbase + jj;
-                uint32_t cnt = 0;
+                const int gj = col_g[cbase + jj];
+                if (gj >= 0 && gj != gi) valid |= 1u << jj;
+            }
+        }
+
+        double S[32];
+        uint32_t Np[N_PLANES_N];
 #pragma unroll
-                for (int k = 0; k <= NPL; k++) cnt |= ((R[k] >> jj) & 1u) << k;
-                const bool active = row_ok && col >= c0 && col < c1;
-                if (active) {
-                    const int gj = col_g[col];
-                    if (gj == gi) cnt = 0;      // a genome is never paired with itself (isValidPair, ds_impl.hpp:89-91)
-                    if (prm.counts_out)
-                        prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = (int32_t)cnt;
-                    if (cnt > 0) {
-                        const int den = ta + col_tv[col] - (int)cnt;
-                        S[jj] += (double)(int)cnt / (double)den;   // algorithm_impl.hpp:250-254
-                        n16[jj >> 1] += 1u << (16 * (jj & 1));
+        for (int j = 0; j < 32; j++) S[j] = 0.0;
+#pragma unroll
+        for (int k = 0; k < N_PLANES_N; k++) Np[k] = 0u;
+
+        uint32_t plo[NPL], phi[NPL];     // bit-sliced counters of this lane's half list: columns 0..31 / 32..63
+        uint32_t pe_lo = 0u, pe_hi = 0u; // pending carry of weight 8 (one per two 8-lookup steps)
+        bool pending = false;
+#pragma unroll
+        for (int k = 0; k < NPL; k++) { plo[k] = 0u; phi[k] = 0u; }
+
+        // ---- software pipeline state: descriptors two stages ahead, slab extents one stage ahead ----
+        uint32_t st_cur = 0u, st_nxt = 0u;     // p | q << 16 | flags << 24 of stages k and k + 1
+        if (nst > 0) st_cur = load_stage(prm.stages + sb).w;
+        if (nst > 1) st_nxt = load_stage(prm.stages + sb + 1).w;
+        const int64_t slab0 = (int64_t)group * P * NRANGE;
+        int64_t o_cur = 0; int n_cur = 0;
+        if (group_ok && nst > 0) {
+            const int64_t gi0 = slab0 + (int64_t)st_p(st_cur) * NRANGE + st_q(st_cur);
+            o_cur = prm.ell_off[gi0];
+            n_cur = (int)(prm.ell_off[gi0 + 1] - o_cur);
+        }
+        uint4 cur0 = make_uint4(0, 0, 0, 0), cur1 = cur0;
+        if (n_cur > 0) {
+            const uint4 *src = prm.ell + o_cur * 32 + lane;
+            cur0 = __ldg(src); cur1 = __ldg(src + 32);
+        }
+        int ta = (row_ok && nst > 0) ? prm.T[(int64_t)st_p(st_cur) * prm.t_ld + ti] : 0;
+
+        for (int k = 0; k < nst; k++) {
+            const int slot = k & 1;
+            uint4 st_n2 = make_uint4(0u, 0u, 0u, 0u);
+            if (k + 2 < nst) st_n2 = load_stage(prm.stages + sb + k + 2);
+            int64_t o_nxt = 0; int n_nxt = 0;
+            if (group_ok && k + 1 < nst) {
+                const int64_t gi1 = slab0 + (int64_t)st_p(st_nxt) * NRANGE + st_q(st_nxt);
+                o_nxt = prm.ell_off[gi1];
+                n_nxt = (int)(prm.ell_off[gi1 + 1] - o_nxt);
+            }
+            int ta_nxt = 0;
+            if (st_last(st_cur) && row_ok && k + 1 < nst) ta_nxt = prm.T[(int64_t)st_p(st_nxt) * prm.t_ld + ti];
+
+            mbar_wait(&full[slot], use[slot] & 1u);
+            use[slot]++;
+
+            // ================= walk: bit-sliced accumulation of the row half-lists =================
+            {
+                const unsigned char *bm = stage_mem + (size_t)slot * STAGE_BYTES;
+                const uint2 *masks = reinterpret_cast<const uint2 *>(bm + BM_BYTES);
+                const uint4 *src = prm.ell + o_cur * 32 + lane;
+                const uint4 *src_nxt = prm.ell + o_nxt * 32 + lane;
+                for (int c = 0; c < n_cur; c += 2) {
+                    uint4 nx0 = cur0, nx1 = cur1;
+                    if (c + 2 < n_cur) {
+                        nx0 = __ldg(src + (int64_t)(c + 2) * 32); nx1 = __ldg(src + (int64_t)(c + 3) * 32);
+                    } else if (n_nxt > 0) {
+                        nx0 = __ldg(src_nxt); nx1 = __ldg(src_nxt + 32);
+                    }
+                    // 8 lookups -> one carry of weight 8
+                    uint32_t f_lo[2], f_hi[2];
+#pragma unroll
+                    for (int qq = 0; qq < 2; qq++) {
+                        const uint4 v = qq ? cur1 : cur0;
+                        const Mask64 m0 = dict_lookup(bm, masks, v.x), m1 = dict_lookup(bm, masks, v.y);
+                        const Mask64 m2 = dict_lookup(bm, masks, v.z), m3 = dict_lookup(bm, masks, v.w);
+                        uint32_t ta_lo, ta_hi, tb_lo, tb_hi;
+                        PF_CSA(ta_lo, plo[0], plo[0], m0.lo, m1.lo); PF_CSA(ta_hi, phi[0], phi[0], m0.hi, m1.hi);
+                        PF_CSA(tb_lo, plo[0], plo[0], m2.lo, m3.lo); PF_CSA(tb_hi, phi[0], phi[0], m2.hi, m3.hi);
+                        PF_CSA(f_lo[qq], plo[1], plo[1], ta_lo, tb_lo); PF_CSA(f_hi[qq], phi[1], phi[1], ta_hi, tb_hi);
+                    }
+                    uint32_t e_lo, e_hi;
+                    PF_CSA(e_lo, plo[2], plo[2], f_lo[0], f_lo[1]); PF_CSA(e_hi, phi[2], phi[2], f_hi[0], f_hi[1]);
+                    if (!pending) {           // warp-uniform: keep the eights carry for the next step
+                        pe_lo = e_lo; pe_hi = e_hi; pending = true;
+                    } else {                  // two eights -> plane 3, the sixteens carry ripples into planes 4..
+                        uint32_t cl, ch;
+                        PF_CSA(cl, plo[3], plo[3], pe_lo, e_lo); PF_CSA(ch, phi[3], phi[3], pe_hi, e_hi);
+#pragma unroll
+                        for (int kk = 4; kk < NPL; kk++) {
+                            const uint32_t tl = plo[kk] & cl, th = phi[kk] & ch;
+                            plo[kk] ^= cl; phi[kk] ^= ch; cl = tl; ch = th;
+                        }
+                        pending = false;
+                    }
+                    cur0 = nx0; cur1 = nx1;
+                }
+                if (n_cur == 0 && n_nxt > 0) { cur0 = __ldg(src_nxt); cur1 = __ldg(src_nxt + 32); }
+            }
+            // ================= release the slot; the last warp to leave refills it =================
+            __syncwarp();
+            if (lane == 0) {
+                const uint32_t old = atom_add_acq_rel_smem(&done[slot], 1u);
+                if (old == TILE_WARPS - 1) {
+                    done[slot] = 0u;
+                    if (k + 2 < nst) issue(st_n2, slot, cb);
+                }
+            }
+
+            if (st_last(st_cur)) {
+                // ================= SCP finished: fold the pending carry, pair-reduce, epilogue =================
+                const int p = st_p(st_cur);
+                if (pending) {
+                    uint32_t cl = pe_lo, ch = pe_hi;
+#pragma unroll
+                    for (int kk = 3; kk < NPL; kk++) {
+                        const uint32_t tl = plo[kk] & cl, th = phi[kk] & ch;
+                        plo[kk] ^= cl; phi[kk] ^= ch; cl = tl; ch = th;
+                    }
+                    pending = false;
+                }
+                // lane h keeps columns [32h, 32h+32) of both halves of the row
+                uint32_t R[NPL + 1];
+                {
+                    uint32_t carry = 0u;
+#pragma unroll
+                    for (int kk = 0; kk < NPL; kk++) {
+                        const uint32_t mine = h ? phi[kk] : plo[kk];
+                        const uint32_t send = h ? plo[kk] : phi[kk];
+                        const uint32_t theirs = __shfl_xor_sync(0xffffffffu, send, 1);
+                        const uint32_t u = mine ^ theirs;
+                        R[kk] = (u ^ carry) & valid;
+                        carry = (mine & theirs) | (u & carry);
+                        plo[kk] = 0u; phi[kk] = 0u;
+                    }
+                    R[NPL] = carry & valid;
+                }
+                // N += (c > 0), bit-sliced
+                {
+                    uint32_t nz = 0u;
+#pragma unroll
+                    for (int kk = 0; kk <= NPL; kk++) nz |= R[kk];
+#pragma unroll
+                    for (int kk = 0; kk < N_PLANES_N; kk++) { const uint32_t tt = Np[kk] & nz; Np[kk] ^= nz; nz = tt; }
+                }
+                const int32_t *ct = colT + (p & 3) * COLS_PER_TILE + cbase;
+                // counts of 4 columns at a time: nibble -> one bit per byte ((n * 0x00204081) & 0x01010101)
+#pragma unroll
+                for (int g4 = 0; g4 < 8; g4++) {
+                    uint32_t lo = 0u, hi = 0u;
+#pragma unroll
+                    for (int kk = 0; kk <= NPL; kk++) {
+                        const uint32_t sp = (((R[kk] >> (4 * g4)) & 15u) * 0x00204081u) & 0x01010101u;
+                        if (kk < 8) lo += sp << kk; else hi += sp << (kk - 8);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const int jj = 4 * g4 + u;
+                        const int cnt = (int)(((lo >> (8 * u)) & 0xffu) | (((hi >> (8 * u)) & 0xffu) << 8));
+                        if (prm.counts_out) {
+                            const int col = cbase + jj;
+                            if (row_ok && col < ncol)
+                                prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = cnt;
+                        }
+                        const int den = max(ta + ct[jj] - cnt, 1);
+                        S[jj] += (double)cnt / (double)den;       // algorithm_impl.hpp:250-254; cnt == 0 adds +0.0
                     }
                 }
+                ta = ta_nxt;
             }
-            c0 = c1;
+            st_cur = st_nxt; st_nxt = st_n2.w;
+            o_cur = o_nxt; n_cur = n_nxt;
         }
-    }
 
-    // ================= output: AJI = S / N (computeAJI) into the dense matrix =================
-    const int cbase = 32 * h;
+        // ================= output: AJI = S / N (computeAJI) into the dense matrix =================
 #pragma unroll
-    for (int jj = 0; jj < 32; jj++) {
-        const int col = cbase + jj;
-        if (row_ok && col < ncol) {
-            const int gj = col_g[col];
-            const int n = (int)((n16[jj >> 1] >> (16 * (jj & 1))) & 0xffffu);
-            const double aji = (n > 0) ? S[jj] / (double)n : 0.0;
-            const int64_t j = j0 + col;
-            if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + j] = S[jj];
-            if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + j] = n;
-            if (prm.symmetric) {
-                if (gi < gj) {
-                    prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = aji;
-                    prm.out[(int64_t)gj * prm.out_rs + (int64_t)gi * prm.out_cs] = aji;
-                } else if (gi == gj) {
-                    prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = 0.0;
+        for (int jj = 0; jj < 32; jj++) {
+            const int col = cbase + jj;
+            if (row_ok && col < ncol) {
+                const int gj = col_g[col];
+                int n = 0;
+#pragma unroll
+                for (int kk = 0; kk < N_PLANES_N; kk++) n |= (int)((Np[kk] >> jj) & 1u) << kk;
+                const double aji = (n > 0) ? S[jj] / (double)n : 0.0;
+                const int64_t j = j0 + col;
+                if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + j] = S[jj];
+                if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + j] = n;
+                if (prm.symmetric) {
+                    if (gi < gj) {
+                        prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = aji;
+                        prm.out[(int64_t)gj * prm.out_rs + (int64_t)gi * prm.out_cs] = aji;
+                    } else if (gi == gj) {
+                        prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = 0.0;
+                    }
+                } else {
+                    prm.out[(int64_t)row * prm.out_rs + j * prm.out_cs] = (gi == gj) ? 0.0 : aji;
                 }
-            } else {
-                prm.out[(int64_t)row * prm.out_rs + j * prm.out_cs] = (gi == gj) ? 0.0 : aji;
             }
         }
+        __syncthreads();   // every warp is done with col_g / colT / both slots before the next tile refills them
     }
 }
 

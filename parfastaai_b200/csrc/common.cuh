@@ -13,12 +13,42 @@ namespace pfaai {
 constexpr int NTETRA = PFAAI_NTETRAMERS;     // 160000
 constexpr int TET_BITS = 18;                 // 2^18 = 262144 > 160000
 constexpr uint32_t TET_MASK = (1u << TET_BITS) - 1;
-constexpr uint32_t ELL_SENTINEL = NTETRA;    // padding value of packed row slices; its bitmap word is always 0
 
 // ---- tile geometry of the core kernel ----
 constexpr int ROWS_PER_WARP = 16;            // one warp = 16 rows x 2 half-lists
 constexpr int COLS_PER_TILE = 64;            // one 64-bit column mask per distinct tetramer
-constexpr int BM_WORDS = NTETRA / 16 + 1;    // 16 presence bits + 16 rank bits per word; last word = sentinel
+constexpr int TILE_WARPS = 16;               // 512 threads, <= 128 registers each
+constexpr int TILE_THREADS = TILE_WARPS * 32;
+constexpr int TILE_ROWS = TILE_WARPS * ROWS_PER_WARP;   // 256 rows x 64 columns per tile
+
+// The tetramer universe is cut into NRANGE ranges; one pipeline stage holds the dictionary of one
+// (column block, SCP, range): a presence/rank bitmap over the range plus one 64-bit column mask per
+// distinct tetramer.  Row lists are stored per range with range-local ids.
+constexpr int NRANGE = 2;
+constexpr int RANGE_T = NTETRA / NRANGE;     // 80000 tetramers per range
+constexpr int BM_WORDS = RANGE_T / 16;       // 5000 words: 16 presence bits (low) + 16-bit rank (high)
+constexpr int BM_WORDS_PAD = BM_WORDS + 4;   // + 4 always-zero words: the padding id lands there
+constexpr int BM_BYTES = BM_WORDS_PAD * 4;   // 20016, a multiple of 16 (bulk-copy granularity)
+constexpr uint32_t PAD_ID = RANGE_T;         // padding value of packed row slices (range-local id)
+// a range-local id v is stored in the row slabs as  x = (v>>4) << 7 | (31 - (v&15)):  x>>5 is the byte offset of
+// its bitmap word, x&31 the left shift that moves its presence bit to bit 31 (and drops the rank half-word)
+__host__ __device__ __forceinline__ uint32_t slab_encode(uint32_t v) { return ((v >> 4) << 7) | (31u - (v & 15u)); }
+constexpr int MAX_SUB = 64;                   // a (block, SCP, range) dictionary is split into <= 8 column sub-ranges
+
+// shared memory of the tile kernel: [misc 2 KB][stage 0][stage 1]
+constexpr int SMEM_TOTAL = 227 * 1024;                       // 232448
+constexpr int SMEM_MISC = 2048;
+constexpr int STAGE_BYTES = ((SMEM_TOTAL - SMEM_MISC) / 2) & ~127;   // 115200
+constexpr int MASK_CAP = ((STAGE_BYTES - BM_BYTES) / 8) & ~1;        // entries incl. the all-zero miss slot 0
+
+struct __align__(16) StageDesc {             // one pipeline stage = one bulk copy
+    int64_t off;                             // byte offset of the blob [bitmap BM_BYTES][masks] in the dictionary buffer
+    uint32_t bytes;                          // size of the bulk copy (multiple of 16)
+    uint16_t p;                              // SCP index
+    uint8_t q;                               // tetramer range
+    uint8_t flags;                           // 1 = first stage of SCP p, 2 = last stage of SCP p
+};
+static_assert(sizeof(StageDesc) == 16, "StageDesc is loaded as one uint4");
 
 struct Ctx;  // pfaai_gpu.cu
 

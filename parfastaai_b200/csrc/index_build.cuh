@@ -238,57 +238,4 @@ __global__ void __launch_bounds__(RS_THREADS) k_radix_scatter(const uint64_t *__
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// Row-slice packing (per compute call): the rows of the output are regrouped 16 at a time into
-// warp-interleaved slices so that the tile kernel's per-lane list walk is one coalesced 512-byte
-// LDG.128 per warp.  Lane l = 2*r + h of group g walks elements k = 2*k' + h of row g*16+r's list:
-//   slice[(off(g,p) + c)*32 + l] = { list[2*(4c+0)+h], list[2*(4c+1)+h], list[2*(4c+2)+h], list[2*(4c+3)+h] }
-// padded with ELL_SENTINEL.  n_chunks(g,p) = ceil(max_r len / 8).
-// ------------------------------------------------------------------------------------------------
-__global__ void k_pack_count(const int64_t *__restrict__ seg_off, const int32_t *__restrict__ rows, int n_rows,
-                             int n_groups, int P, int32_t *__restrict__ nch) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (int64_t)n_groups * P) return;
-    const int g = (int)(i / P), p = (int)(i % P);
-    int mx = 0;
-    for (int r = 0; r < ROWS_PER_WARP; r++) {
-        const int row = g * ROWS_PER_WARP + r;
-        if (row < n_rows) {
-            const int64_t s = (int64_t)rows[row] * P + p;
-            mx = max(mx, (int)(seg_off[s + 1] - seg_off[s]));
-        }
-    }
-    nch[i] = (mx + 7) >> 3;
-}
-
-__global__ void __launch_bounds__(256) k_pack_fill(const int64_t *__restrict__ seg_off, const uint32_t *__restrict__ vals,
-                                                    const int32_t *__restrict__ rows, int n_rows, int n_groups, int P,
-                                                    const int64_t *__restrict__ ell_off, const int32_t *__restrict__ nch,
-                                                    uint4 *__restrict__ ell) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const int r = lane >> 1, h = lane & 1;
-    for (int64_t w = warp0; w < (int64_t)n_groups * P; w += nwarps) {
-        const int g = (int)(w / P), p = (int)(w % P);
-        const int row = g * ROWS_PER_WARP + r;
-        int64_t o = 0; int len = 0;
-        if (row < n_rows) {
-            const int64_t s = (int64_t)rows[row] * P + p;
-            o = seg_off[s]; len = (int)(seg_off[s + 1] - o);
-        }
-        const int n = nch[w];
-        uint4 *dst = ell + ell_off[w] * 32 + lane;
-        for (int c = 0; c < n; c++) {
-            uint32_t q[4];
-#pragma unroll
-            for (int e = 0; e < 4; e++) {
-                const int k = 2 * (4 * c + e) + h;
-                q[e] = (k < len) ? vals[o + k] : ELL_SENTINEL;
-            }
-            dst[(int64_t)c * 32] = make_uint4(q[0], q[1], q[2], q[3]);
-        }
-    }
-}
-
 }  // namespace pfaai

@@ -8,6 +8,7 @@
 #include "aji_tile.cuh"
 #include "common.cuh"
 #include "index_build.cuh"
+#include "tile_index.cuh"
 
 namespace pfaai {
 
@@ -33,10 +34,11 @@ struct Ctx {
     DevBuf F, Lc, Lp64, Lp32, T, seg_len, seg_off, itemsA, itemsB, vals, tile_sums, block_hist, block_base, flags;
     // compute
     DevBuf rows, row_t, cols, col_t, ell_nch, ell_off, ell, tiles, out, S_out, N_out, counts_out;
+    DevBuf nsub, sub, colT, blob, stage_off, stages, stage_begin;
     int64_t out_rows = 0, out_cols = 0;
     int last_mode = -1;
     // events / stats
-    cudaEvent_t ev[12] = {};
+    cudaEvent_t ev[14] = {};
     pfaai_timings_t tm = {};
     int launches = 0;
 };
@@ -64,7 +66,7 @@ template <typename T> static inline T *ptr(DevBuf &b) { return reinterpret_cast<
 #define PF_TRY(call) do { int rc__ = (call); if (rc__ != PFAAI_OK) return rc__; } while (0)
 #define PF_LAUNCH_CHECK(c) do { (c)->launches++; PF_CUDA((c), cudaGetLastError()); } while (0)
 
-enum { EV_H2D0, EV_H2D1, EV_B0, EV_S0, EV_S1, EV_B1, EV_P0, EV_P1, EV_T0, EV_T1, EV_D0, EV_D1 };
+enum { EV_H2D0, EV_H2D1, EV_B0, EV_S0, EV_S1, EV_B1, EV_P0, EV_P1, EV_T0, EV_T1, EV_D0, EV_D1, EV_K0, EV_K1 };
 
 static float ev_ms(Ctx *c, int a, int b) {
     float ms = 0.f;
@@ -137,7 +139,8 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
     cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->F, &c->Lc, &c->Lp64, &c->Lp32, &c->T, &c->seg_len, &c->seg_off, &c->itemsA, &c->itemsB, &c->vals,
                      &c->tile_sums, &c->block_hist, &c->block_base, &c->flags, &c->rows, &c->row_t, &c->cols, &c->col_t,
-                     &c->ell_nch, &c->ell_off, &c->ell, &c->tiles, &c->out, &c->S_out, &c->N_out, &c->counts_out};
+                     &c->ell_nch, &c->ell_off, &c->ell, &c->tiles, &c->out, &c->S_out, &c->N_out, &c->counts_out,
+                     &c->nsub, &c->sub, &c->colT, &c->blob, &c->stage_off, &c->stages, &c->stage_begin};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
@@ -295,12 +298,6 @@ int64_t pfaai_gpu_n_pairs(int mode, int G, int nQ) {
 // =====================================================================================================
 namespace pfaai {
 
-constexpr int TILE_WARPS = 12;                               // 384 threads, <= 168 registers each
-constexpr int TILE_ROWS = TILE_WARPS * ROWS_PER_WARP;        // 192 rows x 64 cols per CTA
-constexpr int SMEM_FIXED = ((BM_WORDS + 3) & ~3) * 4 + COLS_PER_TILE * (8 + 4 + 4 + 4) + 36 * 4;
-constexpr int SMEM_TOTAL = 227 * 1024;
-constexpr int MASK_CAP = (SMEM_TOTAL - SMEM_FIXED) / 8 - 1;
-
 struct ModePlan {
     std::vector<int32_t> rows, row_t, cols, col_t;
     int64_t out_rows = 0, out_cols = 0, rs = 0, cs = 0;
@@ -350,9 +347,12 @@ static int upload_i32(Ctx *c, DevBuf &b, const std::vector<int32_t> &v) {
 
 template <int NPL>
 static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles) {
-    auto kern = aji_tile_kernel<TILE_WARPS, NPL>;
+    auto kern = aji_tile_kernel<NPL>;
     PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
-    kern<<<(unsigned)n_tiles, TILE_WARPS * 32, SMEM_TOTAL, c->stream>>>(prm);
+    // persistent CTAs, one per SM; CTA b walks tiles b, b + grid, ... (row-block-major order keeps the
+    // concurrently processed tiles on the same row slabs, which stay L2-resident)
+    const int grid = std::min(n_tiles, c->sm_count);
+    kern<<<(unsigned)grid, TILE_THREADS, SMEM_TOTAL, c->stream>>>(prm);
     PF_LAUNCH_CHECK(c);
     return PFAAI_OK;
 }
@@ -365,36 +365,82 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     const int P = c->P;
     const int n_rows = (int)m.rows.size(), n_cols = (int)m.cols.size();
     const int n_groups = (n_rows + ROWS_PER_WARP - 1) / ROWS_PER_WARP;
-    const int launches_before = c->launches;
-    // plane capacity: a lane performs 4*ceil(max_len/8) lookups per SCP
-    const int lane_lookups = 4 * ((c->max_len + 7) / 8);
-    if (lane_lookups > 4095) { set_error(c, "compute: a (SCP, genome) tetramer list exceeds 8184 entries"); return PFAAI_ERR_CONSTRUCT; }
+    // bit-plane capacity: per SCP a lane performs <= max_len/2 + 16 lookups (two ranges, each padded to 8 per lane)
+    const int lane_lookups = c->max_len / 2 + 16;
+    if (lane_lookups > 4095) { set_error(c, "compute: a (SCP, genome) tetramer list exceeds 8158 entries"); return PFAAI_ERR_CONSTRUCT; }
+    if (P > 1023) { set_error(c, "compute: more than 1023 SCPs"); return PFAAI_ERR_CONSTRUCT; }
 
     PF_CUDA(c, cudaEventRecord(c->ev[EV_P0], c->stream));
     PF_TRY(upload_i32(c, c->rows, m.rows)); PF_TRY(upload_i32(c, c->row_t, m.row_t));
     PF_TRY(upload_i32(c, c->cols, m.cols)); PF_TRY(upload_i32(c, c->col_t, m.col_t));
-    // ---- pack the row slices ----
-    const int64_t ngp = (int64_t)n_groups * P;
-    PF_TRY(ensure(c, c->ell_nch, sizeof(int32_t) * (size_t)ngp));
-    PF_TRY(ensure(c, c->ell_off, sizeof(int64_t) * (size_t)(ngp + 1)));
-    k_pack_count<<<(unsigned)ceil_div64(ngp, 256), 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), ptr<int32_t>(c->rows), n_rows,
-                                                                        n_groups, P, ptr<int32_t>(c->ell_nch));
+    // ---- K4a: pack the row slabs ----
+    const int64_t ngp = (int64_t)n_groups * P, nslab = ngp * NRANGE;
+    PF_TRY(ensure(c, c->ell_nch, sizeof(int32_t) * (size_t)nslab));
+    PF_TRY(ensure(c, c->ell_off, sizeof(int64_t) * (size_t)(nslab + 1)));
+    k_pack_count<<<(unsigned)ceil_div64(ngp, 256), 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals),
+                                                                        ptr<int32_t>(c->rows), n_rows, n_groups, P,
+                                                                        ptr<int32_t>(c->ell_nch));
     PF_LAUNCH_CHECK(c);
-    PF_TRY(launch_scan(c, ptr<int32_t>(c->ell_nch), ngp, ptr<int64_t>(c->ell_off), nullptr));
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->ell_nch), nslab, ptr<int64_t>(c->ell_off), nullptr));
     int64_t total_chunks = 0;
-    PF_CUDA(c, cudaMemcpyAsync(&total_chunks, ptr<int64_t>(c->ell_off) + ngp, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(&total_chunks, ptr<int64_t>(c->ell_off) + nslab, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
     PF_TRY(ensure(c, c->ell, sizeof(uint4) * 32 * (size_t)total_chunks));
     if (total_chunks > 0) {
         k_pack_fill<<<(unsigned)std::min<int64_t>(ceil_div64(ngp, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
             ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), ptr<int32_t>(c->rows), n_rows, n_groups, P, ptr<int64_t>(c->ell_off),
-            ptr<int32_t>(c->ell_nch), ptr<uint4>(c->ell));
+            ptr<uint4>(c->ell));
         PF_LAUNCH_CHECK(c);
     }
     PF_CUDA(c, cudaEventRecord(c->ev[EV_P1], c->stream));
-    // ---- tile list: row block x column block, I-major so that concurrently resident CTAs share the row
-    //      block's slices in L2; symmetric mode keeps only tiles that contain a cell with row < col ----
+    // ---- K4b: column-block dictionaries + stage lists ----
     const int nrb = (n_groups + TILE_WARPS - 1) / TILE_WARPS, ncb = (n_cols + COLS_PER_TILE - 1) / COLS_PER_TILE;
+    int max_sub = 1;
+    while (max_sub < MAX_SUB && (int64_t)(COLS_PER_TILE / max_sub) * c->max_len + 1 > MASK_CAP) max_sub *= 2;
+    const int64_t ndict = (int64_t)ncb * P * NRANGE;
+    PF_TRY(ensure(c, c->nsub, sizeof(int32_t) * (size_t)ndict));
+    PF_TRY(ensure(c, c->sub, sizeof(SubDesc) * (size_t)(ndict * max_sub)));
+    PF_TRY(ensure(c, c->colT, sizeof(int32_t) * (size_t)ncb * P * COLS_PER_TILE));
+    PF_TRY(ensure(c, c->stage_off, sizeof(int64_t) * (size_t)(ndict + 1)));
+    PF_TRY(ensure(c, c->stages, sizeof(StageDesc) * (size_t)(ndict * max_sub)));
+    PF_TRY(ensure(c, c->stage_begin, sizeof(int64_t) * (size_t)(ncb + 1)));
+    {
+        const int64_t col_postings = std::min<int64_t>(c->nF, (int64_t)n_cols * P * c->max_len);
+        const size_t guess = (size_t)ndict * (BM_BYTES + 16) + 8 * (size_t)col_postings;
+        if (c->blob.cap < guess) PF_TRY(ensure(c, c->blob, guess));
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
+    PF_CUDA(c, cudaFuncSetAttribute(k_dict_build, cudaFuncAttributeMaxDynamicSharedMemorySize, DB_SMEM));
+    unsigned long long *cursor = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->flags.p) + 32);
+    for (int attempt = 0;; attempt++) {
+        PF_CUDA(c, cudaMemsetAsync(reinterpret_cast<char *>(c->flags.p) + 8, 0, 56, c->stream));   // flags[2..], cursor
+        DictParams dp;
+        dp.seg_off = ptr<int64_t>(c->seg_off); dp.vals = ptr<uint32_t>(c->vals);
+        dp.cols = ptr<int32_t>(c->cols); dp.col_t = ptr<int32_t>(c->col_t); dp.n_cols = n_cols;
+        dp.T = ptr<int32_t>(c->T); dp.t_ld = c->G; dp.P = P; dp.max_sub = max_sub;
+        dp.blob = ptr<unsigned char>(c->blob); dp.blob_cap = c->blob.cap; dp.cursor = cursor;
+        dp.nsub = ptr<int32_t>(c->nsub); dp.sub = ptr<SubDesc>(c->sub); dp.colT = ptr<int32_t>(c->colT);
+        dp.err = ptr<int>(c->flags) + 3;
+        if (ndict > 0) {
+            k_dict_build<<<(unsigned)(ncb * P), DB_THREADS, DB_SMEM, c->stream>>>(dp);
+            PF_LAUNCH_CHECK(c);
+        }
+        unsigned long long fl[4];   // {flags[2], flags[3]}, -, -, cursor at byte 32
+        PF_CUDA(c, cudaMemcpyAsync(fl, reinterpret_cast<char *>(c->flags.p) + 8, 32, cudaMemcpyDeviceToHost, c->stream));
+        PF_CUDA(c, cudaStreamSynchronize(c->stream));
+        const bool overflow = (fl[0] >> 32) != 0;
+        if (!overflow) break;
+        if (attempt > 0) { set_error(c, "compute: dictionary buffer overflow after resize"); return PFAAI_ERR_CONSTRUCT; }
+        PF_TRY(ensure(c, c->blob, (size_t)fl[3] + 4096));
+    }
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->nsub), ndict, ptr<int64_t>(c->stage_off), nullptr));
+    k_stage_fill<<<(unsigned)ceil_div64(ndict + 1, 256), 256, 0, c->stream>>>(ptr<int32_t>(c->nsub), ptr<int64_t>(c->stage_off),
+                                                                             ptr<SubDesc>(c->sub), ncb, P, max_sub,
+                                                                             ptr<StageDesc>(c->stages), ptr<int64_t>(c->stage_begin));
+    PF_LAUNCH_CHECK(c);
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
+    // ---- tile list: row block x column block, I-major so that concurrently resident CTAs share the row
+    //      block's slabs in L2; symmetric mode keeps only tiles that contain a cell with row < col ----
     std::vector<int2> tiles;
     int64_t t_index = 0;
     for (int I = 0; I < nrb; I++)
@@ -422,32 +468,30 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         PF_TRY(ensure(c, c->counts_out, sizeof(int32_t) * nk * P));
         PF_CUDA(c, cudaMemsetAsync(c->counts_out.p, 0, sizeof(int32_t) * nk * P, c->stream));
     }
-    PF_CUDA(c, cudaMemsetAsync(ptr<int>(c->flags) + 2, 0, sizeof(int), c->stream));
     TileParams prm;
-    prm.ell = ptr<uint4>(c->ell); prm.ell_off = ptr<int64_t>(c->ell_off); prm.ell_nch = ptr<int32_t>(c->ell_nch);
+    prm.ell = ptr<uint4>(c->ell); prm.ell_off = ptr<int64_t>(c->ell_off);
     prm.rows = ptr<int32_t>(c->rows); prm.row_t = ptr<int32_t>(c->row_t); prm.n_rows = n_rows; prm.n_groups = n_groups;
-    prm.cols = ptr<int32_t>(c->cols); prm.col_t = ptr<int32_t>(c->col_t); prm.n_cols = n_cols;
-    prm.seg_off = ptr<int64_t>(c->seg_off); prm.vals = ptr<uint32_t>(c->vals);
+    prm.cols = ptr<int32_t>(c->cols); prm.n_cols = n_cols;
+    prm.stages = ptr<StageDesc>(c->stages); prm.stage_begin = ptr<int64_t>(c->stage_begin);
+    prm.blob = ptr<unsigned char>(c->blob); prm.colT = ptr<int32_t>(c->colT);
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
     prm.out = ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric;
     prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
     prm.N_out = want_sn ? ptr<int32_t>(c->N_out) : nullptr;
     prm.counts_out = want_counts ? ptr<int32_t>(c->counts_out) : nullptr;
-    prm.tiles = ptr<int2>(c->tiles); prm.err = ptr<int>(c->flags) + 2; prm.mask_cap = MASK_CAP;
+    prm.tiles = ptr<int2>(c->tiles); prm.n_tiles = (int)tiles.size();
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
     if (!tiles.empty() && c->nF > 0) {
         if (lane_lookups <= 511) PF_TRY(launch_tiles<9>(c, prm, (int)tiles.size()));
         else PF_TRY(launch_tiles<12>(c, prm, (int)tiles.size()));
     }
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
-    int fl[4];
-    PF_TRY(read_flags(c, fl));
-    if (fl[2]) { set_error(c, "compute: a single (SCP, genome) tetramer list overflows the shared-memory dictionary"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
     c->tm.pack_ms = ev_ms(c, EV_P0, EV_P1);
+    c->tm.dict_ms = ev_ms(c, EV_K0, EV_K1);
     c->tm.tile_ms = ev_ms(c, EV_T0, EV_T1);
     c->tm.n_tiles = (int32_t)tiles.size();
     c->tm.n_launches = c->launches;   // build + this compute
-    (void)launches_before;
     // algorithmic bytes of the tile kernel: postings once, segment offsets, T, output once
     c->tm.tile_alg_bytes = 4 * c->nF + 8 * ((int64_t)P * c->G + 1) + 4 * (int64_t)P * c->G +
                            (int64_t)(8 * (double)ncell / c->n_shards);

@@ -58,4 +58,4 @@ def test_no_cpu_fallback(lib):
 def test_struct_layouts():
     from parfastaai_b200 import _lib
     assert _lib.PG_DTYPE.itemsize == 8 and _lib.JAC_DTYPE.itemsize == 24
-    assert C.sizeof(_lib.Timings) == 40
+    assert C.sizeof(_lib.Timings) == 48
