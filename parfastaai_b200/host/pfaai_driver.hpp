@@ -1,0 +1,305 @@
+// pfaai_driver.hpp -- C++17 driver surface of the B200 AJI path (header-only; links libpfaai_gpu.so).
+//
+// Keeps the NAMES and call sequence of the reference's driver API so that main.cpp-style callers read the
+// same (paths relative to the reference repo):
+//     ParFAAIData         include/pfaai/ds_impl.hpp:39-151     all-vs-all
+//     ParFAAIQSubData     include/pfaai/ds_impl.hpp:159-337    query subset (-q)
+//     ParFAAIQryTgtData   include/pfaai/ds_impl.hpp:344-490    query DB vs main DB (-r)
+//     ParFAAIImpl         include/pfaai/algorithm_impl.hpp:38-357   run() = computeJAC() + computeAJI()
+//     DataStructInterface include/pfaai/interface.hpp:200-328  construct(), refLc/refLp/refT/refF, id maps
+// What differs underneath: construct() loads Lc/F/T on the host (fastaai_reader.hpp), uploads them through the
+// C-ABI (include/pfaai_gpu.h) and builds the device index; there is no E array (refE() does not exist);
+// run() executes the tile kernel and brings back the dense AJI matrix (plus JAC/AJI lists for small inputs).
+// All CUDA work happens behind the C-ABI; this header contains no CUDA.  No CPU fallback.
+#pragma once
+#include <chrono>
+#include <cstdio>
+#include <iostream>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/pfaai_gpu.h"
+#include "fastaai_reader.hpp"
+
+namespace pfaai_host {
+
+// == JACTuple<int,double> (interface.hpp:61-75)
+struct JACTuple {
+    int genomeA = -1, genomeB = -1;
+    double S = 0.0;
+    int N = 0;
+};
+
+struct PhaseTimer {
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    double lap_ms() {
+        auto t1 = std::chrono::steady_clock::now();
+        double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        t0 = t1;
+        return ms;
+    }
+};
+
+// JAC/AJI lists (the reference's per-pair vectors) are only materialised up to this many pairs; beyond it
+// the dense matrix is the only product (1.25e9 pairs x 24 B would be 30 GB at BASELINE config 5).
+constexpr int64_t JAC_LIST_MAX_PAIRS = 4000000;
+
+// ---------------------------------------------------------------------------------------------------
+// Common part of the three data-structure classes: host arrays + the device context.
+// ---------------------------------------------------------------------------------------------------
+class DataStructBase {
+  protected:
+    const DBMetaData &m_dbMeta;
+    HostIndex m_ix;
+    std::vector<int32_t> m_Lp;
+    pfaai_gpu_ctx *m_ctx = nullptr;
+    pfaai_status m_errorCode = PFAAI_OK;
+    int m_device = 0;
+    bool m_hostT = false;   // query-DB mode: T comes from the host (F is inner-joined, T is not)
+
+    virtual int loadHostIndex(HostIndex &ix) = 0;   // SQLite rc
+
+  public:
+    explicit DataStructBase(const DBMetaData &meta) : m_dbMeta(meta) {}
+    DataStructBase(const DataStructBase &) = delete;
+    DataStructBase &operator=(const DataStructBase &) = delete;
+    virtual ~DataStructBase() { if (m_ctx) pfaai_gpu_destroy(m_ctx); }
+
+    void setDevice(int device) { m_device = device; }
+    pfaai_gpu_ctx *ctx() const { return m_ctx; }
+    const HostIndex &hostIndex() const { return m_ix; }
+
+    // == refLc / refLp / refT / refF / refProteinSet (interface.hpp:246-256).  refLp/refT are read back from
+    // the device build (parity hooks); refT is row-major P x nGenomes.
+    const std::vector<int32_t> &refLc() const { return m_ix.Lc; }
+    const std::vector<int32_t> &refLp() const { return m_Lp; }
+    const std::vector<int32_t> &refT() const { return m_ix.T; }
+    const std::vector<pfaai_pg_t> &refF() const { return m_ix.F; }
+    const std::vector<std::string> &refProteinSet() const { return m_dbMeta.proteinSet; }
+    int nTetramers() const { return NTETRAMERS; }
+
+    virtual const std::vector<std::string> &refQuerySet() const = 0;
+    virtual const std::vector<std::string> &refTargetSet() const = 0;
+    virtual int qrySetSize() const = 0;
+    virtual int tgtSetSize() const = 0;
+    virtual int64_t nGenomePairs() const = 0;
+    virtual bool isQryGenome(int genome) const = 0;
+    virtual bool isValidPair(int qry, int tgt) const = 0;
+    virtual int64_t genomePairToIndex(int genomeA, int genomeB) const = 0;
+    virtual int mapQueryId(int qry) const = 0;
+    virtual int mapTargetId(int tgt) const = 0;
+    // what the C-ABI needs to know about the mode
+    virtual int mode() const = 0;
+    virtual const std::vector<int32_t> &queryIds() const = 0;
+    virtual unsigned computeFlags() const { return 0u; }
+
+    // == construct() (interface.hpp:306-327): host load, then upload + device build behind the C-ABI
+    virtual pfaai_status construct() {
+        PhaseTimer tm;
+        if (loadHostIndex(m_ix) != SQLITE_OK) {
+            std::cerr << "Error in Lc, F, T host load ; Error code : " << PFAAI_ERR_SQLITE_DB << std::endl;
+            return m_errorCode = PFAAI_ERR_SQLITE_DB;
+        }
+        std::printf("Lc, F, T host load  : %10.3f ms; |F| = %zu\n", tm.lap_ms(), m_ix.F.size());
+        int rc = pfaai_gpu_create(&m_ctx, m_device, 0);
+        if (rc != PFAAI_OK) {
+            std::cerr << "Error in GPU context ; " << pfaai_gpu_last_error(nullptr) << std::endl;
+            return m_errorCode = (pfaai_status)rc;
+        }
+        rc = pfaai_gpu_upload_index(m_ctx, m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(),
+                                    m_hostT ? m_ix.T.data() : nullptr);
+        if (rc == PFAAI_OK) rc = pfaai_gpu_build(m_ctx);
+        if (rc != PFAAI_OK) {
+            std::cerr << "Error in device index build ; " << pfaai_gpu_last_error(m_ctx) << std::endl;
+            return m_errorCode = (pfaai_status)rc;
+        }
+        m_Lp.resize(NTETRAMERS);
+        std::vector<int32_t> Tdev((size_t)m_ix.nProteins * m_ix.nGenomes);
+        rc = pfaai_gpu_get_arrays(m_ctx, nullptr, m_Lp.data(), Tdev.data(), nullptr, nullptr);
+        if (rc != PFAAI_OK) {
+            std::cerr << "Error in device index read-back ; " << pfaai_gpu_last_error(m_ctx) << std::endl;
+            return m_errorCode = (pfaai_status)rc;
+        }
+        if (!m_hostT && Tdev != m_ix.T) {
+            // single-DB modes: the device T (histogram of F) must equal proteinTetramerCounts' T
+            std::cerr << "Error in T construction ; device histogram of F differs from the <SCP>_genomes table" << std::endl;
+            return m_errorCode = PFAAI_ERR_CONSTRUCT;
+        }
+        pfaai_timings_t t;
+        pfaai_gpu_get_timings(m_ctx, &t);
+        std::printf("Device index build  : %10.3f ms; (H2D %.3f ms, build kernels %.3f ms, of which sort %.3f ms)\n", tm.lap_ms(),
+                    t.h2d_ms, t.build_ms, t.sort_ms);
+        return m_errorCode = PFAAI_OK;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+class ParFAAIData : public DataStructBase {
+    const SQLiteSCPDataBase &m_DBIf;
+    std::vector<int32_t> m_noIds;
+    int m_nGenomes;
+    int loadHostIndex(HostIndex &ix) override { return m_DBIf.loadIndex(ix); }
+
+  public:
+    ParFAAIData(const SQLiteSCPDataBase &dbif, const DBMetaData &dbMeta)
+        : DataStructBase(dbMeta), m_DBIf(dbif), m_nGenomes((int)dbMeta.genomeSet.size()) {}
+    const std::vector<std::string> &refQuerySet() const override { return m_dbMeta.genomeSet; }
+    const std::vector<std::string> &refTargetSet() const override { return m_dbMeta.genomeSet; }
+    int qrySetSize() const override { return m_nGenomes; }
+    int tgtSetSize() const override { return m_nGenomes; }
+    int64_t nGenomePairs() const override { return (int64_t)m_nGenomes * (m_nGenomes - 1) / 2; }          // ds_impl.hpp:78-81
+    int64_t genomePairToIndex(int a, int b) const override {                                              // ds_impl.hpp:83-86
+        return (int64_t)m_nGenomes * a + b - ((int64_t)(a + 2) * (a + 1)) / 2;
+    }
+    int mapQueryId(int q) const override { return q; }
+    int mapTargetId(int t) const override { return t; }
+    bool isQryGenome(int) const override { return true; }
+    bool isValidPair(int q, int t) const override { return q < t; }
+    int mode() const override { return PFAAI_ALL_VS_ALL; }
+    const std::vector<int32_t> &queryIds() const override { return m_noIds; }
+};
+
+// ---------------------------------------------------------------------------------------------------
+class ParFAAIQSubData : public DataStructBase {
+    const SQLiteSCPDataBase &m_DBIf;
+    std::vector<std::string> m_qryGenomeSet;
+    int m_nGenomes, m_nQryGenomes;
+    std::vector<int32_t> m_qryLookup;        // query index (file order) -> genome id
+    std::vector<int> m_genomeIndexMap;       // genome id -> query index | index among the non-query genomes
+    std::vector<char> m_qryIndicator;
+    int loadHostIndex(HostIndex &ix) override { return m_DBIf.loadIndex(ix); }
+
+  public:
+    ParFAAIQSubData(const SQLiteSCPDataBase &dbif, const DBMetaData &dbMeta, const std::vector<std::string> &qryGenomeSet)
+        : DataStructBase(dbMeta), m_DBIf(dbif), m_qryGenomeSet(qryGenomeSet), m_nGenomes((int)dbMeta.genomeSet.size()),
+          m_nQryGenomes((int)qryGenomeSet.size()), m_qryLookup(qryGenomeSet.size(), -1), m_genomeIndexMap(dbMeta.genomeSet.size(), -1),
+          m_qryIndicator(dbMeta.genomeSet.size(), 0) {
+        std::unordered_map<std::string, int> qSet;
+        for (int i = 0; i < m_nQryGenomes; i++) qSet.emplace(m_qryGenomeSet[i], i);
+        for (int g = 0, j = 0; g < m_nGenomes; g++) {             // ds_impl.hpp:211-224
+            auto it = qSet.find(dbMeta.genomeSet[g]);
+            if (it != qSet.end()) { m_qryIndicator[g] = 1; m_qryLookup[it->second] = g; m_genomeIndexMap[g] = it->second; }
+            else m_genomeIndexMap[g] = j++;
+        }
+    }
+    const std::vector<std::string> &refQuerySet() const override { return m_qryGenomeSet; }
+    const std::vector<std::string> &refTargetSet() const override { return m_dbMeta.genomeSet; }
+    int qrySetSize() const override { return m_nQryGenomes; }
+    int tgtSetSize() const override { return m_nGenomes; }
+    int64_t nGenomePairs() const override {                                                               // ds_impl.hpp:244-249
+        return (int64_t)m_nQryGenomes * (m_nGenomes - m_nQryGenomes) + (int64_t)m_nQryGenomes * (m_nQryGenomes - 1) / 2;
+    }
+    int64_t genomePairToIndex(int a, int b) const override {                                              // ds_impl.hpp:251-263
+        const int nT = m_nGenomes - m_nQryGenomes;
+        if (m_qryIndicator[b]) {
+            const int64_t qa = m_genomeIndexMap[a], qb = m_genomeIndexMap[b];
+            return (int64_t)m_nQryGenomes * nT + m_nQryGenomes * qa + qb - ((qa + 2) * (qa + 1)) / 2;
+        }
+        return (int64_t)m_genomeIndexMap[a] * nT + m_genomeIndexMap[b];
+    }
+    int mapQueryId(int q) const override { return m_genomeIndexMap[q]; }
+    int mapTargetId(int t) const override { return t; }
+    bool isQryGenome(int g) const override { return m_qryIndicator[g] != 0; }
+    bool isValidPair(int q, int t) const override {                                                       // ds_impl.hpp:270-273
+        return m_qryIndicator[q] && (!m_qryIndicator[t] || m_genomeIndexMap[q] < m_genomeIndexMap[t]);
+    }
+    int mode() const override { return PFAAI_QUERY_SUBSET; }
+    const std::vector<int32_t> &queryIds() const override { return m_qryLookup; }
+};
+
+// ---------------------------------------------------------------------------------------------------
+class ParFAAIQryTgtData : public DataStructBase {
+    const QTSQLiteSCPDataBase &m_qtDBIf;
+    std::vector<int32_t> m_qryIds;
+    int m_nT, m_nQ;
+    bool m_refCompat;
+    int loadHostIndex(HostIndex &ix) override { return m_qtDBIf.loadIndex(ix); }
+
+  public:
+    // refCompat = reproduce the reference's T-lookup labels (q, nQ+t) (ds_impl.hpp:434-436);
+    // needed to match xdb_qt_{jac,aji}.bin; only meaningful when nQ == nT (otherwise the reference reads
+    // wrong / out-of-range columns), so it is ignored for nQ != nT.
+    ParFAAIQryTgtData(const QTSQLiteSCPDataBase &qtDBIf, const DBMetaData &dbMeta, const std::vector<std::string> & /*protSet*/,
+                      bool refCompat = true)
+        : DataStructBase(dbMeta), m_qtDBIf(qtDBIf), m_nT((int)dbMeta.genomeSet.size()), m_nQ((int)dbMeta.qyGenomeSet.size()),
+          m_refCompat(refCompat && dbMeta.genomeSet.size() == dbMeta.qyGenomeSet.size()) {
+        m_hostT = true;
+        m_qryIds.resize(m_nQ);
+        for (int q = 0; q < m_nQ; q++) m_qryIds[q] = m_nT + q;
+    }
+    const std::vector<std::string> &refQuerySet() const override { return m_dbMeta.qyGenomeSet; }
+    const std::vector<std::string> &refTargetSet() const override { return m_dbMeta.genomeSet; }
+    int qrySetSize() const override { return m_nQ; }
+    int tgtSetSize() const override { return m_nT; }
+    int nUnionGenomes() const { return m_nT + m_nQ; }
+    int64_t nGenomePairs() const override { return (int64_t)m_nQ * m_nT; }
+    int64_t genomePairToIndex(int a, int b) const override { return (int64_t)mapQueryId(a) * m_nT + b; }   // ds_impl.hpp:411-413
+    int mapQueryId(int q) const override { return q >= m_nT ? q - m_nT : q; }
+    int mapTargetId(int t) const override { return t; }
+    bool isQryGenome(int g) const override { return g >= m_nT; }
+    bool isValidPair(int q, int t) const override { return q >= m_nT && t < m_nT; }
+    int mode() const override { return PFAAI_QUERY_DB; }
+    const std::vector<int32_t> &queryIds() const override { return m_qryIds; }
+    unsigned computeFlags() const override { return m_refCompat ? PFAAI_FLAG_REF_COMPAT_QT : 0u; }
+    bool refCompat() const { return m_refCompat; }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// == ParFAAIImpl (algorithm_impl.hpp:38-357).  The dense matrix is the primary product; the per-pair JAC / AJI
+// vectors (reference JAC order, initJAC of the mode) are filled when nGenomePairs <= JAC_LIST_MAX_PAIRS.
+// ---------------------------------------------------------------------------------------------------
+class ParFAAIImpl {
+    const DataStructBase &c_pfDSRef;
+    std::vector<JACTuple> m_JAC;
+    std::vector<double> m_AJI;
+    std::vector<double> m_matrix;   // [qrySetSize x tgtSetSize] row-major == printOutput's ajiMatrix (main.cpp:143-154)
+    bool m_haveLists = false;
+
+  public:
+    explicit ParFAAIImpl(const DataStructBase &ds) : c_pfDSRef(ds) {}
+
+    int computeJAC() {
+        PhaseTimer tm;
+        pfaai_gpu_ctx *ctx = c_pfDSRef.ctx();
+        if (!ctx) { std::cerr << "Error in JAC Construction ; construct() has not succeeded" << std::endl; return PFAAI_ERR_CONSTRUCT; }
+        const int64_t np = c_pfDSRef.nGenomePairs();
+        const std::vector<int32_t> &q = c_pfDSRef.queryIds();
+        m_matrix.assign((size_t)c_pfDSRef.qrySetSize() * c_pfDSRef.tgtSetSize(), 0.0);
+        m_haveLists = np <= JAC_LIST_MAX_PAIRS;
+        std::vector<pfaai_jac_t> jac;
+        if (m_haveLists) { jac.resize((size_t)np); m_AJI.assign((size_t)np, 0.0); }
+        const int rc = pfaai_gpu_compute(ctx, c_pfDSRef.mode(), q.empty() ? nullptr : q.data(), (int)q.size(), c_pfDSRef.computeFlags(),
+                                         m_matrix.data(), m_haveLists ? jac.data() : nullptr, m_haveLists ? m_AJI.data() : nullptr,
+                                         nullptr);
+        if (rc != PFAAI_OK) { std::cerr << "Error in JAC Construction ; " << pfaai_gpu_last_error(ctx) << std::endl; return rc; }
+        m_JAC.resize(jac.size());
+        for (size_t i = 0; i < jac.size(); i++) { m_JAC[i].genomeA = jac[i].gA; m_JAC[i].genomeB = jac[i].gB; m_JAC[i].S = jac[i].S; m_JAC[i].N = jac[i].N; }
+        pfaai_timings_t t;
+        pfaai_gpu_get_timings(ctx, &t);
+        std::printf("JAC Construction    : %10.3f ms; (row slabs %.3f ms, dictionaries %.3f ms, tile kernel %.3f ms over %d tiles, D2H %.3f ms)\n",
+                    tm.lap_ms(), t.pack_ms, t.dict_ms, t.tile_ms, t.n_tiles, t.d2h_ms);
+        return PFAAI_OK;
+    }
+    // AJI = S / N is fused into the tile kernel (computeAJI, algorithm_impl.hpp:309-322); kept for call compatibility
+    int computeAJI() { return PFAAI_OK; }
+    int run() {
+        const int rc = computeJAC();
+        return rc != PFAAI_OK ? rc : computeAJI();
+    }
+    bool haveLists() const { return m_haveLists; }
+    const std::vector<JACTuple> &getJAC() const { return m_JAC; }
+    const std::vector<double> &getAJI() const { return m_AJI; }
+    const std::vector<double> &getMatrix() const { return m_matrix; }
+
+    void print_aji() const {
+        std::cout << "AJI Ouput : " << std::endl;
+        std::cout << " [(GP1, GP2,   SUM, NCP) ->  AJI]" << std::endl;
+        for (size_t i = 0; i < m_JAC.size(); i++)
+            std::printf(" [%lld, %.17g -> %03.2f] \n", (long long)c_pfDSRef.genomePairToIndex(m_JAC[i].genomeA, m_JAC[i].genomeB),
+                        m_AJI[i], m_AJI[i]);
+    }
+};
+
+}  // namespace pfaai_host

@@ -57,3 +57,22 @@ def run_lengths_from_sorted_e(E, pair_index, n_pairs, P):
     idx = pair_index(E["gA"].astype(np.int64), E["gB"].astype(np.int64))
     np.add.at(cnt, (idx, E["protein"]), 1)
     return cnt
+
+
+def xantho_db_path():
+    """Rebuild the missing 20-genome data/modified_xantho_fastaai2.db from the F/Lc goldens and the name tables
+    (SURVEY App. C.3): functionally equivalent for every query the reference and our loader issue."""
+    dst_dir = db_path("xdb_subset1.db")  # makes the temp dir
+    dst = os.path.join(os.path.dirname(dst_dir), "modified_xantho_fastaai2.db")
+    if not os.path.exists(dst):
+        from parfastaai_b200 import fastaai_db
+        g = load("xanthodb")
+        P, G = g["t"].shape
+        tet = np.repeat(np.arange(160000, dtype=np.int64), g["lc"])
+        seg = g["f"]["genome"].astype(np.int64) * P + g["f"]["protein"]
+        order = np.lexsort((tet, seg))
+        seg_off = np.zeros(G * P + 1, np.int64)
+        np.cumsum(np.bincount(seg, minlength=G * P), out=seg_off[1:])
+        n = names()
+        fastaai_db.write_db(dst, n["xantho_genomes"], n["xantho_proteins"], seg_off, tet[order].astype(np.int32))
+    return dst

@@ -1,0 +1,90 @@
+"""GPU end-to-end tests of par_fastaai.x (C++17 host -> C-ABI -> sm_100a kernels -> CSV): output BYTES against the
+reference's golden CSVs for the three modes, and against the unmodified reference binary (oracle/_ref, when it
+travelled to the box) on a synthetic FastAAI database."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as ge  # noqa: E402
+from tests import golden_util as gu  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cli():
+    ge.build()
+    return ge.CLI
+
+
+def run(cli, *args, threads="4"):
+    r = subprocess.run([cli, *args], capture_output=True, text=True, env=dict(os.environ, OMP_NUM_THREADS=threads))
+    assert r.returncode == 0, (r.returncode, r.stdout[-500:], r.stderr[-500:])
+    return r
+
+
+def test_all_vs_all_csv_bytes(cli, tmp_path):
+    for db, gold in [(gu.db_path("xdb_subset1.db"), "xdb_subset1_aji_matrix_wheader.csv"),
+                     (gu.db_path("xdb_subset2.db"), "xdb_subset2_aji_matrix_wheader.csv"),
+                     (gu.xantho_db_path(), "xanthodb_aji_matrix_wheader.csv")]:
+        out = tmp_path / ("out_" + gold)
+        r = run(cli, db, str(out))
+        assert out.read_bytes() == gu.csv_bytes(gold), gold
+        assert "Writing output with" in r.stdout and "JAC Construction" in r.stdout
+
+
+def test_query_subset_csv_bytes(cli, tmp_path):
+    out = tmp_path / "qsub.csv"
+    run(cli, gu.xantho_db_path(), str(out), "-q", os.path.join(gu.GOLDEN, "qsub_test_input.txt"))
+    assert out.read_bytes() == gu.csv_bytes("qsub_test_output_matrix_wheader.csv")
+
+
+def test_separator_and_long_options(cli, tmp_path):
+    out = tmp_path / "semi.csv"
+    run(cli, gu.db_path("xdb_subset1.db"), str(out), "--separator=;;")
+    assert out.read_bytes() == gu.csv_bytes("xdb_subset1_aji_matrix_wheader.csv").replace(b",", b";;")
+
+
+def test_query_db_mode_reference_values(cli, tmp_path):
+    """No CSV golden is shipped for -r; the reference's own output on these two DBs (reproducing
+    xdb_qt_aji.bin incl. the 1.0009 cell of the label quirk) is the expectation."""
+    out = tmp_path / "qt.csv"
+    run(cli, gu.db_path("xdb_subset1.db"), str(out), "-r", gu.db_path("xdb_subset2.db"))
+    lines = out.read_text().strip().split("\n")
+    n = gu.names()
+    assert lines[0] == "," + ",".join(n["subset1_genomes"])
+    assert [l.split(",")[0] for l in lines[1:]] == n["subset2_genomes"]
+    M = np.array([[float(x) for x in l.split(",")[1:]] for l in lines[1:]])
+    g = gu.load("xdb_qt")
+    assert np.array_equal(M.reshape(-1), g["aji"])                                  # bit-exact vs xdb_qt_aji.bin
+    assert lines[2].split(",")[4] == "1.0009481433436662"
+    # corrected lookup: every value <= 1 and within 1e-2 of the quirk values
+    out2 = tmp_path / "qt2.csv"
+    run(cli, gu.db_path("xdb_subset1.db"), str(out2), "-r", gu.db_path("xdb_subset2.db"), "--no-ref-compat")
+    M2 = np.array([[float(x) for x in l.split(",")[1:]] for l in out2.read_text().strip().split("\n")[1:]])
+    assert M2.max() <= 1.0 and 0 < np.abs(M2 - M).max() < 1e-2
+
+
+def test_against_reference_binary_on_synthetic_db(cli, tmp_path):
+    ref = os.path.join(ROOT, "oracle", "_ref", "par_fastaai_ref.x")
+    if not os.access(ref, os.X_OK):
+        pytest.skip("oracle/_ref/par_fastaai_ref.x not built (needs /root/reference at build time)")
+    from parfastaai_b200 import fastaai_db, synth
+    N, P = 48, 16
+    off, vals = synth.generate(N, P, seed=99)
+    gn, sn = fastaai_db.synthetic_names(N, P)
+    db = str(tmp_path / "syn.db")
+    fastaai_db.write_db(db, gn, sn, off, vals)
+    qfile = tmp_path / "q.txt"
+    qfile.write_text("\n".join(gn[i] for i in (3, 7, 20, 41)) + "\n")
+    for extra in ([], ["-q", str(qfile)], ["-s", "\t"]):
+        a, b = str(tmp_path / "ours.csv"), str(tmp_path / "ref.csv")
+        run(cli, db, a, *extra)
+        r = subprocess.run([ref, db, b, *extra], capture_output=True, text=True, env=dict(os.environ, OMP_NUM_THREADS="4"))
+        assert r.returncode == 0, r.stderr[-300:]
+        assert open(a, "rb").read() == open(b, "rb").read(), extra
