@@ -96,30 +96,38 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_final(const int32_t *__re
 // (K3: this IS the T matrix in the single-DB modes) with one REDG per posting.
 // ------------------------------------------------------------------------------------------------
 constexpr int MI_THREADS = 256;
-constexpr int MI_ITEMS = 8;
+constexpr int MI_ITEMS = 8;                      // rounds per warp: a warp converts 256 consecutive postings
+
+// largest t in [lo, hi] with Lp[t] <= i   (Lp non-decreasing, Lp[lo] <= i)
+__device__ __forceinline__ int tetramer_of(const int64_t *__restrict__ Lp, int lo, int hi, int64_t i) {
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (Lp[mid] <= i) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
 
 __global__ void __launch_bounds__(MI_THREADS) k_make_items(const pfaai_pg_t *__restrict__ F, const int64_t *__restrict__ Lp,
                                                             int64_t nF, int P, int G, uint64_t *__restrict__ items,
                                                             uint32_t *__restrict__ seg_len, int *__restrict__ err) {
-    const int64_t i0 = ((int64_t)blockIdx.x * MI_THREADS + threadIdx.x) * MI_ITEMS;
-    if (i0 == 0 && Lp[NTETRA] != nF) *err = 2;   // sum(Lc) must equal |F|
-    if (i0 >= nF) return;
-    // largest t with Lp[t] <= i0 (Lp is non-decreasing, Lp[0] = 0)
-    int lo = 0, hi = NTETRA - 1;
-    while (lo < hi) {
-        int mid = (lo + hi + 1) >> 1;
-        if (Lp[mid] <= i0) lo = mid; else hi = mid - 1;
-    }
-    int t = lo;
-    int64_t next = Lp[t + 1];  // Lp has NTETRA+1 entries, Lp[NTETRA] = nF
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * MI_THREADS + threadIdx.x) >> 5;
+    const int64_t w0 = warp * (32 * MI_ITEMS);
+    if (w0 == 0 && lane == 0 && Lp[NTETRA] != nF) *err = 2;   // sum(Lc) must equal |F|
+    if (w0 >= nF) return;
+    // warp-uniform bracket [t_lo, t_hi] of the tetramers this warp's postings belong to (two broadcast searches),
+    // then a short per-item search inside it; all F loads and item stores are lane-consecutive (coalesced)
+    const int t_hi = tetramer_of(Lp, 0, NTETRA - 1, min(w0 + 32 * MI_ITEMS - 1, nF - 1));
+    int t = tetramer_of(Lp, 0, t_hi, w0);
 #pragma unroll
     for (int k = 0; k < MI_ITEMS; k++) {
-        const int64_t i = i0 + k;
+        const int64_t i = w0 + k * 32 + lane;
         if (i >= nF) break;
-        while (i >= next && t < NTETRA - 1) { t++; next = Lp[t + 1]; }
+        t = tetramer_of(Lp, t, t_hi, i);
         const pfaai_pg_t e = F[i];
-        if ((unsigned)e.protein >= (unsigned)P || (unsigned)e.genome >= (unsigned)G) { *err = 1; continue; }
-        const uint32_t seg = (uint32_t)e.genome * (uint32_t)P + (uint32_t)e.protein;
+        uint32_t seg = (uint32_t)e.genome * (uint32_t)P + (uint32_t)e.protein;
+        // a bad id fails the build; it is still counted (in segment 0) so that the sort's histograms stay consistent
+        if ((unsigned)e.protein >= (unsigned)P || (unsigned)e.genome >= (unsigned)G) { *err = 1; seg = 0u; }
         items[i] = ((uint64_t)seg << TET_BITS) | (uint32_t)t;
         atomicAdd(&seg_len[seg], 1u);
     }
@@ -141,100 +149,156 @@ __global__ void k_transpose_t(const uint32_t *__restrict__ seg_len, int P, int G
 }
 
 // ------------------------------------------------------------------------------------------------
-// K2b: stable LSD radix sort, 8-bit digits, hand-written (no CUB/Thrust).
-// A fixed set of RS_BLOCKS persistent blocks each owns one contiguous chunk of the input, so the
-// per-(digit, block) histogram is tiny (256 x RS_BLOCKS) and one small block scans it.
-//   pass = k_radix_hist (read 8 B/item) + k_radix_scan + k_radix_scatter (read 8 B, write 8 B / item;
-//   the last pass writes only the 4-byte tetramer).  Stability: chunk order x tile order x warp strip
-//   order x lane order == input order, ranks by __match_any_sync.
+// K2b: stable LSD radix sort, 8-bit digits, hand-written (no CUB/Thrust), one kernel per pass
+// ("onesweep": chained scan with decoupled look-back).
+//   * The global digit histogram of EVERY pass is derived from the segment histogram seg_len (the sort key is
+//     the segment id), so no pass over the items is spent on counting: k_digit_hist + k_digit_scan.
+//   * k_onesweep: a tile of 8192 items is ranked in registers (per-warp match_any ranks, stable), its 256 digit
+//     counts are published in a [tile][digit] status array (2 flag bits + 62-bit count per word, so |F| >= 2^30
+//     is fine) and the exclusive prefix over the preceding tiles is gathered by look-back; the tile is then
+//     reordered by digit in shared memory and written out with consecutive threads on consecutive addresses.
+//     Per pass and item: read 8 B, write 8 B (last pass: 4 B, the tetramer only) -- the HBM minimum for an
+//     out-of-place pass.  Tiles take their index from an atomic counter, so every tile that is waited on is
+//     already resident (forward progress without a cooperative launch).
+//   Stability: tile order x warp strip order x round order x lane order == input order.
 // ------------------------------------------------------------------------------------------------
-constexpr int RS_THREADS = 256;
-constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 8;                       // rounds per warp strip
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;    // 2048 items
 constexpr int RS_RADIX = 256;
+constexpr int OS_THREADS = 512;
+constexpr int OS_WARPS = OS_THREADS / 32;
+constexpr int OS_ITEMS = 16;                          // rounds per warp strip
+constexpr int OS_TILE = OS_THREADS * OS_ITEMS;        // 8192 items = 64 KB
+constexpr int OS_SMEM = OS_TILE * 8 + OS_WARPS * RS_RADIX * 4 + RS_RADIX * (4 + 8) + 64;
+constexpr int MAX_PASSES = 4;
+constexpr uint64_t OS_FLAG_LOCAL = 1ull << 62, OS_FLAG_INCL = 2ull << 62, OS_COUNT_MASK = (1ull << 62) - 1;
 
-__global__ void __launch_bounds__(RS_THREADS) k_radix_hist(const uint64_t *__restrict__ in, int64_t n, int shift,
-                                                            int64_t chunk, uint32_t *__restrict__ block_hist) {
-    __shared__ uint32_t h[RS_WARPS][RS_RADIX];
-    for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&h[0][0])[i] = 0;
+// hist[pass][d] = number of items whose pass-th key digit is d = sum of seg_len over the segments with that digit
+__global__ void __launch_bounds__(256) k_digit_hist(const uint32_t *__restrict__ seg_len, int64_t nseg, int passes,
+                                                     unsigned long long *__restrict__ hist /*[MAX_PASSES][256]*/) {
+    __shared__ unsigned long long h[MAX_PASSES][RS_RADIX];
+    for (int i = threadIdx.x; i < MAX_PASSES * RS_RADIX; i += blockDim.x) (&h[0][0])[i] = 0ull;
     __syncthreads();
-    const int warp = threadIdx.x >> 5;
-    const int64_t lo = (int64_t)blockIdx.x * chunk, hi = min(lo + chunk, n);
-    for (int64_t i = lo + threadIdx.x; i < hi; i += RS_THREADS)
-        atomicAdd(&h[warp][(uint32_t)(in[i] >> shift) & (RS_RADIX - 1)], 1u);
-    __syncthreads();
-    for (int d = threadIdx.x; d < RS_RADIX; d += RS_THREADS) {
-        uint32_t s = 0;
-#pragma unroll
-        for (int w = 0; w < RS_WARPS; w++) s += h[w][d];
-        block_hist[(int64_t)d * gridDim.x + blockIdx.x] = s;   // digit-major
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < nseg; s += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long n = seg_len[s];
+        if (n)
+            for (int k = 0; k < passes; k++) atomicAdd(&h[k][((uint32_t)s >> (8 * k)) & 255u], n);
     }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * RS_RADIX; i += blockDim.x)
+        if ((&h[0][0])[i]) atomicAdd(&hist[i], (&h[0][0])[i]);
 }
 
-// single block: exclusive scan of the digit-major histogram -> global base of every (digit, block)
-__global__ void __launch_bounds__(1024) k_radix_scan(const uint32_t *__restrict__ block_hist, int64_t n,
-                                                      int64_t *__restrict__ base) {
+// in place: hist[pass][*] -> exclusive prefix (global base of every digit); one block of 256 threads per pass
+__global__ void __launch_bounds__(RS_RADIX) k_digit_scan(unsigned long long *__restrict__ hist) {
     __shared__ int64_t scratch[33];
-    const int64_t per = (n + blockDim.x - 1) / blockDim.x;
-    const int64_t lo = (int64_t)threadIdx.x * per, hi = min(lo + per, n);
-    int64_t s = 0;
-    for (int64_t i = lo; i < hi; i++) s += block_hist[i];
-    int64_t run = block_exclusive_scan_i64(s, nullptr, scratch);
-    for (int64_t i = lo; i < hi; i++) { base[i] = run; run += block_hist[i]; }
+    unsigned long long *h = hist + (size_t)blockIdx.x * RS_RADIX;
+    const int64_t v = (int64_t)h[threadIdx.x];
+    const int64_t ex = block_exclusive_scan_i64(v, nullptr, scratch);
+    h[threadIdx.x] = (unsigned long long)ex;
 }
 
+__device__ __forceinline__ uint64_t ld_volatile_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u64(uint64_t *p, uint64_t v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// control: [0] = tile counter, followed (at +8 words) by status[n_tiles][256]; zeroed before every pass
 template <bool LAST>
-__global__ void __launch_bounds__(RS_THREADS) k_radix_scatter(const uint64_t *__restrict__ in, int64_t n, int shift,
-                                                               int64_t chunk, const int64_t *__restrict__ base,
-                                                               uint64_t *__restrict__ out, uint32_t *__restrict__ out_vals) {
-    __shared__ int64_t cursor[RS_RADIX];
-    __shared__ uint32_t wcount[RS_WARPS][RS_RADIX];
-    __shared__ uint32_t tot[RS_RADIX];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__global__ void __launch_bounds__(OS_THREADS, 2) k_onesweep(const uint64_t *__restrict__ in, int64_t n, int shift,
+                                                             const unsigned long long *__restrict__ digit_base /*[256]*/,
+                                                             uint64_t *__restrict__ control, uint64_t *__restrict__ out,
+                                                             uint32_t *__restrict__ out_vals) {
+    extern __shared__ __align__(16) unsigned char os_smem[];
+    uint64_t *sm_items = reinterpret_cast<uint64_t *>(os_smem);                                   // [OS_TILE]
+    uint32_t *wcount = reinterpret_cast<uint32_t *>(os_smem + OS_TILE * 8);                       // [OS_WARPS][256]
+    int64_t *gbase = reinterpret_cast<int64_t *>(os_smem + OS_TILE * 8 + OS_WARPS * RS_RADIX * 4);   // [256]
+    uint32_t *dstart = reinterpret_cast<uint32_t *>(gbase + RS_RADIX);                            // [256]
+    uint32_t *misc = dstart + RS_RADIX;                                                           // [0] tile id; [1..] scan scratch
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    for (int d = threadIdx.x; d < RS_RADIX; d += RS_THREADS) cursor[d] = base[(int64_t)d * gridDim.x + blockIdx.x];
-    const int64_t lo = (int64_t)blockIdx.x * chunk, hi = min(lo + chunk, n);
-    for (int64_t tile0 = lo; tile0 < hi; tile0 += RS_TILE) {
-        for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&wcount[0][0])[i] = 0;
-        __syncthreads();  // also orders the cursor update of the previous tile
-        uint64_t it[RS_ITEMS];
-        uint32_t loc[RS_ITEMS];
+    uint64_t *status = control + 8;
+
+    if (tid == 0) misc[0] = (uint32_t)atomicAdd(reinterpret_cast<unsigned long long *>(control), 1ull);
+    for (int i = tid; i < OS_WARPS * RS_RADIX; i += OS_THREADS) wcount[i] = 0u;
+    __syncthreads();
+    const int64_t tile = misc[0];
+    const int64_t tile0 = tile * OS_TILE;
+    const int n_tile = (int)min((int64_t)OS_TILE, n - tile0);
+
+    // ---- load + per-warp stable ranks ----
+    uint64_t it[OS_ITEMS];
+    uint16_t loc[OS_ITEMS];
+    uint32_t *wc = wcount + warp * RS_RADIX;
 #pragma unroll
-        for (int r = 0; r < RS_ITEMS; r++) {
-            const int64_t i = tile0 + (int64_t)warp * (32 * RS_ITEMS) + r * 32 + lane;
-            const bool valid = i < hi;
-            it[r] = valid ? in[i] : ~0ull;
-            const uint32_t d = valid ? ((uint32_t)(it[r] >> shift) & (RS_RADIX - 1)) : RS_RADIX;  // RS_RADIX = "none"
-            const uint32_t peers = __match_any_sync(0xffffffffu, d);
-            const uint32_t rank = __popc(peers & lt_mask);
-            uint32_t old = 0;
-            if (valid) old = wcount[warp][d];
-            __syncwarp();
-            if (valid && rank == 0) wcount[warp][d] = old + __popc(peers);
-            __syncwarp();
-            loc[r] = old + rank;
-        }
-        __syncthreads();
-        for (int d = threadIdx.x; d < RS_RADIX; d += RS_THREADS) {
-            uint32_t run = 0;
+    for (int r = 0; r < OS_ITEMS; r++) {
+        const int li = warp * (32 * OS_ITEMS) + r * 32 + lane;
+        const bool valid = li < n_tile;
+        it[r] = valid ? in[tile0 + li] : ~0ull;
+        const uint32_t d = valid ? ((uint32_t)(it[r] >> shift) & (RS_RADIX - 1)) : RS_RADIX;   // RS_RADIX = "none"
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t rank = __popc(peers & lt_mask);
+        uint32_t old = 0;
+        if (valid) old = wc[d];
+        __syncwarp();
+        if (valid && rank == 0) wc[d] = old + __popc(peers);
+        __syncwarp();
+        loc[r] = (uint16_t)(old + rank);
+    }
+    __syncthreads();
+
+    // ---- tile digit counts, look-back, bases (threads 0..255 = digits) ----
+    uint32_t cnt = 0;
+    if (tid < RS_RADIX) {
 #pragma unroll
-            for (int w = 0; w < RS_WARPS; w++) { uint32_t c = wcount[w][d]; wcount[w][d] = run; run += c; }
-            tot[d] = run;
-        }
-        __syncthreads();
+        for (int w = 0; w < OS_WARPS; w++) { const uint32_t c = wcount[w * RS_RADIX + tid]; wcount[w * RS_RADIX + tid] = cnt; cnt += c; }
+        st_volatile_u64(&status[tile * RS_RADIX + tid], (tile == 0 ? OS_FLAG_INCL : OS_FLAG_LOCAL) | cnt);
+    }
+    // exclusive scan of the 256 digit counts -> start of every digit inside the tile (warps 0..7 hold the digits)
+    {
+        uint32_t inc = cnt;
 #pragma unroll
-        for (int r = 0; r < RS_ITEMS; r++) {
-            const int64_t i = tile0 + (int64_t)warp * (32 * RS_ITEMS) + r * 32 + lane;
-            if (i < hi) {
-                const uint32_t d = (uint32_t)(it[r] >> shift) & (RS_RADIX - 1);
-                const int64_t pos = cursor[d] + wcount[warp][d] + loc[r];
-                if (LAST) out_vals[pos] = (uint32_t)it[r] & TET_MASK;
-                else out[pos] = it[r];
-            }
-        }
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += o; }
+        if (tid < RS_RADIX && lane == 31) misc[1 + warp] = inc;
         __syncthreads();
-        for (int d = threadIdx.x; d < RS_RADIX; d += RS_THREADS) cursor[d] += tot[d];
+        if (tid < RS_RADIX) {
+            uint32_t woff = 0;
+            for (int w = 0; w < warp; w++) woff += misc[1 + w];
+            dstart[tid] = woff + inc - cnt;
+        }
+    }
+    if (tid < RS_RADIX) {
+        uint64_t excl = 0;
+        for (int64_t t = tile - 1; t >= 0;) {
+            const uint64_t v = ld_volatile_u64(&status[t * RS_RADIX + tid]);
+            if ((v >> 62) == 0) continue;                 // not published yet (tile t is resident: it took its id earlier)
+            excl += v & OS_COUNT_MASK;
+            if (v & OS_FLAG_INCL) break;
+            t--;
+        }
+        if (tile > 0) st_volatile_u64(&status[tile * RS_RADIX + tid], OS_FLAG_INCL | (excl + cnt));
+        gbase[tid] = (int64_t)digit_base[tid] + (int64_t)excl - (int64_t)dstart[tid];
+    }
+    __syncthreads();
+
+    // ---- reorder by digit in shared memory, then coalesced write-out ----
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; r++) {
+        const int li = warp * (32 * OS_ITEMS) + r * 32 + lane;
+        if (li < n_tile) {
+            const uint32_t d = (uint32_t)(it[r] >> shift) & (RS_RADIX - 1);
+            sm_items[dstart[d] + wc[d] + loc[r]] = it[r];
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < n_tile; i += OS_THREADS) {
+        const uint64_t v = sm_items[i];
+        const uint32_t d = (uint32_t)(v >> shift) & (RS_RADIX - 1);
+        const int64_t pos = gbase[d] + i;
+        if (LAST) out_vals[pos] = (uint32_t)v & TET_MASK;
+        else out[pos] = v;
     }
 }
 

@@ -214,8 +214,7 @@ int pfaai_gpu_build(pfaai_gpu_ctx *h) {
     PF_TRY(launch_scan(c, ptr<int32_t>(c->Lc), NTETRA, ptr<int64_t>(c->Lp64), ptr<int32_t>(c->Lp32)));
     // K2a + K3: sort items and the (genome, SCP) histogram
     if (nF > 0) {
-        const int64_t nthreads = ceil_div64(nF, MI_ITEMS);
-        k_make_items<<<(unsigned)ceil_div64(nthreads, MI_THREADS), MI_THREADS, 0, c->stream>>>(
+        k_make_items<<<(unsigned)ceil_div64(nF, (int64_t)MI_THREADS * MI_ITEMS), MI_THREADS, 0, c->stream>>>(
             ptr<pfaai_pg_t>(c->F), ptr<int64_t>(c->Lp64), nF, P, G, ptr<uint64_t>(c->itemsA), ptr<uint32_t>(c->seg_len),
             ptr<int>(c->flags));
         PF_LAUNCH_CHECK(c);
@@ -225,30 +224,36 @@ int pfaai_gpu_build(pfaai_gpu_ctx *h) {
                                                                           c->host_T ? nullptr : ptr<int32_t>(c->T),
                                                                           ptr<int>(c->flags) + 1);
     PF_LAUNCH_CHECK(c);
-    // K2b: stable LSD radix sort on (genome*P + protein); the last pass emits the tetramers only
+    // K2b: stable LSD radix sort on (genome*P + protein), one onesweep kernel per 8-bit digit; the digit histograms
+    // of all passes come from the segment histogram; the last pass emits the tetramers only
     PF_CUDA(c, cudaEventRecord(c->ev[EV_S0], c->stream));
     if (nF > 0) {
         int keybits = 1;
         while (keybits < 31 && ((int64_t)1 << keybits) < nseg) keybits++;
         const int passes = (keybits + 7) / 8;
-        int64_t nb = std::min<int64_t>((int64_t)c->sm_count * 4, ceil_div64(nF, RS_TILE));
-        int64_t chunk = ceil_div64(ceil_div64(nF, nb), RS_TILE) * RS_TILE;
-        nb = ceil_div64(nF, chunk);
-        PF_TRY(ensure(c, c->block_hist, sizeof(uint32_t) * (size_t)(RS_RADIX * nb)));
-        PF_TRY(ensure(c, c->block_base, sizeof(int64_t) * (size_t)(RS_RADIX * nb)));
+        const int64_t n_tiles = ceil_div64(nF, OS_TILE);
+        const size_t control_bytes = sizeof(uint64_t) * (size_t)(8 + n_tiles * RS_RADIX);
+        PF_TRY(ensure(c, c->block_hist, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX));
+        PF_TRY(ensure(c, c->block_base, control_bytes));
+        PF_CUDA(c, cudaMemsetAsync(c->block_hist.p, 0, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX, c->stream));
+        k_digit_hist<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 256), (int64_t)c->sm_count * 2), 256, 0, c->stream>>>(
+            ptr<uint32_t>(c->seg_len), nseg, passes, ptr<unsigned long long>(c->block_hist));
+        PF_LAUNCH_CHECK(c);
+        k_digit_scan<<<passes, RS_RADIX, 0, c->stream>>>(ptr<unsigned long long>(c->block_hist));
+        PF_LAUNCH_CHECK(c);
+        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
+        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
         uint64_t *src = ptr<uint64_t>(c->itemsA), *dst = ptr<uint64_t>(c->itemsB);
         for (int pass = 0; pass < passes; pass++) {
             const int shift = TET_BITS + 8 * pass;
-            k_radix_hist<<<(unsigned)nb, RS_THREADS, 0, c->stream>>>(src, nF, shift, chunk, ptr<uint32_t>(c->block_hist));
-            PF_LAUNCH_CHECK(c);
-            k_radix_scan<<<1, 1024, 0, c->stream>>>(ptr<uint32_t>(c->block_hist), RS_RADIX * nb, ptr<int64_t>(c->block_base));
-            PF_LAUNCH_CHECK(c);
+            const unsigned long long *base = ptr<unsigned long long>(c->block_hist) + (size_t)pass * RS_RADIX;
+            PF_CUDA(c, cudaMemsetAsync(c->block_base.p, 0, control_bytes, c->stream));
             if (pass == passes - 1)
-                k_radix_scatter<true><<<(unsigned)nb, RS_THREADS, 0, c->stream>>>(src, nF, shift, chunk, ptr<int64_t>(c->block_base),
-                                                                                  nullptr, ptr<uint32_t>(c->vals));
+                k_onesweep<true><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, nF, shift, base, ptr<uint64_t>(c->block_base),
+                                                                                        nullptr, ptr<uint32_t>(c->vals));
             else
-                k_radix_scatter<false><<<(unsigned)nb, RS_THREADS, 0, c->stream>>>(src, nF, shift, chunk, ptr<int64_t>(c->block_base),
-                                                                                   dst, nullptr);
+                k_onesweep<false><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, nF, shift, base, ptr<uint64_t>(c->block_base),
+                                                                                         dst, nullptr);
             PF_LAUNCH_CHECK(c);
             std::swap(src, dst);
         }
