@@ -375,3 +375,23 @@ int pfo_genome_major(int P, int G, const int32_t *Lc, const pfo_pg_t *F, int64_t
     free(cur);
     return (pos == nF) ? PFO_OK : PFO_ERR_ARG;
 }
+
+/* Checker for the tile kernel's reciprocal-table division (parfastaai_b200/csrc/aji_tile.cuh, jaccard_exact):
+ * counts the (c, den), 0 <= c <= den <= den_max, for which  q' = fma(fma(-q, den, c), r, q)  with r = RN(1/den),
+ * q = RN(c*r)  differs from the IEEE quotient the reference computes (algorithm_impl.hpp:250-254).  Must be 0. */
+#include <math.h>
+int64_t pfo_check_table_division(int den_max) {
+    int64_t bad = 0;
+#pragma omp parallel for schedule(dynamic, 64) reduction(+ : bad)
+    for (int den = 1; den <= den_max; den++) {
+        const double dd = (double)den, r = 1.0 / dd;
+        for (int c = 0; c <= den; c++) {
+            const double cd = (double)c;
+            volatile double q = cd * r;            /* volatile: no contraction of the product into the fma below */
+            const double rem = fma(-q, dd, cd);
+            const double q2 = fma(rem, r, q);
+            if (q2 != cd / dd) bad++;
+        }
+    }
+    return bad;
+}

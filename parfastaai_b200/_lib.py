@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpfaai_gpu.so")
+LIB_PATH = os.environ.get("PFAAI_GPU_LIB") or os.path.join(HERE, "libpfaai_gpu.so")   # override: kernel A/B experiments
 
 PG_DTYPE = np.dtype([("protein", "<i4"), ("genome", "<i4")])
 JAC_DTYPE = np.dtype([("gA", "<i4"), ("gB", "<i4"), ("S", "<f8"), ("N", "<i4"), ("pad_", "<i4")])

@@ -9,7 +9,7 @@
 //   computeAJI                include/pfaai/algorithm_impl.hpp:309-322  (AJI = S/N)
 //   printOutput matrix fill   src/main.cpp:143-154                   (mirror across the diagonal, zero diagonal)
 //
-// Formulation.  A persistent CTA (one per SM, 16 walker warps) owns tiles of 256 rows x 64 columns of genome
+// Formulation.  A persistent CTA (one per SM, 24 walker warps) owns tiles of 384 rows x 64 columns of genome
 // pairs and, per tile, walks the column block's STAGE LIST: for every SCP in ascending index (the reference's
 // summation order) and every tetramer range, one dictionary blob
 //        [presence/rank bitmap over the range | one 64-bit column mask per distinct tetramer]
@@ -24,7 +24,11 @@
 //              64-bit mask into BIT-SLICED counters (carry-save adders, LOP3 only): one mask add advances
 //              64 pair counters at once.  No atomics, no E array, no per-pair memory traffic.
 //   epilogue : after the last stage of an SCP the two half-lanes exchange halves (SHFL), each lane expands 32
-//              counters, forms J = c / (T(p,a) + T(p,b) - c) in fp64, S += J, N += (c > 0) -- registers only.
+//              counters, forms J = c / (T(p,a) + T(p,b) - c) in fp64, S += J, N += (c > 0).  The 32 fp64 sums of a
+//              lane live in TENSOR MEMORY (tcgen05.ld / tcgen05.st, SASS LDTM / STTM): 64 registers per thread are
+//              freed, which is what lets 24 warps (instead of 16) hide the shared-memory latency of the walk.
+//              The division is done with a shared-memory reciprocal table + two FMAs (correctly rounded, see
+//              jaccard_exact) instead of the ~25-instruction fp64 division sequence.
 // After the last SCP: AJI = S/N written to the dense output (both triangles in symmetric mode).
 #pragma once
 #include "common.cuh"
@@ -88,6 +92,49 @@ __device__ __forceinline__ uint32_t atom_add_acq_rel_smem(uint32_t *p, uint32_t 
     return old;
 }
 
+// ---- PTX wrappers: tensor memory (tcgen05) used as per-thread accumulator storage ----
+__device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst, uint32_t ncols) {   // one full warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {      // the warp that allocated
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// 16 consecutive 32-bit columns of this thread's lane <-> 16 registers (= 8 doubles)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr));
+}
+// the registers of a preceding tmem_ld16 may be read only after this wait; passing them through makes the
+// dependency visible to the compiler as well
+__device__ __forceinline__ void tmem_wait_ld(uint32_t (&v)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                   "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])::"memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+                 "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+                 "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// J = c / den, correctly rounded (== IEEE fp64 division, algorithm_impl.hpp:250-254).  Fast path: r = RN(1/den) from the
+// shared-memory table, q = RN(c*r), q' = RN(q + (c - q*den)*r) with the residual exact in one FMA (Markstein); q' equals
+// RN(c/den) for every 0 <= c <= den < 20000 (checked exhaustively in tests/test_division.py with the same operations).
+__device__ __noinline__ double jaccard_div(int c, int den) { return (double)c / (double)den; }
+__device__ __forceinline__ double jaccard_exact(const double *__restrict__ rcp, int c, int den) {
+    if (den < RCP_N && c <= den) {
+        const double r = rcp[den], cd = (double)c, dd = (double)den;
+        const double q = __dmul_rn(cd, r);
+        return __fma_rn(__fma_rn(-q, dd, cd), r, q);
+    }
+    return jaccard_div(c, den);
+}
+
 // carry-save adder on one 32-bit slice: (h, l) = a + b + c
 #define PF_CSA(h, l, a, b, c)                       \
     do {                                            \
@@ -118,17 +165,19 @@ __device__ __forceinline__ int st_q(uint32_t w) { return (int)((w >> 16) & 0xffu
 __device__ __forceinline__ bool st_first(uint32_t w) { return (w >> 24) & 1u; }
 __device__ __forceinline__ bool st_last(uint32_t w) { return (w >> 25) & 1u; }
 
-constexpr int N_PLANES_N = 10;   // bit-sliced N counter: up to 1023 SCPs
-
-template <int NPL>
+// NPL = bit planes of a half-list counter, NPN = bit planes of the N counter (7: up to 127 SCPs, 10: up to 1023)
+template <int NPL, int NPN>
 __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TileParams prm) {
+    constexpr int N_PLANES_N = NPN;
     extern __shared__ __align__(128) unsigned char smem[];
     // ---- shared memory carve-up: [misc SMEM_MISC][stage 0][stage 1] ----
     uint64_t *full = reinterpret_cast<uint64_t *>(smem);               // [2] mbarriers: blob landed
     uint32_t *done = reinterpret_cast<uint32_t *>(smem + 16);          // [2] warps that finished walking the slot
     int32_t *col_g = reinterpret_cast<int32_t *>(smem + 64);           // [64] genome id of the tile's columns (-1 = none)
     int32_t *colT = reinterpret_cast<int32_t *>(smem + 64 + 256);      // [4][64] ring of T(p, column), slot p & 3
-    unsigned char *stage_mem = smem + SMEM_MISC;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + 32);     // tensor-memory base address (tcgen05.alloc)
+    double *rcp = reinterpret_cast<double *>(smem + SMEM_MISC);        // [RCP_N] RN(1/den)
+    unsigned char *stage_mem = smem + SMEM_MISC + SMEM_RCP;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int P = prm.P;
@@ -141,8 +190,14 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         done[0] = 0u; done[1] = 0u;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (warp == 0) tmem_alloc(tmem_slot, TMEM_COLS);
+    for (int i = tid; i < RCP_N; i += TILE_THREADS) rcp[i] = (i > 0) ? 1.0 / (double)i : 0.0;
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    uint32_t use[2] = {0u, 0u};     // completed fills of each slot (wait parity), identical in every thread
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    // this thread's 64 tensor-memory columns (32 doubles): lane quadrant warp%4, column block warp/4
+    const uint32_t taddr = *tmem_slot + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * TMEM_COLS_PER_WARP);
+    uint32_t use_par = 0u;          // bit s = wait parity of slot s (flips per completed fill), identical in every thread
 
     auto issue = [&](const uint4 st, int slot, int cb) {
         // runs in ONE thread: refill `slot` with the blob of stage `st` (+ the column T values on an SCP's first stage)
@@ -187,12 +242,18 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
             }
         }
 
-        double S[32];
         uint32_t Np[N_PLANES_N];
 #pragma unroll
-        for (int j = 0; j < 32; j++) S[j] = 0.0;
-#pragma unroll
         for (int k = 0; k < N_PLANES_N; k++) Np[k] = 0u;
+        {   // S = 0 for the 32 columns of this lane
+            uint32_t z[16];
+#pragma unroll
+            for (int k = 0; k < 16; k++) z[k] = 0u;
+            __syncwarp();
+#pragma unroll
+            for (int g8 = 0; g8 < 4; g8++) tmem_st16(taddr + 16 * g8, z);
+            tmem_wait_st();
+        }
 
         uint32_t plo[NPL], phi[NPL];     // bit-sliced counters of this lane's half list: columns 0..31 / 32..63
         uint32_t pe_lo = 0u, pe_hi = 0u; // pending carry of weight 8 (one per two 8-lookup steps)
@@ -231,8 +292,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
             int ta_nxt = 0;
             if (st_last(st_cur) && row_ok && k + 1 < nst) ta_nxt = prm.T[(int64_t)st_p(st_nxt) * prm.t_ld + ti];
 
-            mbar_wait(&full[slot], use[slot] & 1u);
-            use[slot]++;
+            mbar_wait(&full[slot], (use_par >> slot) & 1u);
+            use_par ^= 1u << slot;
 
             // ================= walk: bit-sliced accumulation of the row half-lists =================
             {
@@ -324,28 +385,45 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                     for (int kk = 0; kk < N_PLANES_N; kk++) { const uint32_t tt = Np[kk] & nz; Np[kk] ^= nz; nz = tt; }
                 }
                 const int32_t *ct = colT + (p & 3) * COLS_PER_TILE + cbase;
-                // counts of 4 columns at a time: nibble -> one bit per byte ((n * 0x00204081) & 0x01010101)
+                __syncwarp();
+                // 8 columns at a time: fetch their sums from tensor memory, expand the bit-sliced counts
+                // (nibble -> one bit per byte: (n * 0x00204081) & 0x01010101) while the load is in flight, add J, store back
 #pragma unroll
-                for (int g4 = 0; g4 < 8; g4++) {
-                    uint32_t lo = 0u, hi = 0u;
+                for (int g8 = 0; g8 < 4; g8++) {
+                    uint32_t sv[16];
+                    tmem_ld16(taddr + 16 * g8, sv);
+                    int cnt[8];
 #pragma unroll
-                    for (int kk = 0; kk <= NPL; kk++) {
-                        const uint32_t sp = (((R[kk] >> (4 * g4)) & 15u) * 0x00204081u) & 0x01010101u;
-                        if (kk < 8) lo += sp << kk; else hi += sp << (kk - 8);
+                    for (int hf = 0; hf < 2; hf++) {
+                        const int g4 = 2 * g8 + hf;
+                        uint32_t lo = 0u, hi = 0u;
+#pragma unroll
+                        for (int kk = 0; kk <= NPL; kk++) {
+                            const uint32_t sp = (((R[kk] >> (4 * g4)) & 15u) * 0x00204081u) & 0x01010101u;
+                            if (kk < 8) lo += sp << kk; else hi += sp << (kk - 8);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; u++)
+                            cnt[4 * hf + u] = (int)(((lo >> (8 * u)) & 0xffu) | (((hi >> (8 * u)) & 0xffu) << 8));
                     }
+                    tmem_wait_ld(sv);
 #pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const int jj = 4 * g4 + u;
-                        const int cnt = (int)(((lo >> (8 * u)) & 0xffu) | (((hi >> (8 * u)) & 0xffu) << 8));
+                    for (int u = 0; u < 8; u++) {
+                        const int jj = 8 * g8 + u;
                         if (prm.counts_out) {
                             const int col = cbase + jj;
                             if (row_ok && col < ncol)
-                                prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = cnt;
+                                prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = cnt[u];
                         }
-                        const int den = max(ta + ct[jj] - cnt, 1);
-                        S[jj] += (double)cnt / (double)den;       // algorithm_impl.hpp:250-254; cnt == 0 adds +0.0
+                        const int den = max(ta + ct[jj] - cnt[u], 1);
+                        // algorithm_impl.hpp:250-254; cnt == 0 adds +0.0
+                        const double sum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]) + jaccard_exact(rcp, cnt[u], den);
+                        sv[2 * u] = (uint32_t)__double2loint(sum);
+                        sv[2 * u + 1] = (uint32_t)__double2hiint(sum);
                     }
+                    tmem_st16(taddr + 16 * g8, sv);
                 }
+                tmem_wait_st();
                 ta = ta_nxt;
             }
             st_cur = st_nxt; st_nxt = st_n2.w;
@@ -353,32 +431,44 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         }
 
         // ================= output: AJI = S / N (computeAJI) into the dense matrix =================
+        __syncwarp();
 #pragma unroll
-        for (int jj = 0; jj < 32; jj++) {
-            const int col = cbase + jj;
-            if (row_ok && col < ncol) {
-                const int gj = col_g[col];
-                int n = 0;
+        for (int g8 = 0; g8 < 4; g8++) {
+            uint32_t sv[16];
+            tmem_ld16(taddr + 16 * g8, sv);
+            tmem_wait_ld(sv);
 #pragma unroll
-                for (int kk = 0; kk < N_PLANES_N; kk++) n |= (int)((Np[kk] >> jj) & 1u) << kk;
-                const double aji = (n > 0) ? S[jj] / (double)n : 0.0;
-                const int64_t j = j0 + col;
-                if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + j] = S[jj];
-                if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + j] = n;
-                if (prm.symmetric) {
-                    if (gi < gj) {
-                        prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = aji;
-                        prm.out[(int64_t)gj * prm.out_rs + (int64_t)gi * prm.out_cs] = aji;
-                    } else if (gi == gj) {
-                        prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = 0.0;
+            for (int u = 0; u < 8; u++) {
+                const int jj = 8 * g8 + u;
+                const int col = cbase + jj;
+                if (row_ok && col < ncol) {
+                    const double Ssum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]);
+                    const int gj = col_g[col];
+                    int n = 0;
+#pragma unroll
+                    for (int kk = 0; kk < N_PLANES_N; kk++) n |= (int)((Np[kk] >> jj) & 1u) << kk;
+                    const double aji = (n > 0) ? Ssum / (double)n : 0.0;
+                    const int64_t j = j0 + col;
+                    if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + j] = Ssum;
+                    if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + j] = n;
+                    if (prm.symmetric) {
+                        if (gi < gj) {
+                            prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = aji;
+                            prm.out[(int64_t)gj * prm.out_rs + (int64_t)gi * prm.out_cs] = aji;
+                        } else if (gi == gj) {
+                            prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = 0.0;
+                        }
+                    } else {
+                        prm.out[(int64_t)row * prm.out_rs + j * prm.out_cs] = (gi == gj) ? 0.0 : aji;
                     }
-                } else {
-                    prm.out[(int64_t)row * prm.out_rs + j * prm.out_cs] = (gi == gj) ? 0.0 : aji;
                 }
             }
         }
         __syncthreads();   // every warp is done with col_g / colT / both slots before the next tile refills them
     }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(*tmem_slot, TMEM_COLS);
 }
 
 }  // namespace pfaai

@@ -17,9 +17,21 @@ constexpr uint32_t TET_MASK = (1u << TET_BITS) - 1;
 // ---- tile geometry of the core kernel ----
 constexpr int ROWS_PER_WARP = 16;            // one warp = 16 rows x 2 half-lists
 constexpr int COLS_PER_TILE = 64;            // one 64-bit column mask per distinct tetramer
-constexpr int TILE_WARPS = 16;               // 512 threads, <= 128 registers each
+#ifndef PF_TILE_WARPS
+#define PF_TILE_WARPS 24
+#endif
+constexpr int TILE_WARPS = PF_TILE_WARPS;   // 24 warps = 768 threads, <= 80 registers each (the fp64 sums S live in TMEM)
 constexpr int TILE_THREADS = TILE_WARPS * 32;
-constexpr int TILE_ROWS = TILE_WARPS * ROWS_PER_WARP;   // 256 rows x 64 columns per tile
+constexpr int TILE_ROWS = TILE_WARPS * ROWS_PER_WARP;   // 384 rows x 64 columns per tile
+// Tensor memory (256 KB per SM, 128 lanes x 512 32-bit columns) holds the per-pair fp64 sums S: a warp may only touch
+// lanes 32*(warp%4)..+31, so warp w owns columns [64*(w/4), 64*(w/4)+64) of its lane quadrant = 32 doubles per thread.
+constexpr int TMEM_COLS_PER_WARP = 64;
+constexpr int TMEM_COLS = 512;               // allocation must be a power of two >= (TILE_WARPS/4) * 64 = 384
+static_assert(TILE_WARPS % 4 == 0 && (TILE_WARPS / 4) * TMEM_COLS_PER_WARP <= TMEM_COLS, "S does not fit tensor memory");
+// reciprocal table for the Jaccard division: J = c/den via r = RN(1/den), q = c*r, q' = fma(fma(-q,den,c), r, q), which is
+// the correctly rounded quotient for every 0 <= c <= den < 20000 (exhaustively checked, tests/test_division.py)
+constexpr int RCP_N = 2048;
+constexpr int SMEM_RCP = RCP_N * 8;
 
 // The tetramer universe is cut into NRANGE ranges; one pipeline stage holds the dictionary of one
 // (column block, SCP, range): a presence/rank bitmap over the range plus one 64-bit column mask per
@@ -35,10 +47,10 @@ constexpr uint32_t PAD_ID = RANGE_T;         // padding value of packed row slic
 __host__ __device__ __forceinline__ uint32_t slab_encode(uint32_t v) { return ((v >> 4) << 7) | (31u - (v & 15u)); }
 constexpr int MAX_SUB = 64;                   // a (block, SCP, range) dictionary is split into <= 8 column sub-ranges
 
-// shared memory of the tile kernel: [misc 2 KB][stage 0][stage 1]
+// shared memory of the tile kernel: [misc 2 KB][reciprocal table 16 KB][stage 0][stage 1]
 constexpr int SMEM_TOTAL = 227 * 1024;                       // 232448
 constexpr int SMEM_MISC = 2048;
-constexpr int STAGE_BYTES = ((SMEM_TOTAL - SMEM_MISC) / 2) & ~127;   // 115200
+constexpr int STAGE_BYTES = ((SMEM_TOTAL - SMEM_MISC - SMEM_RCP) / 2) & ~127;   // 107008
 constexpr int MASK_CAP = ((STAGE_BYTES - BM_BYTES) / 8) & ~1;        // entries incl. the all-zero miss slot 0
 
 struct __align__(16) StageDesc {             // one pipeline stage = one bulk copy

@@ -350,9 +350,9 @@ static int upload_i32(Ctx *c, DevBuf &b, const std::vector<int32_t> &v) {
     return PFAAI_OK;
 }
 
-template <int NPL>
+template <int NPL, int NPN>
 static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles) {
-    auto kern = aji_tile_kernel<NPL>;
+    auto kern = aji_tile_kernel<NPL, NPN>;
     PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
     // persistent CTAs, one per SM; CTA b walks tiles b, b + grid, ... (row-block-major order keeps the
     // concurrently processed tiles on the same row slabs, which stay L2-resident)
@@ -487,8 +487,13 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.tiles = ptr<int2>(c->tiles); prm.n_tiles = (int)tiles.size();
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
     if (!tiles.empty() && c->nF > 0) {
-        if (lane_lookups <= 511) PF_TRY(launch_tiles<9>(c, prm, (int)tiles.size()));
-        else PF_TRY(launch_tiles<12>(c, prm, (int)tiles.size()));
+        if (lane_lookups <= 511) {
+            if (P <= 127) PF_TRY((launch_tiles<9, 7>(c, prm, (int)tiles.size())));
+            else PF_TRY((launch_tiles<9, 10>(c, prm, (int)tiles.size())));
+        } else {
+            if (P <= 127) PF_TRY((launch_tiles<12, 7>(c, prm, (int)tiles.size())));
+            else PF_TRY((launch_tiles<12, 10>(c, prm, (int)tiles.size())));
+        }
     }
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
