@@ -254,6 +254,7 @@ def main():
     ap.add_argument("--ref-genomes", type=int, default=64, help="size of the reference arm's bounded sample")
     ap.add_argument("--cpu-baseline-genomes", type=int, default=96)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--verify", action="store_true", help="N>1: gather the shards on rank 0 and compare with an unsharded compute")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         log("[bench] note: fewer than 3 warm-up steps requested; the timing rules ask for W >= 3")
@@ -279,30 +280,50 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
         dist.barrier()
     import parfastaai_b200 as pf
-    from parfastaai_b200 import synth
+    from parfastaai_b200 import sharding, synth
 
     P = args.scps
     G = args.genomes or (10000 if world == 1 else 50000)
     pairs_total = G * (G - 1) // 2
 
-    # ---- synthetic workload in pinned host memory (reference-format arrays: Lc, F) ----
+    class _DevMem:   # raw device pointer of the C-ABI context -> torch tensor (for copies / NCCL on the index buffers)
+        def __init__(self, ptr, nbytes):
+            self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+    # ---- synthetic workload (reference-format arrays Lc, F) in pinned host memory; only rank 0 holds it ----
     t0 = time.perf_counter()
-    off, vals = synth.generate(G, P, seed=SEED)
-    nF = int(off[-1])
-    F_pin = torch.empty(nF * 2, dtype=torch.int32).pin_memory()
-    Lc_pin = torch.empty(pf.NTETRA, dtype=torch.int32).pin_memory()
-    F = F_pin.numpy().view(pf.PG_DTYPE)
-    Lc = Lc_pin.numpy()
-    synth.to_reference(G, P, off, vals, out_F=F, out_Lc=Lc)
-    log(f"[rank {rank}] synthetic {G} x {P}: |F| = {nF}, generated in {time.perf_counter()-t0:.1f} s")
+    off = vals = None
+    nF_t = torch.zeros(1, dtype=torch.int64, device=dev)
+    if rank == 0:
+        off, vals = synth.generate(G, P, seed=SEED)
+        nF = int(off[-1])
+        F_pin = torch.empty(nF * 2, dtype=torch.int32).pin_memory()
+        Lc_pin = torch.empty(pf.NTETRA, dtype=torch.int32).pin_memory()
+        F = F_pin.numpy().view(pf.PG_DTYPE)
+        Lc = Lc_pin.numpy()
+        synth.to_reference(G, P, off, vals, out_F=F, out_Lc=Lc)
+        nF_t[0] = nF
+        log(f"[rank 0] synthetic {G} x {P}: |F| = {nF}, generated in {time.perf_counter()-t0:.1f} s")
+        if world > 1:
+            vals = None   # 7 GB at config 5; not needed any more
+    if world > 1:
+        dist.broadcast(nF_t, src=0)
+    nF = int(nF_t.item())
 
     stream = torch.cuda.Stream(device=dev)
     ctx = pf.PfaaiGpu(local_rank)
     ctx.set_stream(stream.cuda_stream)
     ctx.set_shard(rank, world)
-    rows_out, cols_out = G, G
-    M_pin = torch.empty(rows_out * cols_out, dtype=torch.float64).pin_memory()
-    M = M_pin.numpy().reshape(rows_out, cols_out)
+    my_rows, my_cols = sharding.shard_shape(pf.ALL_VS_ALL, G, 0, rank, world)
+    my_pairs = sharding.pair_count(pf.ALL_VS_ALL, G, 0, rank, world)
+    M_pin = torch.empty(my_rows * my_cols, dtype=torch.float64).pin_memory()
+    M = M_pin.numpy().reshape(my_rows, my_cols)
+    if world > 1:
+        # N > 1: the index is replicated by a broadcast over NVLink from the rank that holds the database
+        # (BASELINE north_star); the contexts expose their device index buffers for it
+        f_ptr, lc_ptr, _ = ctx.index_device_buffers(P, G, nF)
+        F_dev = torch.as_tensor(_DevMem(f_ptr, max(8 * nF, 8)), device=dev)
+        Lc_dev = torch.as_tensor(_DevMem(lc_ptr, 4 * pf.NTETRA), device=dev)
 
     def barrier():
         if world > 1:
@@ -316,12 +337,23 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def replicate_index():
+        """host (rank 0) -> every GPU: one H2D on rank 0, then NCCL broadcast over NVLink / NVSwitch"""
+        if world == 1:
+            ctx.upload_index(P, G, F, Lc)
+            return
+        if rank == 0:
+            F_dev.copy_(F_pin.view(torch.uint8), non_blocking=True)
+            Lc_dev.copy_(Lc_pin.view(torch.uint8), non_blocking=True)
+        dist.broadcast(F_dev, src=0)
+        dist.broadcast(Lc_dev, src=0)
+
     def step_device():
         ctx.build()
         ctx.compute_device(pf.ALL_VS_ALL)
 
     def step_e2e():
-        ctx.upload_index(P, G, F, Lc)
+        replicate_index()
         ctx.build()
         ctx.compute_device(pf.ALL_VS_ALL)
         ctx.download_matrix(M)
@@ -347,18 +379,47 @@ def main():
         return ms, tile_ms, launches, (clk.summary() if clk else None), tm
 
     # ---- device-resident metric ----
-    ctx.upload_index(P, G, F, Lc)
+    with torch.cuda.stream(stream):
+        replicate_index()
     for _ in range(args.warmup):
         step_device()
     ms_dev, tile_ms, launches, clocks, tm = timed(step_device, args.steps, sampler_index=local_rank)
     value = pairs_total * args.steps / (ms_dev / 1e3)
     # ---- end to end through the host-buffer C-ABI ----
     for _ in range(min(args.warmup, 2)):
-        step_e2e()
+        with torch.cuda.stream(stream):
+            step_e2e()
     ms_e2e, _, _, _, tm_e2e = timed(step_e2e, args.steps)
     e2e_value = pairs_total * args.steps / (ms_e2e / 1e3)
-    h2d = 8 * nF + 4 * pf.NTETRA
-    d2h = 8 * rows_out * cols_out
+    h2d = 8 * nF + 4 * pf.NTETRA                      # rank 0 only; the other ranks receive the index over NVLink
+    d2h = 8 * my_rows * my_cols                       # bytes all ranks copy back per step
+    if world > 1:
+        d2h_t = torch.tensor([8.0 * my_rows * my_cols], dtype=torch.float64, device=dev)
+        dist.all_reduce(d2h_t)
+        d2h = int(d2h_t.item())
+    launches = int(max_over_ranks(float(launches)))
+
+    verify = None
+    if args.verify:
+        # gather the shards' compact matrices on rank 0, assemble (mirror) and compare with an unsharded compute
+        lay = sharding.owned_indices(G, rank, world)
+        if world == 1:
+            full = M
+        elif rank == 0:
+            parts, lays = [M.copy()], [lay]
+            for r in range(1, world):
+                shp = sharding.shard_shape(pf.ALL_VS_ALL, G, 0, r, world)
+                buf = torch.empty(shp, dtype=torch.float64, device=dev)
+                dist.recv(buf, src=r)
+                parts.append(buf.cpu().numpy()); lays.append(sharding.owned_indices(G, r, world))
+            full = sharding.assemble(pf.ALL_VS_ALL, parts, lays, np.empty((G, G)))
+        else:
+            dist.send(torch.from_numpy(M).to(dev), dst=0)
+        if rank == 0:
+            ctx.set_shard(0, 1)
+            ref = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+            ctx.set_shard(rank, world)
+            verify = {"max_abs_diff_vs_unsharded": float(np.abs(full - ref).max()), "identical": bool(np.array_equal(full, ref))}
 
     peak, peak_src = measured_peaks()
     tile_avg_ms = float(np.mean(tile_ms))
@@ -382,7 +443,9 @@ def main():
         "config": {"workload": f"synthetic {G} genomes x {P} SCPs all-vs-all (BASELINE config {'4' if G == 10000 else '5' if G == 50000 else 'custom'}; "
                                f"SURVEY 8(d) recipe, seed {SEED})",
                    "genomes": G, "scps": P, "postings": nF, "pairs": pairs_total, "mode": "all-vs-all",
-                   "parallelism": f"row-block tiles sharded over {world} rank(s), index replicated, no collective",
+                   "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); index replicated "
+                                   f"on every GPU (N>1: one H2D on rank 0 + NCCL broadcast over NVLink inside the e2e region); "
+                                   f"no data-path collective; every rank copies only its own upper-triangle rows D2H"),
                    "l2_policy": "inputs larger than L2 (F = %.2f GB, matrix = %.2f GB vs 126 MB L2)" % (8 * nF / 1e9, d2h / 1e9),
                    "step": "index build (scan + histogram + radix sort) + row-slab packing + column dictionaries + tile kernel"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -398,6 +461,8 @@ def main():
                       "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"]},
     }
 
+    if verify is not None:
+        line["verify"] = verify
     # ---- CPU baseline (rank 0, N=1 only): the reference itself on a bounded sample, plus our OpenMP port ----
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T = synth.t_matrix(G, P, off)

@@ -73,9 +73,19 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *ctx);
 const char *pfaai_gpu_last_error(const pfaai_gpu_ctx *ctx); /* ctx may be NULL: error of the last create */
 /* run on this cudaStream_t (e.g. torch's current stream); default = a stream the context creates */
 int  pfaai_gpu_set_stream(pfaai_gpu_ctx *ctx, void *cuda_stream);
-/* multi-GPU row-block sharding: this context computes tiles t with t % n_shards == shard (no collective:
- * row blocks are independent); cells owned by other shards are left untouched (zero). */
+/* Multi-GPU row-block sharding (one context per GPU, every context holds the whole index; no data-path collective,
+ * row blocks are independent: SURVEY 8(e)).  The target axis of the output (rows of the all-vs-all matrix, columns =
+ * target genomes of the other two modes) is cut into blocks of 384 genomes; block b belongs to shard f(b mod 2n),
+ * f(x) = x < n ? x : 2n-1-x (folded, balances the triangular all-vs-all work).  A sharded context computes and stores
+ * ONLY its own blocks, compactly and in ascending order:
+ *   ALL_VS_ALL    [owned rows x G]; only cells with row < column are computed (the rest stays 0): the gathering host
+ *                 mirrors, M[j][i] = M[i][j], so every pair is computed, copied D2H and stored exactly once;
+ *   QUERY_SUBSET / QUERY_DB   [n_qry x owned targets].
+ * The JAC / counts hooks of pfaai_gpu_compute need an unsharded context. */
 int  pfaai_gpu_set_shard(pfaai_gpu_ctx *ctx, int shard, int n_shards);
+/* layout of the last compute: axis (0 = rows, 1 = columns) that is sharded, the number of owned indices along it and
+ * (ids != NULL) their global indices in storage order.  Unsharded: n = the full extent, ids = 0..n-1. */
+int  pfaai_gpu_shard_layout(const pfaai_gpu_ctx *ctx, int *axis, int64_t *n, int32_t *ids);
 
 /* ---- phase 1/2: index --------------------------------------------------------------------------
  * Upload the reference's arrays exactly as DataBaseInterface delivers them (interface.hpp:153-196):
@@ -86,6 +96,12 @@ int  pfaai_gpu_set_shard(pfaai_gpu_ctx *ctx, int shard, int n_shards);
  * n_genomes is the TOTAL number of genome ids (query-DB mode: nT + nQ, targets first). */
 int  pfaai_gpu_upload_index(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes,
                             const pfaai_pg_t *F, const int32_t *Lc, int64_t nF, const int32_t *T);
+/* The same for a caller that fills the index itself on the device (e.g. a broadcast / all-gather over NVLink from
+ * the rank that read the database): sizes the context's F [nF], Lc [160000] and T [P x G] buffers and returns their
+ * device pointers; the caller writes them on the context's stream (or synchronises) before pfaai_gpu_build().
+ * host_T != 0 declares that T will be provided (query-DB mode), otherwise it is derived on the device. */
+int  pfaai_gpu_index_device_buffers(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes, int64_t nF, int host_T,
+                                    void **F_dev, void **Lc_dev, void **T_dev);
 /* Device build: Lp (exclusive scan), per-(genome,SCP) segment histogram, T, and the genome-major
  * postings by a stable LSD radix sort of the postings on (genome, SCP). */
 int  pfaai_gpu_build(pfaai_gpu_ctx *ctx);

@@ -26,7 +26,7 @@ EXPORTS = [
     "pfaai_gpu_create", "pfaai_gpu_destroy", "pfaai_gpu_last_error", "pfaai_gpu_set_stream", "pfaai_gpu_set_shard",
     "pfaai_gpu_upload_index", "pfaai_gpu_build", "pfaai_gpu_get_arrays", "pfaai_gpu_compute_device",
     "pfaai_gpu_matrix_shape", "pfaai_gpu_matrix_dev", "pfaai_gpu_download_matrix", "pfaai_gpu_compute",
-    "pfaai_gpu_n_pairs", "pfaai_gpu_get_timings",
+    "pfaai_gpu_n_pairs", "pfaai_gpu_get_timings", "pfaai_gpu_shard_layout", "pfaai_gpu_index_device_buffers",
 ]
 
 
@@ -71,6 +71,8 @@ def load():
     L.pfaai_gpu_n_pairs.argtypes = [i32, i32, i32]
     L.pfaai_gpu_n_pairs.restype = i64
     L.pfaai_gpu_get_timings.argtypes = [vp, C.POINTER(Timings)]
+    L.pfaai_gpu_shard_layout.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(i64), vp]
+    L.pfaai_gpu_index_device_buffers.argtypes = [vp, i32, i32, i64, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     _lib = L
     return L
 
@@ -115,6 +117,7 @@ class PfaaiGpu:
 
     def set_shard(self, shard, n_shards):
         self._check(self._L.pfaai_gpu_set_shard(self._h, shard, n_shards), "set_shard")
+        self._n_shards = n_shards
 
     def upload_index(self, P, G, F, Lc, T=None):
         F = np.ascontiguousarray(F, dtype=PG_DTYPE)
@@ -127,6 +130,22 @@ class PfaaiGpu:
                 raise ValueError("T must be P x G")
         self.P, self.G, self.nF = P, G, F.shape[0]
         self._check(self._L.pfaai_gpu_upload_index(self._h, P, G, _p(F), _p(Lc), F.shape[0], _p(T)), "upload_index")
+
+    def index_device_buffers(self, P, G, nF, host_T=False):
+        """Size the device index buffers and return their pointers (F, Lc, T) for a caller-side fill (NCCL broadcast)."""
+        f, lc, t = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._check(self._L.pfaai_gpu_index_device_buffers(self._h, P, G, nF, int(host_T), C.byref(f), C.byref(lc), C.byref(t)),
+                    "index_device_buffers")
+        self.P, self.G, self.nF = P, G, nF
+        return f.value, lc.value, t.value
+
+    def shard_layout(self):
+        """-> (axis, ids): the sharded axis of the last compute's matrix and the global indices stored along it."""
+        axis, n = C.c_int(), C.c_int64()
+        self._check(self._L.pfaai_gpu_shard_layout(self._h, C.byref(axis), C.byref(n), None), "shard_layout")
+        ids = np.zeros(n.value, np.int32)
+        self._check(self._L.pfaai_gpu_shard_layout(self._h, C.byref(axis), C.byref(n), _p(ids)), "shard_layout")
+        return axis.value, ids
 
     def build(self):
         self._check(self._L.pfaai_gpu_build(self._h), "build")
@@ -173,6 +192,11 @@ class PfaaiGpu:
             shape = (nq, self.G)
         else:
             shape = (nq, self.G - nq)
+        if getattr(self, "_n_shards", 1) > 1:
+            if want_jac or want_counts:
+                raise PfaaiError("the JAC / counts hooks need an unsharded context")
+            self.compute_device(mode, q, flags)
+            return {"matrix": self.download_matrix(matrix_out), "jac": None, "aji": None, "counts": None}
         M = matrix_out if matrix_out is not None else np.empty(shape, np.float64)
         npairs = self.n_pairs(mode, nq)
         jac = np.zeros(npairs, JAC_DTYPE) if want_jac else None

@@ -52,13 +52,14 @@ struct TileParams {
     const int32_t *T;          // [P x t_ld]
     int t_ld, P;
     // output
-    double *out;               // cell (row i, col j) -> out[i*out_rs + j*out_cs]; symmetric: indexed by genome ids
+    double *out;               // cell (row i, col j) -> out[(i - I*TILE_ROWS + tile.z)*out_rs + j*out_cs]
     int64_t out_rs, out_cs;
-    int symmetric;
+    int symmetric;             // all-vs-all: only cells with row genome < column genome are computed ...
+    int mirror;                // ... and also stored at the transposed position (single-shard contexts)
     double *S_out;             // optional hooks, [n_rows x n_cols]
     int32_t *N_out;
     int32_t *counts_out;       // optional, [n_rows x n_cols x P]
-    const int2 *tiles;         // (row block, col block)
+    const int4 *tiles;         // (row block I, col block J, first output row of block I in this shard's matrix, -)
     int n_tiles;
 };
 
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
     };
 
     for (int t = blockIdx.x; t < prm.n_tiles; t += gridDim.x) {
-        const int2 tile = prm.tiles[t];
+        const int4 tile = prm.tiles[t];
         const int cb = tile.y;
         const int64_t sb = prm.stage_begin[cb];
         const int nst = (int)(prm.stage_begin[cb + 1] - sb);
@@ -221,6 +222,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         const int row = group * ROWS_PER_WARP + r;
         const bool row_ok = row < prm.n_rows;
         const int gi = row_ok ? prm.rows[row] : -1;
+        const int64_t row_out = (int64_t)(row - tile.x * TILE_ROWS + tile.z);
         const int ti = row_ok ? prm.row_t[row] : 0;
         const int j0 = cb * COLS_PER_TILE;
         const int ncol = min(COLS_PER_TILE, prm.n_cols - j0);
@@ -451,15 +453,13 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                     const int64_t j = j0 + col;
                     if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + j] = Ssum;
                     if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + j] = n;
-                    if (prm.symmetric) {
+                    if (prm.symmetric) {       // rows[] and cols[] are the identity: gi == row, gj == j
                         if (gi < gj) {
-                            prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = aji;
-                            prm.out[(int64_t)gj * prm.out_rs + (int64_t)gi * prm.out_cs] = aji;
-                        } else if (gi == gj) {
-                            prm.out[(int64_t)gi * prm.out_rs + (int64_t)gj * prm.out_cs] = 0.0;
-                        }
+                            prm.out[row_out * prm.out_rs + j * prm.out_cs] = aji;
+                            if (prm.mirror) prm.out[j * prm.out_rs + (int64_t)row * prm.out_cs] = aji;
+                        }                      // the diagonal and (sharded) the lower triangle stay 0 from the memset
                     } else {
-                        prm.out[(int64_t)row * prm.out_rs + j * prm.out_cs] = (gi == gj) ? 0.0 : aji;
+                        prm.out[row_out * prm.out_rs + j * prm.out_cs] = (gi == gj) ? 0.0 : aji;
                     }
                 }
             }

@@ -37,6 +37,8 @@ struct Ctx {
     DevBuf nsub, sub, colT, blob, stage_off, stages, stage_begin;
     int64_t out_rows = 0, out_cols = 0;
     int last_mode = -1;
+    std::vector<int32_t> owned_rows;   // kernel rows of this shard, in the order they are stored
+    int shard_axis = 0;
     // events / stats
     cudaEvent_t ev[14] = {};
     pfaai_timings_t tm = {};
@@ -188,6 +190,23 @@ int pfaai_gpu_upload_index(pfaai_gpu_ctx *h, int P, int G, const pfaai_pg_t *F, 
     PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));   // the caller may reuse its buffers
     c->tm.h2d_ms = ev_ms(c, EV_H2D0, EV_H2D1);
+    c->uploaded = true;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_index_device_buffers(pfaai_gpu_ctx *h, int P, int G, int64_t nF, int host_T, void **F_dev, void **Lc_dev, void **T_dev) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (P <= 0 || G <= 0 || nF < 0 || (int64_t)P * G >= (1ll << 31)) { set_error(c, "index_device_buffers: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (host_T != 0); c->built = false; c->uploaded = false;
+    PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
+    PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
+    if (F_dev) *F_dev = c->F.p;
+    if (Lc_dev) *Lc_dev = c->Lc.p;
+    if (T_dev) *T_dev = c->T.p;
+    c->tm.h2d_ms = 0.f;
     c->uploaded = true;
     return PFAAI_OK;
 }
@@ -445,20 +464,37 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     PF_LAUNCH_CHECK(c);
     PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
     // ---- tile list: row block x column block, I-major so that concurrently resident CTAs share the row
-    //      block's slabs in L2; symmetric mode keeps only tiles that contain a cell with row < col ----
-    std::vector<int2> tiles;
-    int64_t t_index = 0;
-    for (int I = 0; I < nrb; I++)
+    //      block's slabs in L2; symmetric mode keeps only tiles that contain a cell with row < col.
+    //      Sharding: row block I belongs to shard fold(I mod 2n) (folded assignment balances the
+    //      triangular work); a sharded context stores only its own row blocks, compactly, in ascending order ----
+    const bool sharded = c->n_shards > 1;
+    if (sharded && (want_sn || want_counts)) { set_error(c, "compute: the JAC / counts hooks need an unsharded context"); return PFAAI_ERR_CONSTRUCT; }
+    std::vector<int4> tiles;
+    c->owned_rows.clear();
+    int local_rows = 0;
+    for (int I = 0; I < nrb; I++) {
+        const int f = I % (2 * c->n_shards);
+        const int owner = f < c->n_shards ? f : 2 * c->n_shards - 1 - f;
+        if (owner != c->shard) continue;
+        const int row0 = I * TILE_ROWS, nr = std::min(TILE_ROWS, n_rows - row0);
         for (int J = 0; J < ncb; J++) {
             if (m.symmetric) {
-                const int row_min = I * TILE_ROWS, col_max = std::min((J + 1) * COLS_PER_TILE, n_cols) - 1;
-                if (row_min >= col_max) continue;
+                const int col_max = std::min((J + 1) * COLS_PER_TILE, n_cols) - 1;
+                if (row0 >= col_max) continue;
             }
-            if (t_index++ % c->n_shards == c->shard) tiles.push_back(make_int2(I, J));
+            tiles.push_back(make_int4(I, J, sharded ? local_rows : row0, 0));
         }
-    PF_TRY(ensure(c, c->tiles, sizeof(int2) * tiles.size()));
-    if (!tiles.empty()) PF_CUDA(c, cudaMemcpyAsync(c->tiles.p, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, c->stream));
-    // ---- outputs ----
+        for (int r = 0; r < nr; r++) c->owned_rows.push_back(row0 + r);
+        local_rows += nr;
+    }
+    PF_TRY(ensure(c, c->tiles, sizeof(int4) * tiles.size()));
+    if (!tiles.empty()) PF_CUDA(c, cudaMemcpyAsync(c->tiles.p, tiles.data(), sizeof(int4) * tiles.size(), cudaMemcpyHostToDevice, c->stream));
+    // ---- outputs: the kernel's row axis is the output's row axis in all-vs-all and its column axis otherwise ----
+    c->shard_axis = m.symmetric ? 0 : 1;
+    if (sharded) {
+        if (m.symmetric) m.out_rows = local_rows;                    // [owned rows x G], row stride G
+        else { m.out_cols = local_rows; m.cs = local_rows; }         // [nQ x owned targets]
+    }
     c->out_rows = m.out_rows; c->out_cols = m.out_cols;
     const size_t ncell = (size_t)m.out_rows * m.out_cols, nk = (size_t)n_rows * n_cols;
     PF_TRY(ensure(c, c->out, sizeof(double) * ncell));
@@ -480,11 +516,11 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.stages = ptr<StageDesc>(c->stages); prm.stage_begin = ptr<int64_t>(c->stage_begin);
     prm.blob = ptr<unsigned char>(c->blob); prm.colT = ptr<int32_t>(c->colT);
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
-    prm.out = ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric;
+    prm.out = ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !sharded) ? 1 : 0;
     prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
     prm.N_out = want_sn ? ptr<int32_t>(c->N_out) : nullptr;
     prm.counts_out = want_counts ? ptr<int32_t>(c->counts_out) : nullptr;
-    prm.tiles = ptr<int2>(c->tiles); prm.n_tiles = (int)tiles.size();
+    prm.tiles = ptr<int4>(c->tiles); prm.n_tiles = (int)tiles.size();
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
     if (!tiles.empty() && c->nF > 0) {
         if (lane_lookups <= 511) {
@@ -504,7 +540,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     c->tm.n_launches = c->launches;   // build + this compute
     // algorithmic bytes of the tile kernel: postings once, segment offsets, T, output once
     c->tm.tile_alg_bytes = 4 * c->nF + 8 * ((int64_t)P * c->G + 1) + 4 * (int64_t)P * c->G +
-                           (int64_t)(8 * (double)ncell / c->n_shards);
+                           8 * (int64_t)ncell;
     c->last_mode = mode;
     return PFAAI_OK;
 }
@@ -525,6 +561,15 @@ int pfaai_gpu_matrix_shape(const pfaai_gpu_ctx *h, int64_t *rows, int64_t *cols)
     if (!c) return PFAAI_ERR_CONSTRUCT;
     if (rows) *rows = c->out_rows;
     if (cols) *cols = c->out_cols;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_shard_layout(const pfaai_gpu_ctx *h, int *axis, int64_t *n, int32_t *ids) {
+    const Ctx *c = reinterpret_cast<const Ctx *>(h);
+    if (!c || c->last_mode < 0) return PFAAI_ERR_CONSTRUCT;
+    if (axis) *axis = c->shard_axis;
+    if (n) *n = (int64_t)c->owned_rows.size();
+    if (ids) std::copy(c->owned_rows.begin(), c->owned_rows.end(), ids);
     return PFAAI_OK;
 }
 

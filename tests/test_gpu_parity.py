@@ -168,24 +168,41 @@ def test_synthetic_subset_and_query_db_vs_oracle(pf, orc):
     ctx.close()
 
 
-def test_sharded_tiles_cover_matrix_exactly_once(pf, orc):
-    """Row-block sharding: the union of the shards' matrices is the full matrix, bit for bit."""
-    from parfastaai_b200 import synth
-    N, P = 500, 4
+@pytest.mark.parametrize("n_shards", [2, 3])
+def test_sharded_row_blocks_assemble_to_the_full_matrix(pf, orc, n_shards):
+    """Row-block sharding: every shard stores only its own blocks of 384 target genomes, compactly; the host
+    assembly (mirror in all-vs-all) reproduces the unsharded matrix bit for bit; every pair is computed exactly once."""
+    from parfastaai_b200 import sharding, synth
+    N, P = 1000, 3
     off, vals = synth.generate(N, P, seed=21)
     Lc, F = synth.to_reference(N, P, off, vals)
     ctx = pf.PfaaiGpu(0)
     ctx.upload_index(P, N, F, Lc)
     ctx.build()
     full = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
-    acc = np.zeros_like(full)
-    hits = np.zeros(full.shape, np.int32)
-    for s in range(3):
-        ctx.set_shard(s, 3)
+    axis, ids = ctx.shard_layout()
+    assert axis == 0 and np.array_equal(ids, np.arange(N))
+    qids = np.array([5, 17, 400, 401, 999], np.int32)
+    full_q = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=False)["matrix"].copy()
+    parts, lay, parts_q, lay_q, pairs = [], [], [], [], 0
+    for s in range(n_shards):
+        ctx.set_shard(s, n_shards)
         part = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
-        hits += part != 0
-        acc += part
+        axis, ids = ctx.shard_layout()
+        assert axis == 0 and np.array_equal(ids, sharding.owned_indices(N, s, n_shards))
+        assert part.shape == sharding.shard_shape(pf.ALL_VS_ALL, N, 0, s, n_shards)
+        # only cells with row < column are computed
+        assert all(np.all(part[k, :g + 1] == 0) for k, g in enumerate(ids))
+        pairs += sharding.pair_count(pf.ALL_VS_ALL, N, 0, s, n_shards)
+        parts.append(part.copy()); lay.append(ids)
+        pq = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=False)["matrix"]
+        axis, idq = ctx.shard_layout()
+        assert axis == 1 and pq.shape == (5, idq.shape[0])
+        parts_q.append(pq.copy()); lay_q.append(idq)
+        with pytest.raises(pf.PfaaiError):
+            ctx.compute(pf.ALL_VS_ALL, want_jac=True)
     ctx.set_shard(0, 1)
-    assert hits.max() == 1
-    assert np.array_equal(acc, full)
+    assert pairs == N * (N - 1) // 2
+    assert np.array_equal(sharding.assemble(pf.ALL_VS_ALL, parts, lay, np.empty((N, N))), full)
+    assert np.array_equal(sharding.assemble(pf.QUERY_SUBSET, parts_q, lay_q, np.empty((5, N))), full_q)
     ctx.close()
