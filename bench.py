@@ -295,6 +295,13 @@ def main():
     off = vals = None
     nF_t = torch.zeros(1, dtype=torch.int64, device=dev)
     if rank == 0:
+        if world > 1:
+            # torchrun exports OMP_NUM_THREADS=1; the synthetic generator (host tooling, OpenMP) should use the box
+            try:
+                import ctypes
+                ctypes.CDLL("libgomp.so.1").omp_set_num_threads(max(1, (os.cpu_count() or 1)))
+            except OSError:
+                pass
         off, vals = synth.generate(G, P, seed=SEED)
         nF = int(off[-1])
         F_pin = torch.empty(nF * 2, dtype=torch.int32).pin_memory()
