@@ -149,13 +149,16 @@ struct Mask64 { uint32_t lo, hi; };
 
 // x = slab_encode(v): bitmap word at byte offset x>>5; shifting it left by x&31 puts v's presence bit in
 // bit 31 and the presence bits of smaller tetramers below it (the rank half-word falls off the top).
-__device__ __forceinline__ Mask64 dict_lookup(const unsigned char *__restrict__ bm, const uint2 *__restrict__ masks, uint32_t x) {
-    const uint32_t w = *reinterpret_cast<const uint32_t *>(bm + (x >> 5));
-    const uint32_t t = __funnelshift_l(0u, w, x);                  // w << (x & 31)
+// A miss (57 % of the lookups on the synthetic family) adds the zero mask and issues no second load.
+// bm32 / masks32: 32-bit shared-space addresses of the stage's bitmap and mask array.
+__device__ __forceinline__ Mask64 dict_lookup(uint32_t bm32, uint32_t masks32, uint32_t x) {
+    uint32_t w;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(bm32 + (x >> 5)));
+    const uint32_t t = __funnelshift_l(0u, w, x);                   // w << (x & 31)
     const uint32_t idx = (w >> 16) + __popc(t);                     // rank of the word + #present <= v  (>= 1 on a hit)
-    const uint32_t slot = ((int32_t)t < 0) ? idx : 0u;              // slot 0 is the all-zero "miss" mask
-    const uint2 m = masks[slot];
-    Mask64 r; r.lo = m.x; r.hi = m.y;
+    Mask64 r; r.lo = 0u; r.hi = 0u;
+    if ((int32_t)t < 0)
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.lo), "=r"(r.hi) : "r"(masks32 + 8u * idx));
     return r;
 }
 
@@ -222,7 +225,6 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         const int row = group * ROWS_PER_WARP + r;
         const bool row_ok = row < prm.n_rows;
         const int gi = row_ok ? prm.rows[row] : -1;
-        const int64_t row_out = (int64_t)(row - tile.x * TILE_ROWS + tile.z);
         const int ti = row_ok ? prm.row_t[row] : 0;
         const int j0 = cb * COLS_PER_TILE;
         const int ncol = min(COLS_PER_TILE, prm.n_cols - j0);
@@ -299,8 +301,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
 
             // ================= walk: bit-sliced accumulation of the row half-lists =================
             {
-                const unsigned char *bm = stage_mem + (size_t)slot * STAGE_BYTES;
-                const uint2 *masks = reinterpret_cast<const uint2 *>(bm + BM_BYTES);
+                const uint32_t bm = smem_u32(stage_mem) + (uint32_t)slot * STAGE_BYTES;
+                const uint32_t masks = bm + BM_BYTES;
                 const uint4 *src = prm.ell + o_cur * 32 + lane;
                 const uint4 *src_nxt = prm.ell + o_nxt * 32 + lane;
                 for (int c = 0; c < n_cur; c += 2) {
@@ -433,38 +435,77 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         }
 
         // ================= output: AJI = S / N (computeAJI) into the dense matrix =================
-        __syncwarp();
+        // The tile (384 x 64 doubles) is staged in the two (now idle) stage slots and written out in contiguous
+        // segments: rows of 512 B for the direct cells, columns of 3 KB for the transposed ones (the mirror image in
+        // all-vs-all mode, everything in the query modes whose output is the kernel's transpose).  `out` may be
+        // device memory or mapped pinned host memory (pfaai_gpu_compute with a pinned matrix: the D2H copy is the
+        // kernel's own store stream and overlaps the remaining tiles).
+        double *stg = reinterpret_cast<double *>(stage_mem);                          // [TILE_ROWS][STG_PITCH]
+        int32_t *row_g = reinterpret_cast<int32_t *>(stage_mem + (size_t)TILE_ROWS * STG_PITCH * 8);   // [TILE_ROWS]
+        __syncthreads();   // every warp has finished walking both slots
+        {
+            const int rl = warp * ROWS_PER_WARP + r;
+            if (h == 0) row_g[rl] = gi;
+            __syncwarp();
 #pragma unroll
-        for (int g8 = 0; g8 < 4; g8++) {
-            uint32_t sv[16];
-            tmem_ld16(taddr + 16 * g8, sv);
-            tmem_wait_ld(sv);
+            for (int g8 = 0; g8 < 4; g8++) {
+                uint32_t sv[16];
+                tmem_ld16(taddr + 16 * g8, sv);
+                tmem_wait_ld(sv);
 #pragma unroll
-            for (int u = 0; u < 8; u++) {
-                const int jj = 8 * g8 + u;
-                const int col = cbase + jj;
-                if (row_ok && col < ncol) {
+                for (int u = 0; u < 8; u++) {
+                    const int jj = 8 * g8 + u;
+                    const int col = cbase + jj;
                     const double Ssum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]);
-                    const int gj = col_g[col];
                     int n = 0;
 #pragma unroll
                     for (int kk = 0; kk < N_PLANES_N; kk++) n |= (int)((Np[kk] >> jj) & 1u) << kk;
-                    const double aji = (n > 0) ? Ssum / (double)n : 0.0;
-                    const int64_t j = j0 + col;
-                    if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + j] = Ssum;
-                    if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + j] = n;
-                    if (prm.symmetric) {       // rows[] and cols[] are the identity: gi == row, gj == j
-                        if (gi < gj) {
-                            prm.out[row_out * prm.out_rs + j * prm.out_cs] = aji;
-                            if (prm.mirror) prm.out[j * prm.out_rs + (int64_t)row * prm.out_cs] = aji;
-                        }                      // the diagonal and (sharded) the lower triangle stay 0 from the memset
-                    } else {
-                        prm.out[row_out * prm.out_rs + j * prm.out_cs] = (gi == gj) ? 0.0 : aji;
+                    stg[rl * STG_PITCH + col] = (n > 0) ? Ssum / (double)n : 0.0;
+                    if (row_ok && col < ncol) {
+                        if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + (j0 + col)] = Ssum;
+                        if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + (j0 + col)] = n;
                     }
                 }
             }
         }
-        __syncthreads();   // every warp is done with col_g / colT / both slots before the next tile refills them
+        __syncthreads();
+        {
+            const int row0 = tile.x * TILE_ROWS;
+            const int nrow = min(TILE_ROWS, prm.n_rows - row0);
+            const int64_t ro0 = (int64_t)tile.z;                       // output row of the tile's first row
+            if (prm.out_cs == 1) {
+                // direct cells, one 512-B row segment per warp instruction pair; symmetric: only gi < gj, diagonal = 0
+                for (int rl = warp; rl < nrow; rl += TILE_WARPS) {
+                    const int g_i = row_g[rl];
+                    double *dst = prm.out + (ro0 + rl) * prm.out_rs + j0;
+#pragma unroll
+                    for (int c = lane; c < COLS_PER_TILE; c += 32) {
+                        if (c < ncol) {
+                            const int g_j = col_g[c];
+                            const double v = stg[rl * STG_PITCH + c];
+                            if (prm.symmetric) { if (g_i <= g_j) dst[c] = (g_i == g_j) ? 0.0 : v; }
+                            else dst[c] = (g_i == g_j) ? 0.0 : v;
+                        }
+                    }
+                }
+            }
+            if (prm.out_cs != 1 || prm.mirror) {
+                // transposed cells: for a fixed column the tile's rows are contiguous in the output
+                const int64_t cstride = (prm.out_cs != 1) ? prm.out_cs : prm.out_rs;   // step between columns j
+                const int64_t rbase = (prm.out_cs != 1) ? ro0 : (int64_t)row0;          // mirror: indexed by genome id
+                for (int c = warp; c < ncol; c += TILE_WARPS) {
+                    const int g_j = col_g[c];
+                    double *dst = prm.out + (int64_t)(j0 + c) * cstride + rbase;
+                    for (int rl = lane; rl < nrow; rl += 32) {
+                        const int g_i = row_g[rl];
+                        const double v = stg[rl * STG_PITCH + c];
+                        if (prm.symmetric) { if (g_i < g_j) dst[rl] = v; }
+                        else dst[rl] = (g_i == g_j) ? 0.0 : v;
+                    }
+                }
+            }
+        }
+        __syncthreads();   // staging, col_g and colT are free again before the next tile refills the slots
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();

@@ -53,6 +53,10 @@ constexpr int SMEM_MISC = 2048;
 constexpr int STAGE_BYTES = ((SMEM_TOTAL - SMEM_MISC - SMEM_RCP) / 2) & ~127;   // 107008
 constexpr int MASK_CAP = ((STAGE_BYTES - BM_BYTES) / 8) & ~1;        // entries incl. the all-zero miss slot 0
 
+// output staging of a finished tile inside the two stage slots: [TILE_ROWS][STG_PITCH] doubles + the rows' genome ids
+constexpr int STG_PITCH = COLS_PER_TILE + 1;                           // 65: conflict-free column reads
+static_assert((size_t)TILE_ROWS * STG_PITCH * 8 + TILE_ROWS * 4 <= 2 * (size_t)STAGE_BYTES, "tile staging does not fit");
+
 struct __align__(16) StageDesc {             // one pipeline stage = one bulk copy
     int64_t off;                             // byte offset of the blob [bitmap BM_BYTES][masks] in the dictionary buffer
     uint32_t bytes;                          // size of the bulk copy (multiple of 16)

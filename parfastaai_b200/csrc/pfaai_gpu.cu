@@ -37,6 +37,7 @@ struct Ctx {
     DevBuf nsub, sub, colT, blob, stage_off, stages, stage_begin;
     int64_t out_rows = 0, out_cols = 0;
     int last_mode = -1;
+    bool out_on_device = true;          // false: the last compute stored straight into the caller's pinned matrix
     std::vector<int32_t> owned_rows;   // kernel rows of this shard, in the order they are stored
     int shard_axis = 0;
     // events / stats
@@ -381,8 +382,10 @@ static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles) {
     return PFAAI_OK;
 }
 
+// direct_host: non-NULL = the caller's matrix is pinned host memory; the tile kernel stores straight into it (device alias
+// direct_dev) and no device copy of the matrix exists afterwards
 static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, unsigned flags, bool want_sn, bool want_counts,
-                            ModePlan &m) {
+                            ModePlan &m, double *direct_dev = nullptr) {
     if (!c->built) { set_error(c, "compute: index not built"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
     PF_TRY(plan_mode(c, mode, qry_ids, nQ, flags, m));
@@ -497,8 +500,12 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     }
     c->out_rows = m.out_rows; c->out_cols = m.out_cols;
     const size_t ncell = (size_t)m.out_rows * m.out_cols, nk = (size_t)n_rows * n_cols;
-    PF_TRY(ensure(c, c->out, sizeof(double) * ncell));
-    PF_CUDA(c, cudaMemsetAsync(c->out.p, 0, sizeof(double) * ncell, c->stream));
+    if (direct_dev && sharded) direct_dev = nullptr;   // compact shards keep zero-filled cells: staged path
+    c->out_on_device = (direct_dev == nullptr);
+    if (!direct_dev) {
+        PF_TRY(ensure(c, c->out, sizeof(double) * ncell));
+        PF_CUDA(c, cudaMemsetAsync(c->out.p, 0, sizeof(double) * ncell, c->stream));
+    }
     if (want_sn) {
         PF_TRY(ensure(c, c->S_out, sizeof(double) * nk)); PF_TRY(ensure(c, c->N_out, sizeof(int32_t) * nk));
         PF_CUDA(c, cudaMemsetAsync(c->S_out.p, 0, sizeof(double) * nk, c->stream));
@@ -516,7 +523,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.stages = ptr<StageDesc>(c->stages); prm.stage_begin = ptr<int64_t>(c->stage_begin);
     prm.blob = ptr<unsigned char>(c->blob); prm.colT = ptr<int32_t>(c->colT);
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
-    prm.out = ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !sharded) ? 1 : 0;
+    prm.out = direct_dev ? direct_dev : ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !sharded) ? 1 : 0;
     prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
     prm.N_out = want_sn ? ptr<int32_t>(c->N_out) : nullptr;
     prm.counts_out = want_counts ? ptr<int32_t>(c->counts_out) : nullptr;
@@ -575,12 +582,13 @@ int pfaai_gpu_shard_layout(const pfaai_gpu_ctx *h, int *axis, int64_t *n, int32_
 
 const double *pfaai_gpu_matrix_dev(const pfaai_gpu_ctx *h) {
     const Ctx *c = reinterpret_cast<const Ctx *>(h);
-    return c ? reinterpret_cast<const double *>(c->out.p) : nullptr;
+    return (c && c->out_on_device) ? reinterpret_cast<const double *>(c->out.p) : nullptr;
 }
 
 int pfaai_gpu_download_matrix(pfaai_gpu_ctx *h, double *M) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     if (!c || !M || c->last_mode < 0) { set_error(c, "download_matrix: nothing computed"); return PFAAI_ERR_CONSTRUCT; }
+    if (!c->out_on_device) { set_error(c, "download_matrix: the last compute stored the matrix directly into pinned host memory"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
     PF_CUDA(c, cudaEventRecord(c->ev[EV_D0], c->stream));
     PF_CUDA(c, cudaMemcpyAsync(M, c->out.p, sizeof(double) * (size_t)c->out_rows * c->out_cols, cudaMemcpyDeviceToHost, c->stream));
@@ -596,8 +604,19 @@ int pfaai_gpu_compute(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_
     if (!c) return PFAAI_ERR_CONSTRUCT;
     ModePlan m;
     const bool want_sn = jac || aji;
-    PF_TRY(compute_internal(c, mode, qry_ids, n_qry, flags, want_sn, counts != nullptr, m));
-    if (aji_matrix) PF_TRY(pfaai_gpu_download_matrix(h, aji_matrix));
+    // a pinned (page-locked, mapped) host matrix is written by the tile kernel itself: the D2H transfer is the kernel's
+    // store stream and overlaps the computation; pageable memory goes through a device buffer + one copy
+    double *direct_dev = nullptr;
+    if (aji_matrix) {
+        cudaPointerAttributes attr;
+        if (cudaPointerGetAttributes(&attr, aji_matrix) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer)
+            direct_dev = reinterpret_cast<double *>(attr.devicePointer);
+        else
+            cudaGetLastError();
+    }
+    PF_TRY(compute_internal(c, mode, qry_ids, n_qry, flags, want_sn, counts != nullptr, m, direct_dev));
+    c->tm.d2h_ms = 0.f;
+    if (aji_matrix && c->out_on_device) PF_TRY(pfaai_gpu_download_matrix(h, aji_matrix));
     if (!want_sn && !counts) return PFAAI_OK;
     // ---- small-N outputs in the reference's JAC order (initJAC of the mode) ----
     const int G = c->G, P = c->P;

@@ -206,3 +206,28 @@ def test_sharded_row_blocks_assemble_to_the_full_matrix(pf, orc, n_shards):
     assert np.array_equal(sharding.assemble(pf.ALL_VS_ALL, parts, lay, np.empty((N, N))), full)
     assert np.array_equal(sharding.assemble(pf.QUERY_SUBSET, parts_q, lay_q, np.empty((5, N))), full_q)
     ctx.close()
+
+
+def test_pinned_host_matrix_is_stored_directly_and_identically(pf, orc):
+    """pfaai_gpu_compute with a page-locked matrix: the tile kernel stores straight into host memory (no device copy
+    of the matrix, no D2H call); the bytes must equal the staged path's in all three modes, ragged tile edges included."""
+    import torch
+    from parfastaai_b200 import synth
+    N, P = 700, 5
+    off, vals = synth.generate(N, P, seed=33)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    qids = np.array([699, 3, 384, 64, 63], np.int32)
+    for mode, q, shape in [(pf.ALL_VS_ALL, None, (N, N)), (pf.QUERY_SUBSET, qids, (5, N)),
+                           (pf.QUERY_DB, np.arange(N - 90, N, dtype=np.int32), (90, N - 90))]:
+        staged = ctx.compute(mode, qry_ids=q, want_jac=False)["matrix"].copy()
+        assert ctx.matrix_dev_ptr()
+        pin = torch.full(shape, -7.0, dtype=torch.float64).pin_memory()   # poisoned: every cell must be written
+        direct = ctx.compute(mode, qry_ids=q, want_jac=False, matrix_out=pin.numpy())["matrix"]
+        assert not ctx.matrix_dev_ptr()
+        assert np.array_equal(direct, staged)
+        with pytest.raises(pf.PfaaiError):
+            ctx.download_matrix()
+    ctx.close()
