@@ -185,7 +185,7 @@ def reference_baseline(P, n_genomes, threads, tmpdir):
             "pairs_per_s_wall": pairs / wall}
 
 
-def run_reference_arm(args, rank):
+def run_reference_arm(args, rank, emit):
     if rank != 0:
         return 0
     P = args.scps
@@ -236,7 +236,7 @@ def run_reference_arm(args, rank):
                                 "genomes": n, "scps": P})
     line["e2e"] = {"value": line["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     line["gpu_launches"] = 0
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -259,11 +259,18 @@ def main():
     if args.warmup < 3 and args.impl == "ours":
         log("[bench] note: fewer than 3 warm-up steps requested; the timing rules ask for W >= 3")
 
+    # stdout carries exactly ONE JSON line: everything else that lands on fd 1 (e.g. NCCL's version banner) goes to stderr
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(json_fd, (json.dumps(obj) + "\n").encode())
+
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        return run_reference_arm(args, rank)
+        return run_reference_arm(args, rank, emit)
 
     import torch
     import torch.distributed as dist
@@ -498,7 +505,7 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     return 0
 
 

@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_final(const int32_t *__re
 // (K3: this IS the T matrix in the single-DB modes) with one REDG per posting.
 // ------------------------------------------------------------------------------------------------
 constexpr int MI_THREADS = 256;
-constexpr int MI_ITEMS = 8;                      // rounds per warp: a warp converts 256 consecutive postings
+constexpr int MI_ITEMS = 16;                     // rounds per warp: a warp converts 512 consecutive postings
 
 // largest t in [lo, hi] with Lp[t] <= i   (Lp non-decreasing, Lp[lo] <= i)
 __device__ __forceinline__ int tetramer_of(const int64_t *__restrict__ Lp, int lo, int hi, int64_t i) {
@@ -115,15 +115,32 @@ __global__ void __launch_bounds__(MI_THREADS) k_make_items(const pfaai_pg_t *__r
     const int64_t w0 = warp * (32 * MI_ITEMS);
     if (w0 == 0 && lane == 0 && Lp[NTETRA] != nF) *err = 2;   // sum(Lc) must equal |F|
     if (w0 >= nF) return;
-    // warp-uniform bracket [t_lo, t_hi] of the tetramers this warp's postings belong to (two broadcast searches),
-    // then a short per-item search inside it; all F loads and item stores are lane-consecutive (coalesced)
-    const int t_hi = tetramer_of(Lp, 0, NTETRA - 1, min(w0 + 32 * MI_ITEMS - 1, nF - 1));
-    int t = tetramer_of(Lp, 0, t_hi, w0);
-#pragma unroll
+    const int64_t last = min(w0 + 32 * MI_ITEMS - 1, nF - 1);
+    // one warp-uniform search for the tetramer of the warp's first posting; the next 32 block boundaries are then held
+    // one per lane, and (the common case: the warp's 512 postings span fewer than 32 tetramer blocks) every posting finds
+    // its tetramer with a 5-step shuffle search instead of touching Lp again.  All F loads / item stores are coalesced.
+    const int t0 = tetramer_of(Lp, 0, NTETRA - 1, w0);
+    const int tb = min(t0 + 1 + lane, NTETRA);
+    const int64_t bnd = Lp[tb];                                       // start of block t0+1+lane (Lp[NTETRA] = nF)
+    const bool local = __shfl_sync(0xffffffffu, bnd, 31) > last || t0 + 32 >= NTETRA;
+    const int t_hi = local ? 0 : tetramer_of(Lp, t0, NTETRA - 1, last);
+#pragma unroll 4
     for (int k = 0; k < MI_ITEMS; k++) {
         const int64_t i = w0 + k * 32 + lane;
-        if (i >= nF) break;
-        t = tetramer_of(Lp, t, t_hi, i);
+        const bool valid = i < nF;
+        int t;
+        if (local) {           // t = t0 + #{boundaries <= i}; boundaries ascend, so a binary search over the lanes
+            int pos = 0;
+#pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) {
+                const int64_t b = __shfl_sync(0xffffffffu, bnd, pos + sft - 1);
+                if (b <= i) pos += sft;
+            }
+            t = min(t0 + pos, NTETRA - 1);
+        } else {
+            t = valid ? tetramer_of(Lp, t0, t_hi, i) : 0;
+        }
+        if (!valid) continue;
         const pfaai_pg_t e = F[i];
         uint32_t seg = (uint32_t)e.genome * (uint32_t)P + (uint32_t)e.protein;
         // a bad id fails the build; it is still counted (in segment 0) so that the sort's histograms stay consistent
@@ -163,12 +180,19 @@ __global__ void k_transpose_t(const uint32_t *__restrict__ seg_len, int P, int G
 //   Stability: tile order x warp strip order x round order x lane order == input order.
 // ------------------------------------------------------------------------------------------------
 constexpr int RS_RADIX = 256;
-constexpr int OS_THREADS = 512;
+#ifndef PF_OS_THREADS
+#define PF_OS_THREADS 384
+#endif
+#ifndef PF_OS_CTAS
+#define PF_OS_CTAS 2
+#endif
+constexpr int OS_THREADS = PF_OS_THREADS;         // >= 256 (one thread per digit in the scan / look-back phases)
 constexpr int OS_WARPS = OS_THREADS / 32;
 constexpr int OS_ITEMS = 16;                          // rounds per warp strip
 constexpr int OS_TILE = OS_THREADS * OS_ITEMS;        // 8192 items = 64 KB
 constexpr int OS_SMEM = OS_TILE * 8 + OS_WARPS * RS_RADIX * 4 + RS_RADIX * (4 + 8) + 64;
 constexpr int MAX_PASSES = 4;
+constexpr int OS_LB = 8;                               // look-back window: status words fetched per round trip
 constexpr uint64_t OS_FLAG_LOCAL = 1ull << 62, OS_FLAG_INCL = 2ull << 62, OS_COUNT_MASK = (1ull << 62) - 1;
 
 // hist[pass][d] = number of items whose pass-th key digit is d = sum of seg_len over the segments with that digit
@@ -207,7 +231,7 @@ __device__ __forceinline__ void st_volatile_u64(uint64_t *p, uint64_t v) {
 
 // control: [0] = tile counter, followed (at +8 words) by status[n_tiles][256]; zeroed before every pass
 template <bool LAST>
-__global__ void __launch_bounds__(OS_THREADS, 2) k_onesweep(const uint64_t *__restrict__ in, int64_t n, int shift,
+__global__ void __launch_bounds__(OS_THREADS, PF_OS_CTAS) k_onesweep(const uint64_t *__restrict__ in, int64_t n, int shift,
                                                              const unsigned long long *__restrict__ digit_base /*[256]*/,
                                                              uint64_t *__restrict__ control, uint64_t *__restrict__ out,
                                                              uint32_t *__restrict__ out_vals) {
@@ -229,23 +253,42 @@ __global__ void __launch_bounds__(OS_THREADS, 2) k_onesweep(const uint64_t *__re
     const int n_tile = (int)min((int64_t)OS_TILE, n - tile0);
 
     // ---- load + per-warp stable ranks ----
+    // peers of an item = the lanes of its round that hold the same digit, found with 8 ballots (one per digit bit; the 16
+    // rounds are independent, so the ballots pipeline -- MATCH.ANY serialised this phase: 40 % of the v1 kernel's stalls);
+    // the lowest peer lane then bumps the warp's digit counter and broadcasts the old value.
     uint64_t it[OS_ITEMS];
+    uint32_t peers[OS_ITEMS];
     uint16_t loc[OS_ITEMS];
     uint32_t *wc = wcount + warp * RS_RADIX;
 #pragma unroll
     for (int r = 0; r < OS_ITEMS; r++) {
         const int li = warp * (32 * OS_ITEMS) + r * 32 + lane;
+        it[r] = (li < n_tile) ? in[tile0 + li] : ~0ull;
+    }
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; r++) {
+        const int li = warp * (32 * OS_ITEMS) + r * 32 + lane;
         const bool valid = li < n_tile;
-        it[r] = valid ? in[tile0 + li] : ~0ull;
-        const uint32_t d = valid ? ((uint32_t)(it[r] >> shift) & (RS_RADIX - 1)) : RS_RADIX;   // RS_RADIX = "none"
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const uint32_t rank = __popc(peers & lt_mask);
+        const uint32_t d = (uint32_t)(it[r] >> shift) & (RS_RADIX - 1);
+        uint32_t m = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            const bool bit = (d >> b) & 1u;
+            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+            m &= bit ? bal : ~bal;
+        }
+        peers[r] = valid ? m : 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; r++) {
+        const uint32_t d = (uint32_t)(it[r] >> shift) & (RS_RADIX - 1);
+        const uint32_t pm = peers[r];
+        const int leader = __ffs(pm) - 1;                 // -1 for an invalid item
         uint32_t old = 0;
-        if (valid) old = wc[d];
+        if (lane == leader) { old = wc[d]; wc[d] = old + __popc(pm); }
         __syncwarp();
-        if (valid && rank == 0) wc[d] = old + __popc(peers);
-        __syncwarp();
-        loc[r] = (uint16_t)(old + rank);
+        old = __shfl_sync(0xffffffffu, old, leader & 31);
+        loc[r] = (uint16_t)(old + __popc(pm & lt_mask));
     }
     __syncthreads();
 
@@ -270,13 +313,24 @@ __global__ void __launch_bounds__(OS_THREADS, 2) k_onesweep(const uint64_t *__re
         }
     }
     if (tid < RS_RADIX) {
+        // look-back, OS_LB predecessors per round trip: their status words are fetched together (independent loads) and
+        // consumed nearest-first; a word that is not published yet is re-polled (its tile is resident: it took its id
+        // earlier).  A one-at-a-time walk costs one L2 latency per in-flight predecessor and dominated the v1 kernel.
         uint64_t excl = 0;
-        for (int64_t t = tile - 1; t >= 0;) {
-            const uint64_t v = ld_volatile_u64(&status[t * RS_RADIX + tid]);
-            if ((v >> 62) == 0) continue;                 // not published yet (tile t is resident: it took its id earlier)
-            excl += v & OS_COUNT_MASK;
-            if (v & OS_FLAG_INCL) break;
-            t--;
+        bool done = (tile == 0);
+        for (int64_t t = tile - 1; !done; t -= OS_LB) {
+            uint64_t v[OS_LB];
+#pragma unroll
+            for (int u = 0; u < OS_LB; u++)
+                v[u] = (t - u >= 0) ? ld_volatile_u64(&status[(t - u) * RS_RADIX + tid]) : OS_FLAG_INCL;   // before tile 0: prefix 0
+#pragma unroll
+            for (int u = 0; u < OS_LB; u++) {
+                if (!done) {
+                    while ((v[u] >> 62) == 0) v[u] = ld_volatile_u64(&status[(t - u) * RS_RADIX + tid]);
+                    excl += v[u] & OS_COUNT_MASK;
+                    done = (v[u] & OS_FLAG_INCL) != 0;
+                }
+            }
         }
         if (tile > 0) st_volatile_u64(&status[tile * RS_RADIX + tid], OS_FLAG_INCL | (excl + cnt));
         gbase[tid] = (int64_t)digit_base[tid] + (int64_t)excl - (int64_t)dstart[tid];

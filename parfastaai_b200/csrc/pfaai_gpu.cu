@@ -438,6 +438,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     }
     PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
     PF_CUDA(c, cudaFuncSetAttribute(k_dict_build, cudaFuncAttributeMaxDynamicSharedMemorySize, DB_SMEM));
+    PF_CUDA(c, cudaFuncSetAttribute(k_dict_build, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     unsigned long long *cursor = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->flags.p) + 32);
     for (int attempt = 0;; attempt++) {
         PF_CUDA(c, cudaMemsetAsync(reinterpret_cast<char *>(c->flags.p) + 8, 0, 56, c->stream));   // flags[2..], cursor

@@ -107,6 +107,7 @@ __global__ void __launch_bounds__(256) k_pack_fill(const int64_t *__restrict__ s
 // ------------------------------------------------------------------------------------------------
 constexpr int DB_THREADS = 512;
 constexpr int DB_WARPS = DB_THREADS / 32;
+constexpr int DB_ILP = 1;                         // independent posting loads in flight per warp (4 measured slower: 7.2 vs 6.1 ms)
 constexpr int DB_WPT = (BM_WORDS + DB_THREADS - 1) / DB_THREADS;   // bitmap words scanned per thread
 constexpr int DB_SMEM = BM_BYTES + MASK_CAP * 8 + COLS_PER_TILE * (8 + 4 + 4) + 40 * 4 + 16;
 
@@ -137,13 +138,22 @@ __device__ __forceinline__ uint32_t dict_count(const DictParams &prm, const Dict
     int maxlen = 0;
     for (int c = c0; c < c1; c++) maxlen = max(maxlen, q ? s.col_len[c] - s.col_split[c] : s.col_split[c]);
     const int nchunk = (maxlen + 31) >> 5, ncs = c1 - c0;
-    for (int t = warp; t < nchunk * ncs; t += DB_WARPS) {
-        const int c = c0 + t % ncs, k = (t / ncs) * 32 + lane;
-        const int beg = q ? s.col_split[c] : 0, cnt = q ? s.col_len[c] - beg : s.col_split[c];
-        if (k < cnt) {
-            const uint32_t v = prm.vals[s.col_beg[c] + beg + k] - (uint32_t)q * RANGE_T;
-            atomicOr(&s.W[v >> 4], 1u << (v & 15u));
+    // DB_ILP independent (column, 32-posting chunk) tasks per warp and step: the loads are issued together
+    for (int t0 = warp; t0 < nchunk * ncs; t0 += DB_WARPS * DB_ILP) {
+        uint32_t v[DB_ILP];
+#pragma unroll
+        for (int u = 0; u < DB_ILP; u++) {
+            const int t = t0 + u * DB_WARPS;
+            v[u] = ~0u;
+            if (t < nchunk * ncs) {
+                const int c = c0 + t % ncs, k = (t / ncs) * 32 + lane;
+                const int beg = q ? s.col_split[c] : 0, cnt = q ? s.col_len[c] - beg : s.col_split[c];
+                if (k < cnt) v[u] = __ldg(prm.vals + s.col_beg[c] + beg + k) - (uint32_t)q * RANGE_T;
+            }
         }
+#pragma unroll
+        for (int u = 0; u < DB_ILP; u++)
+            if (v[u] != ~0u) atomicOr(&s.W[v[u] >> 4], 1u << (v[u] & 15u));
     }
     __syncthreads();
     const int w0 = tid * DB_WPT, w1 = min(w0 + DB_WPT, BM_WORDS);
@@ -189,14 +199,27 @@ __device__ __forceinline__ void dict_emit(const DictParams &prm, const DictSmem 
     for (int c = c0; c < c1; c++) maxlen = max(maxlen, q ? s.col_len[c] - s.col_split[c] : s.col_split[c]);
     const int nchunk = (maxlen + 31) >> 5, ncs = c1 - c0;
     uint32_t *m32 = reinterpret_cast<uint32_t *>(s.masks);
-    for (int t = warp; t < nchunk * ncs; t += DB_WARPS) {
-        const int c = c0 + t % ncs, k = (t / ncs) * 32 + lane;
-        const int beg = q ? s.col_split[c] : 0, cnt = q ? s.col_len[c] - beg : s.col_split[c];
-        if (k < cnt) {
-            const uint32_t v = prm.vals[s.col_beg[c] + beg + k] - (uint32_t)q * RANGE_T;
-            const uint32_t w = s.W[v >> 4];
-            const uint32_t idx = (w >> 16) + __popc(w & ((2u << (v & 15u)) - 1u) & 0xffffu);   // rank + #present <= v
-            atomicOr(&m32[2 * idx + (c >> 5)], 1u << (c & 31));
+    for (int t0 = warp; t0 < nchunk * ncs; t0 += DB_WARPS * DB_ILP) {
+        uint32_t v[DB_ILP];
+        int cc[DB_ILP];
+#pragma unroll
+        for (int u = 0; u < DB_ILP; u++) {
+            const int t = t0 + u * DB_WARPS;
+            v[u] = ~0u; cc[u] = 0;
+            if (t < nchunk * ncs) {
+                const int c = c0 + t % ncs, k = (t / ncs) * 32 + lane;
+                const int beg = q ? s.col_split[c] : 0, cnt = q ? s.col_len[c] - beg : s.col_split[c];
+                cc[u] = c;
+                if (k < cnt) v[u] = __ldg(prm.vals + s.col_beg[c] + beg + k) - (uint32_t)q * RANGE_T;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < DB_ILP; u++) {
+            if (v[u] != ~0u) {
+                const uint32_t w = s.W[v[u] >> 4];
+                const uint32_t idx = (w >> 16) + __popc(w & ((2u << (v[u] & 15u)) - 1u) & 0xffffu);   // rank + #present <= v
+                atomicOr(&m32[2 * idx + (cc[u] >> 5)], 1u << (cc[u] & 31));
+            }
         }
     }
     const uint32_t bytes = BM_BYTES + 8u * n_pad;
@@ -222,7 +245,7 @@ __device__ __forceinline__ void dict_emit(const DictParams &prm, const DictSmem 
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(DB_THREADS, 1) k_dict_build(const DictParams prm) {
+__global__ void __launch_bounds__(DB_THREADS, 2) k_dict_build(const DictParams prm) {   // 2 CTAs / SM: the phases are latency-bound
     extern __shared__ __align__(16) unsigned char sm[];
     DictSmem s;
     s.W = reinterpret_cast<uint32_t *>(sm);
