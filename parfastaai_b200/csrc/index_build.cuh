@@ -183,6 +183,9 @@ constexpr int RS_RADIX = 256;
 #ifndef PF_OS_THREADS
 #define PF_OS_THREADS 384
 #endif
+#ifndef PF_OS_MATCH
+#define PF_OS_MATCH 0                             // 1: MATCH.ANY ranks (fewer instructions, longer latency); 0: 8 ballots per item
+#endif
 #ifndef PF_OS_CTAS
 #define PF_OS_CTAS 2
 #endif
@@ -270,6 +273,9 @@ __global__ void __launch_bounds__(OS_THREADS, PF_OS_CTAS) k_onesweep(const uint6
         const int li = warp * (32 * OS_ITEMS) + r * 32 + lane;
         const bool valid = li < n_tile;
         const uint32_t d = (uint32_t)(it[r] >> shift) & (RS_RADIX - 1);
+#if PF_OS_MATCH
+        const uint32_t m = __match_any_sync(0xffffffffu, valid ? d : (RS_RADIX + (uint32_t)lane));
+#else
         uint32_t m = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
         for (int b = 0; b < 8; b++) {
@@ -277,6 +283,7 @@ __global__ void __launch_bounds__(OS_THREADS, PF_OS_CTAS) k_onesweep(const uint6
             const uint32_t bal = __ballot_sync(0xffffffffu, bit);
             m &= bit ? bal : ~bal;
         }
+#endif
         peers[r] = valid ? m : 0u;
     }
 #pragma unroll

@@ -7,7 +7,7 @@
 // exit codes: 0 ok, 1 DB open failure, 3 bad subset / overlapping query DB / construct failure,
 // 105 missing input file, 106 missing required argument, 109 unknown argument (CLI11's codes).
 // Everything between the SQLite load and the CSV writer runs on the GPU behind include/pfaai_gpu.h.
-// Extra switches of this build: --device N, --no-ref-compat (query-DB mode: corrected T lookup instead of the
+// Extra switches of this build: --device N, --gpus N (row-block sharding over N GPUs), --no-ref-compat (query-DB mode: corrected T lookup instead of the
 // reference's label quirk), --dump-index PREFIX (host only: write Lc/F/T as raw little-endian arrays and exit;
 // used by the CPU tests of the loader), --format-doubles FILE (test hook of the CSV cell formatter).
 #include <sys/stat.h>
@@ -33,8 +33,8 @@ struct AppParams {
     std::string outFieldSeparator = ",";
     std::vector<std::string> qryGenomeSet;
     std::string dumpIndexPrefix, formatDoublesFile;
-    int device = 0;
-    bool refCompat = true;
+    int device = 0, nGpus = 1;
+    bool refCompat = true, sameDevice = false;
 
     static bool is_file(const std::string &p) {
         struct stat st;
@@ -50,7 +50,8 @@ struct AppParams {
            << "  -r,--query_db TEXT:FILE     Path to the Query Database [Optional (default: Same as the Input DB)]\n"
            << "  -s,--separator TEXT [,]     Field Separator in the output file [Optional (default: ,)].\n"
            << "  -q,--query_subset TEXT:FILE Path to Query List (Should be subset of genomoes in the input DB.)\n"
-           << "  --device INT [0]            CUDA device ordinal\n"
+           << "  --device INT [0]            first CUDA device ordinal\n"
+           << "  --gpus INT [1]              number of GPUs (devices device..device+gpus-1); output row blocks are sharded over them\n"
            << "  --no-ref-compat             query-DB mode: corrected T lookup (default reproduces the reference)\n"
            << "  --dump-index TEXT           host only: write PREFIX.{lc,f,t}.bin and exit\n";
     }
@@ -89,7 +90,12 @@ struct AppParams {
                 std::string d;
                 if (!need(d)) return fail(114, "--device: 1 required INT missing");
                 device = std::atoi(d.c_str());
-            } else if (a == "--no-ref-compat") refCompat = false;
+            } else if (a == "--gpus") {
+                std::string d;
+                if (!need(d)) return fail(114, "--gpus: 1 required INT missing");
+                nGpus = std::max(1, std::atoi(d.c_str()));
+            } else if (a == "--same-device") sameDevice = true;   // test hook: all shards on one GPU
+            else if (a == "--no-ref-compat") refCompat = false;
             else if (a == "--dump-index") {
                 if (!need(dumpIndexPrefix)) return fail(114, "--dump-index: 1 required TEXT missing");
             } else if (a == "--format-doubles") {
@@ -163,7 +169,7 @@ void printOutput(const DataStructBase &pfdata, const ParFAAIImpl &impl, const Ap
 }
 
 template <typename DataT> int construct_run_print(DataT &data, const AppParams &args) {
-    data.setDevice(args.device);
+    data.setDevices(args.device, args.nGpus, args.sameDevice);
     const pfaai_status rc = data.construct();    // (the reference tests the wrong variable here; we return the code)
     if (rc != PFAAI_OK) return rc;
     ParFAAIImpl impl(data);

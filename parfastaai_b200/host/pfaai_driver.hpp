@@ -17,6 +17,7 @@
 #include <iostream>
 #include <memory>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -54,9 +55,9 @@ class DataStructBase {
     const DBMetaData &m_dbMeta;
     HostIndex m_ix;
     std::vector<int32_t> m_Lp;
-    pfaai_gpu_ctx *m_ctx = nullptr;
+    std::vector<pfaai_gpu_ctx *> m_ctxs;     // one context per GPU; every GPU holds the whole index
     pfaai_status m_errorCode = PFAAI_OK;
-    int m_device = 0;
+    std::vector<int> m_devices{0};
     bool m_hostT = false;   // query-DB mode: T comes from the host (F is inner-joined, T is not)
 
     virtual int loadHostIndex(HostIndex &ix) = 0;   // SQLite rc
@@ -65,10 +66,17 @@ class DataStructBase {
     explicit DataStructBase(const DBMetaData &meta) : m_dbMeta(meta) {}
     DataStructBase(const DataStructBase &) = delete;
     DataStructBase &operator=(const DataStructBase &) = delete;
-    virtual ~DataStructBase() { if (m_ctx) pfaai_gpu_destroy(m_ctx); }
+    virtual ~DataStructBase() { for (pfaai_gpu_ctx *c : m_ctxs) pfaai_gpu_destroy(c); }
 
-    void setDevice(int device) { m_device = device; }
-    pfaai_gpu_ctx *ctx() const { return m_ctx; }
+    void setDevice(int device) { m_devices.assign(1, device); }
+    // run on GPUs first .. first+n-1: output row blocks are sharded over them, no collective
+    // (same_device: all n contexts on GPU `first` -- exercises the sharded path on a single-GPU box)
+    void setDevices(int first, int n, bool same_device = false) {
+        m_devices.clear();
+        for (int i = 0; i < n; i++) m_devices.push_back(same_device ? first : first + i);
+    }
+    int nDevices() const { return (int)m_devices.size(); }
+    pfaai_gpu_ctx *ctx(int k = 0) const { return k < (int)m_ctxs.size() ? m_ctxs[k] : nullptr; }
     const HostIndex &hostIndex() const { return m_ix; }
 
     // == refLc / refLp / refT / refF / refProteinSet (interface.hpp:246-256).  refLp/refT are read back from
@@ -103,18 +111,33 @@ class DataStructBase {
             return m_errorCode = PFAAI_ERR_SQLITE_DB;
         }
         std::printf("Lc, F, T host load  : %10.3f ms; |F| = %zu\n", tm.lap_ms(), m_ix.F.size());
-        int rc = pfaai_gpu_create(&m_ctx, m_device, 0);
-        if (rc != PFAAI_OK) {
-            std::cerr << "Error in GPU context ; " << pfaai_gpu_last_error(nullptr) << std::endl;
-            return m_errorCode = (pfaai_status)rc;
+        // one host thread per GPU (the C-ABI is one-thread-per-context): upload + device build on every GPU in parallel
+        const int n = (int)m_devices.size();
+        m_ctxs.assign(n, nullptr);
+        std::vector<int> rcs(n, PFAAI_OK);
+        std::vector<std::string> errs(n);
+        auto work = [&](int k) {
+            int rc = pfaai_gpu_create(&m_ctxs[k], m_devices[k], 0);
+            if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(nullptr); return; }
+            rc = pfaai_gpu_upload_index(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(),
+                                        m_hostT ? m_ix.T.data() : nullptr);
+            if (rc == PFAAI_OK) rc = pfaai_gpu_build(m_ctxs[k]);
+            if (rc == PFAAI_OK) rc = pfaai_gpu_set_shard(m_ctxs[k], k, n);
+            if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(m_ctxs[k]); }
+        };
+        {
+            std::vector<std::thread> th;
+            for (int k = 1; k < n; k++) th.emplace_back(work, k);
+            work(0);
+            for (auto &t : th) t.join();
         }
-        rc = pfaai_gpu_upload_index(m_ctx, m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(),
-                                    m_hostT ? m_ix.T.data() : nullptr);
-        if (rc == PFAAI_OK) rc = pfaai_gpu_build(m_ctx);
-        if (rc != PFAAI_OK) {
-            std::cerr << "Error in device index build ; " << pfaai_gpu_last_error(m_ctx) << std::endl;
-            return m_errorCode = (pfaai_status)rc;
-        }
+        for (int k = 0; k < n; k++)
+            if (rcs[k] != PFAAI_OK) {
+                std::cerr << "Error in device index build (GPU " << m_devices[k] << ") ; " << errs[k] << std::endl;
+                return m_errorCode = (pfaai_status)rcs[k];
+            }
+        pfaai_gpu_ctx *m_ctx = m_ctxs[0];
+        int rc;
         m_Lp.resize(NTETRAMERS);
         std::vector<int32_t> Tdev((size_t)m_ix.nProteins * m_ix.nGenomes);
         rc = pfaai_gpu_get_arrays(m_ctx, nullptr, m_Lp.data(), Tdev.data(), nullptr, nullptr);
@@ -129,8 +152,8 @@ class DataStructBase {
         }
         pfaai_timings_t t;
         pfaai_gpu_get_timings(m_ctx, &t);
-        std::printf("Device index build  : %10.3f ms; (H2D %.3f ms, build kernels %.3f ms, of which sort %.3f ms)\n", tm.lap_ms(),
-                    t.h2d_ms, t.build_ms, t.sort_ms);
+        std::printf("Device index build  : %10.3f ms; (%d GPU(s); GPU %d: H2D %.3f ms, build kernels %.3f ms, of which sort %.3f ms)\n",
+                    tm.lap_ms(), n, m_devices[0], t.h2d_ms, t.build_ms, t.sort_ms);
         return m_errorCode = PFAAI_OK;
     }
 };
@@ -262,24 +285,70 @@ class ParFAAIImpl {
 
     int computeJAC() {
         PhaseTimer tm;
+        const int n = c_pfDSRef.nDevices();
         pfaai_gpu_ctx *ctx = c_pfDSRef.ctx();
         if (!ctx) { std::cerr << "Error in JAC Construction ; construct() has not succeeded" << std::endl; return PFAAI_ERR_CONSTRUCT; }
         const int64_t np = c_pfDSRef.nGenomePairs();
         const std::vector<int32_t> &q = c_pfDSRef.queryIds();
-        m_matrix.assign((size_t)c_pfDSRef.qrySetSize() * c_pfDSRef.tgtSetSize(), 0.0);
-        m_haveLists = np <= JAC_LIST_MAX_PAIRS;
-        std::vector<pfaai_jac_t> jac;
-        if (m_haveLists) { jac.resize((size_t)np); m_AJI.assign((size_t)np, 0.0); }
-        const int rc = pfaai_gpu_compute(ctx, c_pfDSRef.mode(), q.empty() ? nullptr : q.data(), (int)q.size(), c_pfDSRef.computeFlags(),
-                                         m_matrix.data(), m_haveLists ? jac.data() : nullptr, m_haveLists ? m_AJI.data() : nullptr,
-                                         nullptr);
-        if (rc != PFAAI_OK) { std::cerr << "Error in JAC Construction ; " << pfaai_gpu_last_error(ctx) << std::endl; return rc; }
-        m_JAC.resize(jac.size());
-        for (size_t i = 0; i < jac.size(); i++) { m_JAC[i].genomeA = jac[i].gA; m_JAC[i].genomeB = jac[i].gB; m_JAC[i].S = jac[i].S; m_JAC[i].N = jac[i].N; }
+        const size_t nQ = (size_t)c_pfDSRef.qrySetSize(), nT = (size_t)c_pfDSRef.tgtSetSize();
+        m_matrix.assign(nQ * nT, 0.0);
         pfaai_timings_t t;
-        pfaai_gpu_get_timings(ctx, &t);
-        std::printf("JAC Construction    : %10.3f ms; (row slabs %.3f ms, dictionaries %.3f ms, tile kernel %.3f ms over %d tiles, D2H %.3f ms)\n",
-                    tm.lap_ms(), t.pack_ms, t.dict_ms, t.tile_ms, t.n_tiles, t.d2h_ms);
+        if (n == 1) {
+            m_haveLists = np <= JAC_LIST_MAX_PAIRS;
+            std::vector<pfaai_jac_t> jac;
+            if (m_haveLists) { jac.resize((size_t)np); m_AJI.assign((size_t)np, 0.0); }
+            const int rc = pfaai_gpu_compute(ctx, c_pfDSRef.mode(), q.empty() ? nullptr : q.data(), (int)q.size(), c_pfDSRef.computeFlags(),
+                                             m_matrix.data(), m_haveLists ? jac.data() : nullptr, m_haveLists ? m_AJI.data() : nullptr,
+                                             nullptr);
+            if (rc != PFAAI_OK) { std::cerr << "Error in JAC Construction ; " << pfaai_gpu_last_error(ctx) << std::endl; return rc; }
+            m_JAC.resize(jac.size());
+            for (size_t i = 0; i < jac.size(); i++) { m_JAC[i].genomeA = jac[i].gA; m_JAC[i].genomeB = jac[i].gB; m_JAC[i].S = jac[i].S; m_JAC[i].N = jac[i].N; }
+            pfaai_gpu_get_timings(ctx, &t);
+        } else {
+            // every GPU computes its own output row blocks (all-vs-all: upper triangle only); the host scatters the compact
+            // parts into the dense matrix and mirrors -- "only the final matrix is gathered to the host writer"
+            m_haveLists = false; m_JAC.clear(); m_AJI.clear();
+            std::vector<int> rcs(n, PFAAI_OK);
+            std::vector<std::vector<double>> parts(n);
+            std::vector<std::vector<int32_t>> ids(n);
+            std::vector<int> axes(n, 0);
+            auto work = [&](int k) {
+                pfaai_gpu_ctx *c = c_pfDSRef.ctx(k);
+                int rc = pfaai_gpu_compute_device(c, c_pfDSRef.mode(), q.empty() ? nullptr : q.data(), (int)q.size(), c_pfDSRef.computeFlags());
+                int64_t rows = 0, cols = 0, cnt = 0;
+                if (rc == PFAAI_OK) rc = pfaai_gpu_matrix_shape(c, &rows, &cols);
+                if (rc == PFAAI_OK) { parts[k].resize((size_t)rows * cols); rc = pfaai_gpu_download_matrix(c, parts[k].data()); }
+                if (rc == PFAAI_OK) rc = pfaai_gpu_shard_layout(c, &axes[k], &cnt, nullptr);
+                if (rc == PFAAI_OK) { ids[k].resize((size_t)cnt); rc = pfaai_gpu_shard_layout(c, &axes[k], &cnt, ids[k].data()); }
+                rcs[k] = rc;
+            };
+            std::vector<std::thread> th;
+            for (int k = 1; k < n; k++) th.emplace_back(work, k);
+            work(0);
+            for (auto &x : th) x.join();
+            for (int k = 0; k < n; k++)
+                if (rcs[k] != PFAAI_OK) { std::cerr << "Error in JAC Construction ; " << pfaai_gpu_last_error(c_pfDSRef.ctx(k)) << std::endl; return rcs[k]; }
+            double *M = m_matrix.data();
+            for (int k = 0; k < n; k++) {
+                const std::vector<int32_t> &id = ids[k];
+                const double *part = parts[k].data();
+                if (axes[k] == 0) {                     // all-vs-all: owned rows, cells right of the diagonal + their mirror images
+#pragma omp parallel for schedule(dynamic, 16)
+                    for (int64_t r = 0; r < (int64_t)id.size(); r++) {
+                        const size_t i = (size_t)id[r];
+                        for (size_t j = i + 1; j < nT; j++) { const double v = part[(size_t)r * nT + j]; M[i * nT + j] = v; M[j * nT + i] = v; }
+                    }
+                } else {                                // query modes: owned target columns
+                    const size_t nc = id.size();
+#pragma omp parallel for schedule(static)
+                    for (int64_t qi = 0; qi < (int64_t)nQ; qi++)
+                        for (size_t cidx = 0; cidx < nc; cidx++) M[(size_t)qi * nT + (size_t)id[cidx]] = part[(size_t)qi * nc + cidx];
+                }
+            }
+            pfaai_gpu_get_timings(ctx, &t);
+        }
+        std::printf("JAC Construction    : %10.3f ms; (%d GPU(s); GPU 0: row slabs %.3f ms, dictionaries %.3f ms, tile kernel %.3f ms over %d tiles, D2H %.3f ms)\n",
+                    tm.lap_ms(), n, t.pack_ms, t.dict_ms, t.tile_ms, t.n_tiles, t.d2h_ms);
         return PFAAI_OK;
     }
     // AJI = S / N is fused into the tile kernel (computeAJI, algorithm_impl.hpp:309-322); kept for call compatibility

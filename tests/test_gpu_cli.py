@@ -88,3 +88,28 @@ def test_against_reference_binary_on_synthetic_db(cli, tmp_path):
         r = subprocess.run([ref, db, b, *extra], capture_output=True, text=True, env=dict(os.environ, OMP_NUM_THREADS="4"))
         assert r.returncode == 0, r.stderr[-300:]
         assert open(a, "rb").read() == open(b, "rb").read(), extra
+
+
+def test_multi_gpu_sharded_cli_matches_single_gpu(cli, tmp_path):
+    """--gpus N: output row blocks sharded over N contexts, host scatter + mirror; bytes must equal the 1-GPU CSV.
+    On a single-GPU box the N contexts share the device (--same-device); with >= 2 GPUs both layouts are run."""
+    import torch
+    from parfastaai_b200 import fastaai_db, synth
+    N, P = 900, 3                      # 3 row blocks of 384
+    off, vals = synth.generate(N, P, seed=77)
+    gn, sn = fastaai_db.synthetic_names(N, P)
+    db = str(tmp_path / "syn900.db")
+    fastaai_db.write_db(db, gn, sn, off, vals)
+    qfile = tmp_path / "q.txt"
+    qfile.write_text("\n".join(gn[i] for i in (899, 0, 384, 385, 500)) + "\n")
+    variants = [["--gpus", "2", "--same-device"], ["--gpus", "3", "--same-device"]]
+    if torch.cuda.device_count() >= 2:
+        variants.append(["--gpus", "2"])
+    for extra in ([], ["-q", str(qfile)]):
+        one = str(tmp_path / "one.csv")
+        run(cli, db, one, *extra)
+        for v in variants:
+            many = str(tmp_path / "many.csv")
+            r = run(cli, db, many, *extra, *v)
+            assert open(one, "rb").read() == open(many, "rb").read(), (extra, v)
+            assert f"{v[1]} GPU(s)" in r.stdout
