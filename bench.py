@@ -351,16 +351,39 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    if world > 1:
+        # one-time, untimed: hand every rank its 1/N slice of F in its OWN pinned host memory (as a one-process-per-GPU loader
+        # would hold it): rank 0 uploads F once, broadcasts it, every rank copies its slice back
+        per = (nF + world - 1) // world
+        per += (-per) % 2                                   # 16-byte aligned slices
+        lo, hi = min(nF, rank * per), min(nF, (rank + 1) * per)
+        with torch.cuda.stream(stream):
+            if rank == 0:
+                F_dev.copy_(F_pin.view(torch.uint8), non_blocking=True)
+                Lc_dev.copy_(Lc_pin.view(torch.uint8), non_blocking=True)
+            dist.broadcast(F_dev, src=0)
+            dist.broadcast(Lc_dev, src=0)
+            F_slice_pin = torch.empty(8 * per, dtype=torch.uint8).pin_memory()
+            Lc_pin_r = torch.empty(4 * pf.NTETRA, dtype=torch.uint8).pin_memory()
+            F_slice_pin[:8 * (hi - lo)].copy_(F_dev[8 * lo:8 * hi], non_blocking=True)
+            Lc_pin_r.copy_(Lc_dev, non_blocking=True)
+        stream.synchronize()
+        # all-gather staging: N equal slices (the last one padded) -> the context's F buffer
+        F_gather = torch.empty(8 * per * world, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            del F_pin, F
+        index_resident = True
+
     def replicate_index():
-        """host (rank 0) -> every GPU: one H2D on rank 0, then NCCL broadcast over NVLink / NVSwitch"""
+        """host -> every GPU.  N = 1: pfaai_gpu_upload_index.  N > 1: every rank copies ITS slice of F H2D over its own
+        PCIe link, the slices are all-gathered over NVLink / NVSwitch (NCCL) into every context's index buffer."""
         if world == 1:
             ctx.upload_index(P, G, F, Lc)
             return
-        if rank == 0:
-            F_dev.copy_(F_pin.view(torch.uint8), non_blocking=True)
-            Lc_dev.copy_(Lc_pin.view(torch.uint8), non_blocking=True)
-        dist.broadcast(F_dev, src=0)
-        dist.broadcast(Lc_dev, src=0)
+        F_gather[8 * per * rank:8 * per * (rank + 1)].copy_(F_slice_pin, non_blocking=True)
+        Lc_dev.copy_(Lc_pin_r, non_blocking=True)
+        dist.all_gather_into_tensor(F_gather, F_gather[8 * per * rank:8 * per * (rank + 1)])
+        F_dev.copy_(F_gather[:8 * nF], non_blocking=True)
 
     def step_device():
         ctx.build()
@@ -369,12 +392,8 @@ def main():
     def step_e2e():
         replicate_index()
         ctx.build()
-        if world == 1:
-            # one host-buffer call; M is pinned, so the tile kernel stores the matrix straight into it
-            ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=M)
-        else:
-            ctx.compute_device(pf.ALL_VS_ALL)
-            ctx.download_matrix(M)
+        # one host-buffer call; M is pinned, so the tile kernel stores the (shard's) matrix straight into it
+        ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=M)
 
     def timed(fn, steps, sampler_index=None):
         tile_ms, launches = [], 0
@@ -397,7 +416,7 @@ def main():
         return ms, tile_ms, launches, (clk.summary() if clk else None), tm
 
     # ---- device-resident metric ----
-    with torch.cuda.stream(stream):
+    if world == 1:
         replicate_index()
     for _ in range(args.warmup):
         step_device()
@@ -409,7 +428,7 @@ def main():
             step_e2e()
     ms_e2e, _, _, _, tm_e2e = timed(step_e2e, args.steps)
     e2e_value = pairs_total * args.steps / (ms_e2e / 1e3)
-    h2d = 8 * nF + 4 * pf.NTETRA                      # rank 0 only; the other ranks receive the index over NVLink
+    h2d = 8 * nF + 4 * pf.NTETRA * world              # all ranks together (N > 1: every rank uploads 1/N of F)
     d2h = 8 * my_rows * my_cols                       # bytes all ranks copy back per step
     if world > 1:
         d2h_t = torch.tensor([8.0 * my_rows * my_cols], dtype=torch.float64, device=dev)
@@ -462,7 +481,7 @@ def main():
                                f"SURVEY 8(d) recipe, seed {SEED})",
                    "genomes": G, "scps": P, "postings": nF, "pairs": pairs_total, "mode": "all-vs-all",
                    "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); index replicated "
-                                   f"on every GPU (N>1: one H2D on rank 0 + NCCL broadcast over NVLink inside the e2e region); "
+                                   f"on every GPU (N>1, inside the e2e region: every rank uploads its 1/N slice of F, NCCL all-gather over NVLink); "
                                    f"no data-path collective; every rank copies only its own upper-triangle rows D2H"),
                    "l2_policy": "inputs larger than L2 (F = %.2f GB, matrix = %.2f GB vs 126 MB L2)" % (8 * nF / 1e9, d2h / 1e9),
                    "step": "index build (scan + histogram + radix sort) + row-slab packing + column dictionaries + tile kernel"},

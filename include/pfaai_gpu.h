@@ -126,9 +126,11 @@ int  pfaai_gpu_download_matrix(pfaai_gpu_ctx *ctx, double *aji_matrix);
 /* One call with host buffers: compute + matrix in host memory, plus the optional small-N outputs in the
  * reference's JAC order (initJAC of the mode): jac [n_pairs] (labels, S, N), aji [n_pairs],
  * counts [n_pairs x P] per-SCP intersection counts.  Any output pointer may be NULL.
- * If aji_matrix is page-locked host memory (cudaHostAlloc / cudaHostRegister) and the context is unsharded, the tile
- * kernel stores every cell straight into it (the transfer overlaps the computation; no device copy of the matrix
- * exists afterwards: pfaai_gpu_matrix_dev returns NULL); pageable memory is filled by compute_device + download. */
+ * If aji_matrix is page-locked host memory (cudaHostAlloc / cudaHostRegister) the tile kernel stores every computed
+ * cell straight into it (the transfer overlaps the computation; no device copy of the matrix exists afterwards:
+ * pfaai_gpu_matrix_dev returns NULL); pageable memory is filled by compute_device + download.  Sharded all-vs-all
+ * contexts compute only cells with row < column: with a page-locked matrix the other cells are left UNTOUCHED
+ * (the gathering host overwrites them by mirroring), with pageable memory they are zero. */
 int  pfaai_gpu_compute(pfaai_gpu_ctx *ctx, int mode, const int32_t *qry_ids, int n_qry, unsigned flags,
                        double *aji_matrix, pfaai_jac_t *jac, double *aji, int32_t *counts);
 /* number of JAC entries of a mode (nGenomePairs of the three classes) */

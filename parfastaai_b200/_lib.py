@@ -117,7 +117,7 @@ class PfaaiGpu:
 
     def set_shard(self, shard, n_shards):
         self._check(self._L.pfaai_gpu_set_shard(self._h, shard, n_shards), "set_shard")
-        self._n_shards = n_shards
+        self._n_shards, self._shard = n_shards, shard
 
     def upload_index(self, P, G, F, Lc, T=None):
         F = np.ascontiguousarray(F, dtype=PG_DTYPE)
@@ -192,11 +192,17 @@ class PfaaiGpu:
             shape = (nq, self.G)
         else:
             shape = (nq, self.G - nq)
-        if getattr(self, "_n_shards", 1) > 1:
+        ns = getattr(self, "_n_shards", 1)
+        if ns > 1:
             if want_jac or want_counts:
                 raise PfaaiError("the JAC / counts hooks need an unsharded context")
-            self.compute_device(mode, q, flags)
-            return {"matrix": self.download_matrix(matrix_out), "jac": None, "aji": None, "counts": None}
+            from . import sharding
+            shape = sharding.shard_shape(mode, self.G, nq, self._shard, ns)
+            M = matrix_out if matrix_out is not None else np.zeros(shape, np.float64)
+            if M.shape != tuple(shape):
+                raise ValueError(f"matrix_out must have the shard's shape {shape}")
+            self._check(self._L.pfaai_gpu_compute(self._h, mode, _p(q), nq, flags, _p(M), None, None, None), "compute")
+            return {"matrix": M, "jac": None, "aji": None, "counts": None}
         M = matrix_out if matrix_out is not None else np.empty(shape, np.float64)
         npairs = self.n_pairs(mode, nq)
         jac = np.zeros(npairs, JAC_DTYPE) if want_jac else None

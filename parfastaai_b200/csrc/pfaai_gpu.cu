@@ -501,7 +501,6 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     }
     c->out_rows = m.out_rows; c->out_cols = m.out_cols;
     const size_t ncell = (size_t)m.out_rows * m.out_cols, nk = (size_t)n_rows * n_cols;
-    if (direct_dev && sharded) direct_dev = nullptr;   // compact shards keep zero-filled cells: staged path
     c->out_on_device = (direct_dev == nullptr);
     if (!direct_dev) {
         PF_TRY(ensure(c, c->out, sizeof(double) * ncell));
