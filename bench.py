@@ -462,7 +462,7 @@ def main():
     tile_avg_ms = float(np.mean(tile_ms))
     alg_bytes = int(tm["tile_alg_bytes"])
     achieved = alg_bytes / (tile_avg_ms / 1e3) / 1e9
-    traffic = None
+    traffic = onchip = None
     tp = os.path.join(ROOT, "profiles", "tile_kernel_traffic.json")
     if os.path.exists(tp):
         try:
@@ -470,6 +470,7 @@ def main():
                 tj = json.load(fh)
             if tj.get("genomes") == G and tj.get("scps") == P and world == 1:
                 traffic = tj.get("dram_bytes_per_launch")
+                onchip = tj.get("onchip")
         except Exception:
             traffic = None
 
@@ -494,6 +495,12 @@ def main():
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "alg_bytes_per_launch": alg_bytes, "kernel_ms": tile_avg_ms,
                      "note": "the tile kernel is on-chip (shared-memory lookup / LOP3 issue) bound at this size; see DESIGN.md section 4"},
+        # the limiter of the tile kernel is on-chip: live work rates + the pipe utilisations of the committed
+        # ncu capture of this same configuration (profiles/tile_kernel_traffic.json)
+        "roofline_onchip": {"lookups_per_s": float(tm["n_tiles"]) * 384 * (nF / G) / (tile_avg_ms / 1e3),
+                            "pair_scp_updates_per_s": (my_pairs if world > 1 else pairs_total) * P / (tile_avg_ms / 1e3),
+                            "lookup": "one row tetramer against one 64-column dictionary (LDS.32 + rank + LDS.64 + bit-sliced add)",
+                            "ncu": onchip},
         "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
                       "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"]},
     }
