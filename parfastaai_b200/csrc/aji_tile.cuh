@@ -28,7 +28,7 @@
 //              lane live in TENSOR MEMORY (tcgen05.ld / tcgen05.st, SASS LDTM / STTM): 64 registers per thread are
 //              freed, which is what lets 24 warps (instead of 16) hide the shared-memory latency of the walk.
 //              The division is done with a shared-memory reciprocal table + two FMAs (correctly rounded, see
-//              jaccard_exact) instead of the ~25-instruction fp64 division sequence.
+//              jaccard_fast) instead of the ~25-instruction fp64 division sequence.
 // After the last SCP: AJI = S/N written to the dense output (both triangles in symmetric mode).
 #pragma once
 #include "common.cuh"
@@ -126,14 +126,13 @@ __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.
 // J = c / den, correctly rounded (== IEEE fp64 division, algorithm_impl.hpp:250-254).  Fast path: r = RN(1/den) from the
 // shared-memory table, q = RN(c*r), q' = RN(q + (c - q*den)*r) with the residual exact in one FMA (Markstein); q' equals
 // RN(c/den) for every 0 <= c <= den < 20000 (checked exhaustively in tests/test_division.py with the same operations).
-__device__ __noinline__ double jaccard_div(int c, int den) { return (double)c / (double)den; }
-__device__ __forceinline__ double jaccard_exact(const double *__restrict__ rcp, int c, int den) {
-    if (den < RCP_N && c <= den) {
-        const double r = rcp[den], cd = (double)c, dd = (double)den;
-        const double q = __dmul_rn(cd, r);
-        return __fma_rn(__fma_rn(-q, dd, cd), r, q);
-    }
-    return jaccard_div(c, den);
+__device__ __forceinline__ double lds_f64(uint32_t a) { double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
+__device__ __forceinline__ int lds_s32(uint32_t a) { int v; asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+// rcp32: 32-bit shared address of the reciprocal table; requires 1 <= den < RCP_N and 0 <= c <= den
+__device__ __forceinline__ double jaccard_fast(uint32_t rcp32, int c, int den) {
+    const double r = lds_f64(rcp32 + 8u * (uint32_t)den), cd = (double)c, dd = (double)den;
+    const double q = __dmul_rn(cd, r);
+    return __fma_rn(__fma_rn(-q, dd, cd), r, q);
 }
 
 // carry-save adder on one 32-bit slice: (h, l) = a + b + c
@@ -388,7 +387,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
 #pragma unroll
                     for (int kk = 0; kk < N_PLANES_N; kk++) { const uint32_t tt = Np[kk] & nz; Np[kk] ^= nz; nz = tt; }
                 }
-                const int32_t *ct = colT + (p & 3) * COLS_PER_TILE + cbase;
+                const uint32_t ct32 = smem_u32(colT) + 4u * (uint32_t)((p & 3) * COLS_PER_TILE + cbase);
+                const uint32_t rcp32 = smem_u32(rcp);
                 __syncwarp();
                 // 8 columns at a time: fetch their sums from tensor memory, expand the bit-sliced counts
                 // (nibble -> one bit per byte: (n * 0x00204081) & 0x01010101) while the load is in flight, add J, store back
@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                 for (int g8 = 0; g8 < 4; g8++) {
                     uint32_t sv[16];
                     tmem_ld16(taddr + 16 * g8, sv);
-                    int cnt[8];
+                    int cnt[8], den[8];
 #pragma unroll
                     for (int hf = 0; hf < 2; hf++) {
                         const int g4 = 2 * g8 + hf;
@@ -410,20 +410,35 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                         for (int u = 0; u < 4; u++)
                             cnt[4 * hf + u] = (int)(((lo >> (8 * u)) & 0xffu) | (((hi >> (8 * u)) & 0xffu) << 8));
                     }
-                    tmem_wait_ld(sv);
+                    bool slow = false;   // a denominator beyond the table or c > den (only the query-DB label quirk can do that)
 #pragma unroll
                     for (int u = 0; u < 8; u++) {
-                        const int jj = 8 * g8 + u;
-                        if (prm.counts_out) {
-                            const int col = cbase + jj;
-                            if (row_ok && col < ncol)
-                                prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = cnt[u];
+                        den[u] = max(ta + lds_s32(ct32 + 4u * (uint32_t)(8 * g8 + u)) - cnt[u], 1);
+                        slow |= (den[u] >= RCP_N) | (cnt[u] > den[u]);
+                    }
+                    if (prm.counts_out) {                                   // small-N hook, warp-uniform
+#pragma unroll
+                        for (int u = 0; u < 8; u++) {
+                            const int col = cbase + 8 * g8 + u;
+                            if (row_ok && col < ncol) prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = cnt[u];
                         }
-                        const int den = max(ta + ct[jj] - cnt[u], 1);
-                        // algorithm_impl.hpp:250-254; cnt == 0 adds +0.0
-                        const double sum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]) + jaccard_exact(rcp, cnt[u], den);
-                        sv[2 * u] = (uint32_t)__double2loint(sum);
-                        sv[2 * u + 1] = (uint32_t)__double2hiint(sum);
+                    }
+                    tmem_wait_ld(sv);
+                    // J = c / den, algorithm_impl.hpp:250-254 (c == 0 adds +0.0); one warp-uniform branch per 8 columns
+                    if (!__any_sync(0xffffffffu, slow)) {
+#pragma unroll
+                        for (int u = 0; u < 8; u++) {
+                            const double sum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]) + jaccard_fast(rcp32, cnt[u], den[u]);
+                            sv[2 * u] = (uint32_t)__double2loint(sum);
+                            sv[2 * u + 1] = (uint32_t)__double2hiint(sum);
+                        }
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < 8; u++) {
+                            const double sum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]) + (double)cnt[u] / (double)den[u];
+                            sv[2 * u] = (uint32_t)__double2loint(sum);
+                            sv[2 * u + 1] = (uint32_t)__double2hiint(sum);
+                        }
                     }
                     tmem_st16(taddr + 16 * g8, sv);
                 }
