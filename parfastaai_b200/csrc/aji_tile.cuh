@@ -198,6 +198,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    uint32_t stage32;   // shared-space address of the stage slots (volatile asm: computed once, never rematerialised in the walk loop)
+    asm volatile("{\n.reg .u64 t64;\ncvta.to.shared.u64 t64, %1;\ncvt.u32.u64 %0, t64;\n}" : "=r"(stage32) : "l"(stage_mem));
     // this thread's 64 tensor-memory columns (32 doubles): lane quadrant warp%4, column block warp/4
     const uint32_t taddr = *tmem_slot + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * TMEM_COLS_PER_WARP);
     uint32_t use_par = 0u;          // bit s = wait parity of slot s (flips per completed fill), identical in every thread
@@ -275,11 +277,11 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
             o_cur = prm.ell_off[gi0];
             n_cur = (int)(prm.ell_off[gi0 + 1] - o_cur);
         }
+        // the slabs of a row group lie in stage order, so the walk streams them with ONE running pointer: cur0/cur1 hold the two
+        // chunks of the next step, rp points behind them; only a stage that re-walks its slab (column sub-split) repositions it
         uint4 cur0 = make_uint4(0, 0, 0, 0), cur1 = cur0;
-        if (n_cur > 0) {
-            const uint4 *src = prm.ell + o_cur * 32 + lane;
-            cur0 = __ldg(src); cur1 = __ldg(src + 32);
-        }
+        const uint4 *rp = prm.ell + lane;
+        int64_t o_fetched = -1;                 // chunk index the running pointer has prefetched up to (start of cur0)
         int ta = (row_ok && nst > 0) ? prm.T[(int64_t)st_p(st_cur) * prm.t_ld + ti] : 0;
 
         for (int k = 0; k < nst; k++) {
@@ -300,17 +302,18 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
 
             // ================= walk: bit-sliced accumulation of the row half-lists =================
             {
-                const uint32_t bm = smem_u32(stage_mem) + (uint32_t)slot * STAGE_BYTES;
+                const uint32_t bm = stage32 + (uint32_t)slot * STAGE_BYTES;
                 const uint32_t masks = bm + BM_BYTES;
-                const uint4 *src = prm.ell + o_cur * 32 + lane;
-                const uint4 *src_nxt = prm.ell + o_nxt * 32 + lane;
+                if (n_cur > 0 && o_cur != o_fetched) {
+                    rp = prm.ell + o_cur * 32 + lane;
+                    cur0 = __ldg(rp); cur1 = __ldg(rp + 32);
+                    rp += 64;
+                }
+                o_fetched = o_cur + n_cur;
                 for (int c = 0; c < n_cur; c += 2) {
-                    uint4 nx0 = cur0, nx1 = cur1;
-                    if (c + 2 < n_cur) {
-                        nx0 = __ldg(src + (int64_t)(c + 2) * 32); nx1 = __ldg(src + (int64_t)(c + 3) * 32);
-                    } else if (n_nxt > 0) {
-                        nx0 = __ldg(src_nxt); nx1 = __ldg(src_nxt + 32);
-                    }
+                    // prefetch the next step (possibly the next stage's first chunks; the slab buffer is padded at its end)
+                    const uint4 nx0 = __ldg(rp), nx1 = __ldg(rp + 32);
+                    rp += 64;
                     // 8 lookups -> one carry of weight 8
                     uint32_t f_lo[2], f_hi[2];
 #pragma unroll
@@ -339,7 +342,6 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                     }
                     cur0 = nx0; cur1 = nx1;
                 }
-                if (n_cur == 0 && n_nxt > 0) { cur0 = __ldg(src_nxt); cur1 = __ldg(src_nxt + 32); }
             }
             // ================= release the slot; the last warp to leave refills it =================
             __syncwarp();

@@ -412,7 +412,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     int64_t total_chunks = 0;
     PF_CUDA(c, cudaMemcpyAsync(&total_chunks, ptr<int64_t>(c->ell_off) + nslab, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
-    PF_TRY(ensure(c, c->ell, sizeof(uint4) * 32 * (size_t)total_chunks));
+    PF_TRY(ensure(c, c->ell, sizeof(uint4) * 32 * (size_t)total_chunks + 4096));   // + slack: the walk prefetches one step past the end
     if (total_chunks > 0) {
         k_pack_fill<<<(unsigned)std::min<int64_t>(ceil_div64(ngp, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
             ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), ptr<int32_t>(c->rows), n_rows, n_groups, P, ptr<int64_t>(c->ell_off),
