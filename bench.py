@@ -254,6 +254,8 @@ def main():
     ap.add_argument("--ref-genomes", type=int, default=64, help="size of the reference arm's bounded sample")
     ap.add_argument("--cpu-baseline-genomes", type=int, default=96)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--replicated-build", action="store_true",
+                    help="N>1: every rank builds the whole index (the pre-partitioning path) instead of pfaai_gpu_build_partitioned")
     ap.add_argument("--verify", action="store_true", help="N>1: gather the shards on rank 0 and compare with an unsharded compute")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
@@ -385,13 +387,34 @@ def main():
         dist.all_gather_into_tensor(F_gather, F_gather[8 * per * rank:8 * per * (rank + 1)])
         F_dev.copy_(F_gather[:8 * nF], non_blocking=True)
 
+    partitioned = world > 1 and not args.replicated_build
+    xviews = {}
+    x_ev = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
+
+    def build_index():
+        """N = 1 (or --replicated-build): pfaai_gpu_build.  N > 1: every rank sorts the postings and builds the column
+        dictionaries of ITS OWN row blocks only; the four result buffers are all-gathered in place over NVLink (NCCL)."""
+        if not partitioned:
+            ctx.build()
+            return
+        ctx.build_partitioned()
+        x_ev[0].record(stream)
+        for ptr, chunk, _used in ctx.exchange_buffers():
+            key = (ptr, chunk)
+            if key not in xviews:
+                xviews[key] = torch.as_tensor(_DevMem(ptr, chunk * world), device=dev)
+            buf = xviews[key]
+            dist.all_gather_into_tensor(buf, buf[chunk * rank:chunk * (rank + 1)])
+        x_ev[1].record(stream)
+        ctx.finish_partitioned()
+
     def step_device():
-        ctx.build()
+        build_index()
         ctx.compute_device(pf.ALL_VS_ALL)
 
     def step_e2e():
         replicate_index()
-        ctx.build()
+        build_index()
         # one host-buffer call; M is pinned, so the tile kernel stores the (shard's) matrix straight into it
         ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=M)
 
@@ -418,9 +441,19 @@ def main():
     # ---- device-resident metric ----
     if world == 1:
         replicate_index()
+    if partitioned:
+        # untimed, once: size the shards' dictionary chunks to what this database needs (max over the ranks + 2 %), so that
+        # the in-place all-gather of the timed steps moves almost no padding
+        with torch.cuda.stream(stream):
+            ctx.build_partitioned()
+            used = torch.tensor([float(ctx.exchange_buffers()[0][2])], dtype=torch.float64, device=dev)
+            dist.all_reduce(used, op=dist.ReduceOp.MAX)
+            ctx.set_partition_chunk(int(used.item() * 1.02) + 4096)
     for _ in range(args.warmup):
         step_device()
     ms_dev, tile_ms, launches, clocks, tm = timed(step_device, args.steps, sampler_index=local_rank)
+    exchange_ms = max_over_ranks(x_ev[0].elapsed_time(x_ev[1])) if partitioned else 0.0
+    exchange_bytes = sum(ch for _p, ch, _u in ctx.exchange_buffers()) * world if partitioned else 0
     value = pairs_total * args.steps / (ms_dev / 1e3)
     # ---- end to end through the host-buffer C-ABI ----
     for _ in range(min(args.warmup, 2)):
@@ -454,6 +487,7 @@ def main():
             dist.send(torch.from_numpy(M).to(dev), dst=0)
         if rank == 0:
             ctx.set_shard(0, 1)
+            ctx.build()                                   # the replicated, unsharded path on the same F
             ref = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
             ctx.set_shard(rank, world)
             verify = {"max_abs_diff_vs_unsharded": float(np.abs(full - ref).max()), "identical": bool(np.array_equal(full, ref))}
@@ -481,11 +515,15 @@ def main():
         "config": {"workload": f"synthetic {G} genomes x {P} SCPs all-vs-all (BASELINE config {'4' if G == 10000 else '5' if G == 50000 else 'custom'}; "
                                f"SURVEY 8(d) recipe, seed {SEED})",
                    "genomes": G, "scps": P, "postings": nF, "pairs": pairs_total, "mode": "all-vs-all",
-                   "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); index replicated "
+                   "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); F replicated "
                                    f"on every GPU (N>1, inside the e2e region: every rank uploads its 1/N slice of F, NCCL all-gather over NVLink); "
-                                   f"no data-path collective; every rank copies only its own upper-triangle rows D2H"),
+                                   + ("partitioned index build: every rank sorts / builds the column dictionaries of its own row blocks, "
+                                      "the dictionaries are all-gathered over NVLink (NCCL, in place); " if partitioned else
+                                      "index build replicated on every rank; ") +
+                                   f"no reduction collective; every rank stores only its own upper-triangle rows into pinned host memory"),
                    "l2_policy": "inputs larger than L2 (F = %.2f GB, matrix = %.2f GB vs 126 MB L2)" % (8 * nF / 1e9, d2h / 1e9),
-                   "step": "index build (scan + histogram + radix sort) + row-slab packing + column dictionaries + tile kernel"},
+                   "step": "index build (scan + histogram + radix sort) + row-slab packing + column dictionaries"
+                           + (" + dictionary all-gather" if partitioned else "") + " + tile kernel"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
@@ -502,6 +540,7 @@ def main():
                             "lookup": "one row tetramer against one 64-column dictionary (LDS.32 + rank + LDS.64 + bit-sliced add)",
                             "ncu": onchip},
         "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
+                      "exchange": exchange_ms, "exchange_bytes_per_rank": exchange_bytes,
                       "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"]},
     }
 

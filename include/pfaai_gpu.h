@@ -105,6 +105,36 @@ int  pfaai_gpu_index_device_buffers(pfaai_gpu_ctx *ctx, int n_proteins, int n_ge
 /* Device build: Lp (exclusive scan), per-(genome,SCP) segment histogram, T, and the genome-major
  * postings by a stable LSD radix sort of the postings on (genome, SCP). */
 int  pfaai_gpu_build(pfaai_gpu_ctx *ctx);
+/* Partitioned build for sharded ALL_VS_ALL contexts (the per-GPU share of the index work shrinks with the
+ * number of GPUs instead of being repeated on every one).  Every shard still receives the whole F / Lc, but
+ *   pfaai_gpu_build_partitioned   sorts only the postings of the genomes of ITS OWN row blocks (order-preserving compaction of F,
+ *                                 then the same radix sort on 1/n of the items) and builds the column-block dictionaries of those
+ *                                 genomes into its chunk of four exchange buffers (dictionary blobs, stage descriptors, column T
+ *                                 values, stage ranges).  Chunk sizes depend on (n_genomes, n_proteins, nF, n_shards) only, so
+ *                                 all shards agree on the layout without communicating;
+ *   pfaai_gpu_exchange_buffers    describes the buffers: shard s owns bytes [s*chunk, s*chunk + used) of each.  The caller
+ *                                 all-gathers them in place across the shards' contexts -- NCCL over NVLink for one process
+ *                                 per GPU (bench.py), or pfaai_gpu_exchange_local for contexts that live in one process
+ *                                 (peer copies; the C++ driver);
+ *   pfaai_gpu_finish_partitioned  declares the exchange done; pfaai_gpu_compute*(PFAAI_ALL_VS_ALL) then skips its own
+ *                                 dictionary construction.  Results are identical to the replicated pfaai_gpu_build path.
+ * After a partitioned build the T / seg parity hooks of pfaai_gpu_get_arrays cover this shard's genomes only. */
+typedef struct {
+    void   *buf_dev[4];      /* device pointers: dictionary blobs, stage descriptors, column T values, stage ranges */
+    int64_t chunk_bytes[4];  /* size of one shard's chunk of each buffer (identical on every shard)              */
+    int64_t used_bytes[4];   /* leading bytes of THIS shard's chunk that carry data                              */
+    int32_t shard, n_shards;
+} pfaai_exchange_t;
+int  pfaai_gpu_build_partitioned(pfaai_gpu_ctx *ctx);
+/* Optional: the size of one shard's dictionary-blob chunk for the following partitioned builds (0 = the default upper
+ * bound, which is safe but about twice what is used).  A caller that rebuilds the same database repeatedly takes the
+ * maximum of used_bytes[0] over the shards after the first build and sets it (plus a margin) on EVERY shard, so that the
+ * in-place all-gather moves little padding; a shard whose dictionaries do not fit fails the build with PFAAI_ERR_CONSTRUCT. */
+int  pfaai_gpu_set_partition_chunk(pfaai_gpu_ctx *ctx, int64_t blob_chunk_bytes);
+int  pfaai_gpu_exchange_buffers(pfaai_gpu_ctx *ctx, pfaai_exchange_t *out);
+int  pfaai_gpu_finish_partitioned(pfaai_gpu_ctx *ctx);
+/* exchange + finish for n_shards contexts of THIS process (any mix of devices), after each ran build_partitioned */
+int  pfaai_gpu_exchange_local(pfaai_gpu_ctx **ctxs, int n_shards);
 /* Parity hooks (any pointer may be NULL): Lc/Lp [160000], T [P x G], and the genome-major index:
  * seg_off [G*P+1] (int64, segment g*P+p) and seg_vals [nF] (tetramers, ascending inside a segment). */
 int  pfaai_gpu_get_arrays(pfaai_gpu_ctx *ctx, int32_t *Lc, int32_t *Lp, int32_t *T,

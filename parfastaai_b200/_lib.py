@@ -27,6 +27,8 @@ EXPORTS = [
     "pfaai_gpu_upload_index", "pfaai_gpu_build", "pfaai_gpu_get_arrays", "pfaai_gpu_compute_device",
     "pfaai_gpu_matrix_shape", "pfaai_gpu_matrix_dev", "pfaai_gpu_download_matrix", "pfaai_gpu_compute",
     "pfaai_gpu_n_pairs", "pfaai_gpu_get_timings", "pfaai_gpu_shard_layout", "pfaai_gpu_index_device_buffers",
+    "pfaai_gpu_build_partitioned", "pfaai_gpu_exchange_buffers", "pfaai_gpu_finish_partitioned", "pfaai_gpu_exchange_local",
+    "pfaai_gpu_set_partition_chunk",
 ]
 
 
@@ -37,6 +39,12 @@ class Timings(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class Exchange(C.Structure):
+    """pfaai_exchange_t: the four buffers a partitioned build leaves to be all-gathered across the shards."""
+    _fields_ = [("buf_dev", C.c_void_p * 4), ("chunk_bytes", C.c_int64 * 4), ("used_bytes", C.c_int64 * 4),
+                ("shard", C.c_int32), ("n_shards", C.c_int32)]
 
 
 _lib = None
@@ -73,6 +81,11 @@ def load():
     L.pfaai_gpu_get_timings.argtypes = [vp, C.POINTER(Timings)]
     L.pfaai_gpu_shard_layout.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(i64), vp]
     L.pfaai_gpu_index_device_buffers.argtypes = [vp, i32, i32, i64, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    L.pfaai_gpu_build_partitioned.argtypes = [vp]
+    L.pfaai_gpu_exchange_buffers.argtypes = [vp, C.POINTER(Exchange)]
+    L.pfaai_gpu_finish_partitioned.argtypes = [vp]
+    L.pfaai_gpu_exchange_local.argtypes = [C.POINTER(vp), i32]
+    L.pfaai_gpu_set_partition_chunk.argtypes = [vp, i64]
     _lib = L
     return L
 
@@ -149,6 +162,31 @@ class PfaaiGpu:
 
     def build(self):
         self._check(self._L.pfaai_gpu_build(self._h), "build")
+
+    def build_partitioned(self):
+        """Sharded all-vs-all: index part + dictionaries of this shard's own row blocks only (exchange, then finish)."""
+        self._check(self._L.pfaai_gpu_build_partitioned(self._h), "build_partitioned")
+
+    def exchange_buffers(self):
+        """-> list of (device pointer, chunk bytes, used bytes) for the four buffers to all-gather in place."""
+        x = Exchange()
+        self._check(self._L.pfaai_gpu_exchange_buffers(self._h, C.byref(x)), "exchange_buffers")
+        return [(x.buf_dev[k], int(x.chunk_bytes[k]), int(x.used_bytes[k])) for k in range(4)]
+
+    def set_partition_chunk(self, blob_chunk_bytes):
+        self._check(self._L.pfaai_gpu_set_partition_chunk(self._h, int(blob_chunk_bytes)), "set_partition_chunk")
+
+    def finish_partitioned(self):
+        self._check(self._L.pfaai_gpu_finish_partitioned(self._h), "finish_partitioned")
+
+    @staticmethod
+    def exchange_local(ctxs):
+        """Exchange + finish between the shards' contexts of this process (peer copies)."""
+        L = load()
+        arr = (C.c_void_p * len(ctxs))(*[c._h for c in ctxs])
+        rc = L.pfaai_gpu_exchange_local(arr, len(ctxs))
+        if rc != 0:
+            raise PfaaiError(f"exchange_local rc={rc}: " + "; ".join(L.pfaai_gpu_last_error(c._h).decode() for c in ctxs))
 
     def get_arrays(self, want_lists=True):
         Lc = np.zeros(NTETRA, np.int32)

@@ -46,9 +46,9 @@ struct TileParams {
     const int32_t *cols;       // [n_cols]
     int n_cols;
     const StageDesc *stages;
-    const int64_t *stage_begin;   // [n_col_blocks + 1]
+    const int64_t *stage_rng;  // [n_slots][2]: first / one-past-last stage of the column block stored in slot s
     const unsigned char *blob;
-    const int32_t *colT;       // [n_col_blocks * P * 64]
+    const int32_t *colT;       // [n_slots * P * 64]; slot of a column block = tiles[].w (== J in an unpartitioned context)
     const int32_t *T;          // [P x t_ld]
     int t_ld, P;
     // output
@@ -59,7 +59,7 @@ struct TileParams {
     double *S_out;             // optional hooks, [n_rows x n_cols]
     int32_t *N_out;
     int32_t *counts_out;       // optional, [n_rows x n_cols x P]
-    const int4 *tiles;         // (row block I, col block J, first output row of block I in this shard's matrix, -)
+    const int4 *tiles;         // (row block I, col block J, first output row of block I in this shard's matrix, slot of J)
     int n_tiles;
 };
 
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
     const uint32_t taddr = *tmem_slot + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * TMEM_COLS_PER_WARP);
     uint32_t use_par = 0u;          // bit s = wait parity of slot s (flips per completed fill), identical in every thread
 
-    auto issue = [&](const uint4 st, int slot, int cb) {
+    auto issue = [&](const uint4 st, int slot, int cslot) {
         // runs in ONE thread: refill `slot` with the blob of stage `st` (+ the column T values on an SCP's first stage)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         const uint32_t extra = st_first(st.w) ? COLS_PER_TILE * 4u : 0u;
@@ -212,15 +212,15 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         mbar_expect_tx(&full[slot], st.z + extra);
         bulk_g2s(stage_mem + (size_t)slot * STAGE_BYTES, prm.blob + off, st.z, &full[slot]);
         if (extra)
-            bulk_g2s(colT + (st_p(st.w) & 3) * COLS_PER_TILE, prm.colT + ((int64_t)cb * P + st_p(st.w)) * COLS_PER_TILE, extra,
+            bulk_g2s(colT + (st_p(st.w) & 3) * COLS_PER_TILE, prm.colT + ((int64_t)cslot * P + st_p(st.w)) * COLS_PER_TILE, extra,
                      &full[slot]);
     };
 
     for (int t = blockIdx.x; t < prm.n_tiles; t += gridDim.x) {
         const int4 tile = prm.tiles[t];
-        const int cb = tile.y;
-        const int64_t sb = prm.stage_begin[cb];
-        const int nst = (int)(prm.stage_begin[cb + 1] - sb);
+        const int cb = tile.y, cslot = tile.w;
+        const int64_t sb = prm.stage_rng[2 * cslot];
+        const int nst = (int)(prm.stage_rng[2 * cslot + 1] - sb);
         const int group = tile.x * TILE_WARPS + warp;
         const bool group_ok = group < prm.n_groups;
         const int row = group * ROWS_PER_WARP + r;
@@ -231,8 +231,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         const int ncol = min(COLS_PER_TILE, prm.n_cols - j0);
 
         if (tid == 0) {
-            if (nst > 0) issue(load_stage(prm.stages + sb), 0, cb);
-            if (nst > 1) issue(load_stage(prm.stages + sb + 1), 1, cb);
+            if (nst > 0) issue(load_stage(prm.stages + sb), 0, cslot);
+            if (nst > 1) issue(load_stage(prm.stages + sb + 1), 1, cslot);
         }
         if (tid < COLS_PER_TILE) col_g[tid] = (tid < ncol) ? prm.cols[j0 + tid] : -1;
         __syncthreads();
@@ -349,7 +349,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                 const uint32_t old = atom_add_acq_rel_smem(&done[slot], 1u);
                 if (old == TILE_WARPS - 1) {
                     done[slot] = 0u;
-                    if (k + 2 < nst) issue(st_n2, slot, cb);
+                    if (k + 2 < nst) issue(st_n2, slot, cslot);
                 }
             }
 

@@ -107,9 +107,48 @@ __device__ __forceinline__ int tetramer_of(const int64_t *__restrict__ Lp, int l
     return lo;
 }
 
+// Ownership of a genome in a partitioned build (pfaai_gpu_build_partitioned): owner[genome >> OWN_SHIFT] == shard.  The table has
+// one byte per 128 genomes (128 divides the row-block height, so it can express any assignment of row blocks to shards).
+constexpr int OWN_SHIFT = 7;
+static_assert(TILE_ROWS % (1 << OWN_SHIFT) == 0, "row blocks must be whole ownership granules");
+
+// Partitioned build, pass 1: per 512-posting warp chunk, the number of postings whose genome this shard owns (the
+// order-preserving compaction offsets of pass 2 are the exclusive scan of these counts); also the (genome, SCP)
+// segment histogram of the owned postings.
+__global__ void __launch_bounds__(MI_THREADS) k_count_owned(const pfaai_pg_t *__restrict__ F, int64_t nF, int P, int G,
+                                                             const uint8_t *__restrict__ owner, int shard,
+                                                             int32_t *__restrict__ warp_cnt, uint32_t *__restrict__ seg_len,
+                                                             int *__restrict__ err) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * MI_THREADS + threadIdx.x) >> 5;
+    const int64_t w0 = warp * (32 * MI_ITEMS);
+    if (w0 >= nF) return;
+    int cnt = 0;
+#pragma unroll 4
+    for (int k = 0; k < MI_ITEMS; k++) {
+        const int64_t i = w0 + k * 32 + lane;
+        bool own = false;
+        if (i < nF) {
+            const pfaai_pg_t e = F[i];
+            if ((unsigned)e.protein >= (unsigned)P || (unsigned)e.genome >= (unsigned)G) *err = 1;
+            else if (__ldg(owner + (e.genome >> OWN_SHIFT)) == (uint8_t)shard) {
+                own = true;
+                atomicAdd(&seg_len[(uint32_t)e.genome * (uint32_t)P + (uint32_t)e.protein], 1u);
+            }
+        }
+        cnt += __popc(__ballot_sync(0xffffffffu, own));
+    }
+    if (lane == 0) warp_cnt[warp] = cnt;
+}
+
+// owner == NULL: every posting becomes an item at its own index and is counted in seg_len (replicated build).
+// owner != NULL: only the postings of genomes owned by `shard` become items, compacted in input order from warp_off[warp]
+// on (pass 2 of the partitioned build; seg_len was filled by k_count_owned).
 __global__ void __launch_bounds__(MI_THREADS) k_make_items(const pfaai_pg_t *__restrict__ F, const int64_t *__restrict__ Lp,
                                                             int64_t nF, int P, int G, uint64_t *__restrict__ items,
-                                                            uint32_t *__restrict__ seg_len, int *__restrict__ err) {
+                                                            uint32_t *__restrict__ seg_len, int *__restrict__ err,
+                                                            const uint8_t *__restrict__ owner, int shard,
+                                                            const int64_t *__restrict__ warp_off) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * MI_THREADS + threadIdx.x) >> 5;
     const int64_t w0 = warp * (32 * MI_ITEMS);
@@ -124,6 +163,8 @@ __global__ void __launch_bounds__(MI_THREADS) k_make_items(const pfaai_pg_t *__r
     const int64_t bnd = Lp[tb];                                       // start of block t0+1+lane (Lp[NTETRA] = nF)
     const bool local = __shfl_sync(0xffffffffu, bnd, 31) > last || t0 + 32 >= NTETRA;
     const int t_hi = local ? 0 : tetramer_of(Lp, t0, NTETRA - 1, last);
+    int64_t dst = owner ? warp_off[warp] : 0;
+    const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll 4
     for (int k = 0; k < MI_ITEMS; k++) {
         const int64_t i = w0 + k * 32 + lane;
@@ -139,6 +180,22 @@ __global__ void __launch_bounds__(MI_THREADS) k_make_items(const pfaai_pg_t *__r
             t = min(t0 + pos, NTETRA - 1);
         } else {
             t = valid ? tetramer_of(Lp, t0, t_hi, i) : 0;
+        }
+        if (owner) {
+            bool own = false;
+            uint32_t seg = 0u;
+            if (valid) {
+                const pfaai_pg_t e = F[i];
+                if ((unsigned)e.protein < (unsigned)P && (unsigned)e.genome < (unsigned)G &&
+                    __ldg(owner + (e.genome >> OWN_SHIFT)) == (uint8_t)shard) {
+                    own = true;
+                    seg = (uint32_t)e.genome * (uint32_t)P + (uint32_t)e.protein;
+                }
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, own);
+            if (own) items[dst + __popc(bal & lt_mask)] = ((uint64_t)seg << TET_BITS) | (uint32_t)t;
+            dst += __popc(bal);
+            continue;
         }
         if (!valid) continue;
         const pfaai_pg_t e = F[i];

@@ -34,7 +34,14 @@ struct Ctx {
     DevBuf F, Lc, Lp64, Lp32, T, seg_len, seg_off, itemsA, itemsB, vals, tile_sums, block_hist, block_base, flags;
     // compute
     DevBuf rows, row_t, cols, col_t, ell_nch, ell_off, ell, tiles, out, S_out, N_out, counts_out;
-    DevBuf nsub, sub, colT, blob, stage_off, stages, stage_begin;
+    DevBuf nsub, sub, colT, blob, stage_off, stages, stage_rng;
+    // partitioned build (pfaai_gpu_build_partitioned): this shard built the index part / dictionaries of its own row blocks
+    DevBuf owner_tbl, warp_cnt, warp_off, cb_list;
+    bool partitioned = false, dict_ready = false;
+    int64_t nF_owned = 0;
+    int64_t slot_cap = 0;                 // dictionary slots (column blocks) per shard chunk
+    int64_t blob_chunk_hint = 0;          // pfaai_gpu_set_partition_chunk: agreed size of a shard's blob chunk (0: default bound)
+    int64_t chunk_bytes[4] = {}, used_bytes[4] = {};   // exchange buffers: blob, stages, colT, stage_rng
     int64_t out_rows = 0, out_cols = 0;
     int last_mode = -1;
     bool out_on_device = true;          // false: the last compute stored straight into the caller's pinned matrix
@@ -71,6 +78,13 @@ template <typename T> static inline T *ptr(DevBuf &b) { return reinterpret_cast<
 
 enum { EV_H2D0, EV_H2D1, EV_B0, EV_S0, EV_S1, EV_B1, EV_P0, EV_P1, EV_T0, EV_T1, EV_D0, EV_D1, EV_K0, EV_K1 };
 
+static inline int fold_owner(int block, int n_shards) {   // pfaai_gpu_set_shard: block b belongs to shard f(b mod 2n)
+    const int f = block % (2 * n_shards);
+    return f < n_shards ? f : 2 * n_shards - 1 - f;
+}
+constexpr int RB_CBS = TILE_ROWS / COLS_PER_TILE;          // column blocks per row block
+static_assert(TILE_ROWS % COLS_PER_TILE == 0, "a row block must be a whole number of column blocks");
+
 static float ev_ms(Ctx *c, int a, int b) {
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]) != cudaSuccess) { cudaGetLastError(); return 0.f; }
@@ -96,6 +110,115 @@ static int read_flags(Ctx *c, int *flags_host /*[4]*/) {
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
     return PFAAI_OK;
 }
+
+// K1-K3 + K2b.  partitioned: only the postings of the genomes this shard owns (the genomes of its row blocks) are turned into
+// sort items (order-preserving compaction in two passes over F), so histogram atomics, sort and the genome-major lists shrink
+// by the number of shards; seg_off / T keep their global indexing (non-owned segments are empty, non-owned T columns 0).
+static int build_internal(Ctx *c, bool partitioned) {
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (!c->uploaded) { set_error(c, "build: no index uploaded"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    const int P = c->P, G = c->G;
+    const int64_t nF = c->nF, nseg = (int64_t)P * G;
+    c->launches = 0;
+    c->built = false; c->partitioned = false; c->dict_ready = false;
+    PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
+    PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->seg_len, sizeof(uint32_t) * (size_t)nseg));
+    PF_TRY(ensure(c, c->seg_off, sizeof(int64_t) * (size_t)(nseg + 1)));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B0], c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->flags.p, 0, 64, c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->seg_len.p, 0, sizeof(uint32_t) * (size_t)nseg, c->stream));
+    // K1: Lp = exclusive scan of Lc (parallelPrefixSum)
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->Lc), NTETRA, ptr<int64_t>(c->Lp64), ptr<int32_t>(c->Lp32)));
+    // K2a + K3: sort items and the (genome, SCP) histogram
+    int64_t n_items = nF;
+    const unsigned mi_grid = (unsigned)ceil_div64(nF, (int64_t)MI_THREADS * MI_ITEMS);
+    if (partitioned) {
+        const int ngran = (G + (1 << OWN_SHIFT) - 1) >> OWN_SHIFT;
+        std::vector<uint8_t> own(ngran);
+        for (int i = 0; i < ngran; i++) own[i] = (uint8_t)fold_owner((int)(((int64_t)i << OWN_SHIFT) / TILE_ROWS), c->n_shards);
+        PF_TRY(ensure(c, c->owner_tbl, (size_t)ngran));
+        PF_CUDA(c, cudaMemcpyAsync(c->owner_tbl.p, own.data(), (size_t)ngran, cudaMemcpyHostToDevice, c->stream));
+        n_items = 0;
+        if (nF > 0) {
+            const int64_t nwarp = ceil_div64(nF, 32 * MI_ITEMS);
+            PF_TRY(ensure(c, c->warp_cnt, sizeof(int32_t) * (size_t)nwarp));
+            PF_TRY(ensure(c, c->warp_off, sizeof(int64_t) * (size_t)(nwarp + 1)));
+            k_count_owned<<<mi_grid, MI_THREADS, 0, c->stream>>>(ptr<pfaai_pg_t>(c->F), nF, P, G, ptr<uint8_t>(c->owner_tbl), c->shard,
+                                                                 ptr<int32_t>(c->warp_cnt), ptr<uint32_t>(c->seg_len), ptr<int>(c->flags));
+            PF_LAUNCH_CHECK(c);
+            PF_TRY(launch_scan(c, ptr<int32_t>(c->warp_cnt), nwarp, ptr<int64_t>(c->warp_off), nullptr));
+            PF_CUDA(c, cudaMemcpyAsync(&n_items, ptr<int64_t>(c->warp_off) + nwarp, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+            PF_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+    }
+    c->nF_owned = n_items;
+    PF_TRY(ensure(c, c->itemsA, sizeof(uint64_t) * (size_t)n_items));
+    PF_TRY(ensure(c, c->itemsB, sizeof(uint64_t) * (size_t)n_items));
+    PF_TRY(ensure(c, c->vals, sizeof(uint32_t) * (size_t)n_items));
+    if (nF > 0) {
+        k_make_items<<<mi_grid, MI_THREADS, 0, c->stream>>>(
+            ptr<pfaai_pg_t>(c->F), ptr<int64_t>(c->Lp64), nF, P, G, ptr<uint64_t>(c->itemsA), ptr<uint32_t>(c->seg_len),
+            ptr<int>(c->flags), partitioned ? ptr<uint8_t>(c->owner_tbl) : nullptr, c->shard,
+            partitioned ? ptr<int64_t>(c->warp_off) : nullptr);
+        PF_LAUNCH_CHECK(c);
+    }
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->seg_len), nseg, ptr<int64_t>(c->seg_off), nullptr));
+    k_transpose_t<<<(unsigned)ceil_div64(nseg, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->seg_len), P, G,
+                                                                          c->host_T ? nullptr : ptr<int32_t>(c->T),
+                                                                          ptr<int>(c->flags) + 1);
+    PF_LAUNCH_CHECK(c);
+    // K2b: stable LSD radix sort on (genome*P + protein), one onesweep kernel per 8-bit digit; the digit histograms
+    // of all passes come from the segment histogram; the last pass emits the tetramers only
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_S0], c->stream));
+    if (n_items > 0) {
+        int keybits = 1;
+        while (keybits < 31 && ((int64_t)1 << keybits) < nseg) keybits++;
+        const int passes = (keybits + 7) / 8;
+        const int64_t n_tiles = ceil_div64(n_items, OS_TILE);
+        const size_t control_bytes = sizeof(uint64_t) * (size_t)(8 + n_tiles * RS_RADIX);
+        PF_TRY(ensure(c, c->block_hist, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX));
+        PF_TRY(ensure(c, c->block_base, control_bytes));
+        PF_CUDA(c, cudaMemsetAsync(c->block_hist.p, 0, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX, c->stream));
+        k_digit_hist<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 256), (int64_t)c->sm_count * 2), 256, 0, c->stream>>>(
+            ptr<uint32_t>(c->seg_len), nseg, passes, ptr<unsigned long long>(c->block_hist));
+        PF_LAUNCH_CHECK(c);
+        k_digit_scan<<<passes, RS_RADIX, 0, c->stream>>>(ptr<unsigned long long>(c->block_hist));
+        PF_LAUNCH_CHECK(c);
+        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
+        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
+        uint64_t *src = ptr<uint64_t>(c->itemsA), *dst = ptr<uint64_t>(c->itemsB);
+        for (int pass = 0; pass < passes; pass++) {
+            const int shift = TET_BITS + 8 * pass;
+            const unsigned long long *base = ptr<unsigned long long>(c->block_hist) + (size_t)pass * RS_RADIX;
+            PF_CUDA(c, cudaMemsetAsync(c->block_base.p, 0, control_bytes, c->stream));
+            if (pass == passes - 1)
+                k_onesweep<true><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, n_items, shift, base, ptr<uint64_t>(c->block_base),
+                                                                                        nullptr, ptr<uint32_t>(c->vals));
+            else
+                k_onesweep<false><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, n_items, shift, base, ptr<uint64_t>(c->block_base),
+                                                                                         dst, nullptr);
+            PF_LAUNCH_CHECK(c);
+            std::swap(src, dst);
+        }
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_S1], c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B1], c->stream));
+    int fl[4];
+    PF_TRY(read_flags(c, fl));
+    if (fl[0] == 2) { set_error(c, "build: sum(Lc) != |F|"); return PFAAI_ERR_CONSTRUCT; }
+    if (fl[0]) { set_error(c, "build: posting with protein/genome id out of range"); return PFAAI_ERR_CONSTRUCT; }
+    c->max_len = fl[1];
+    c->tm.build_ms = ev_ms(c, EV_B0, EV_B1);
+    c->tm.sort_ms = ev_ms(c, EV_S0, EV_S1);
+    c->tm.n_launches = c->launches;
+    c->built = true;
+    c->partitioned = partitioned;
+    return PFAAI_OK;
+}
+
+static int build_own_dictionaries(Ctx *c);
 
 }  // namespace pfaai
 
@@ -143,7 +266,8 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
     DevBuf *all[] = {&c->F, &c->Lc, &c->Lp64, &c->Lp32, &c->T, &c->seg_len, &c->seg_off, &c->itemsA, &c->itemsB, &c->vals,
                      &c->tile_sums, &c->block_hist, &c->block_base, &c->flags, &c->rows, &c->row_t, &c->cols, &c->col_t,
                      &c->ell_nch, &c->ell_off, &c->ell, &c->tiles, &c->out, &c->S_out, &c->N_out, &c->counts_out,
-                     &c->nsub, &c->sub, &c->colT, &c->blob, &c->stage_off, &c->stages, &c->stage_begin};
+                     &c->nsub, &c->sub, &c->colT, &c->blob, &c->stage_off, &c->stages, &c->stage_rng,
+                     &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
@@ -212,83 +336,74 @@ int pfaai_gpu_index_device_buffers(pfaai_gpu_ctx *h, int P, int G, int64_t nF, i
     return PFAAI_OK;
 }
 
-int pfaai_gpu_build(pfaai_gpu_ctx *h) {
+int pfaai_gpu_build(pfaai_gpu_ctx *h) { return build_internal(reinterpret_cast<Ctx *>(h), false); }
+
+int pfaai_gpu_build_partitioned(pfaai_gpu_ctx *h) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     if (!c) return PFAAI_ERR_CONSTRUCT;
-    if (!c->uploaded) { set_error(c, "build: no index uploaded"); return PFAAI_ERR_CONSTRUCT; }
-    PF_CUDA(c, cudaSetDevice(c->device));
-    const int P = c->P, G = c->G;
-    const int64_t nF = c->nF, nseg = (int64_t)P * G;
-    c->launches = 0;
-    PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
-    PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
-    PF_TRY(ensure(c, c->seg_len, sizeof(uint32_t) * (size_t)nseg));
-    PF_TRY(ensure(c, c->seg_off, sizeof(int64_t) * (size_t)(nseg + 1)));
-    PF_TRY(ensure(c, c->itemsA, sizeof(uint64_t) * (size_t)nF));
-    PF_TRY(ensure(c, c->itemsB, sizeof(uint64_t) * (size_t)nF));
-    PF_TRY(ensure(c, c->vals, sizeof(uint32_t) * (size_t)nF));
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_B0], c->stream));
-    PF_CUDA(c, cudaMemsetAsync(c->flags.p, 0, 64, c->stream));
-    PF_CUDA(c, cudaMemsetAsync(c->seg_len.p, 0, sizeof(uint32_t) * (size_t)nseg, c->stream));
-    // K1: Lp = exclusive scan of Lc (parallelPrefixSum)
-    PF_TRY(launch_scan(c, ptr<int32_t>(c->Lc), NTETRA, ptr<int64_t>(c->Lp64), ptr<int32_t>(c->Lp32)));
-    // K2a + K3: sort items and the (genome, SCP) histogram
-    if (nF > 0) {
-        k_make_items<<<(unsigned)ceil_div64(nF, (int64_t)MI_THREADS * MI_ITEMS), MI_THREADS, 0, c->stream>>>(
-            ptr<pfaai_pg_t>(c->F), ptr<int64_t>(c->Lp64), nF, P, G, ptr<uint64_t>(c->itemsA), ptr<uint32_t>(c->seg_len),
-            ptr<int>(c->flags));
-        PF_LAUNCH_CHECK(c);
+    if (c->n_shards < 2) { set_error(c, "build_partitioned: needs a sharded context (pfaai_gpu_set_shard with n_shards > 1)"); return PFAAI_ERR_CONSTRUCT; }
+    if (c->host_T) { set_error(c, "build_partitioned: all-vs-all only (T is derived on the device)"); return PFAAI_ERR_CONSTRUCT; }
+    PF_TRY(build_internal(c, true));
+    PF_TRY(build_own_dictionaries(c));
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_set_partition_chunk(pfaai_gpu_ctx *h, int64_t blob_chunk_bytes) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || blob_chunk_bytes < 0) { set_error(c, "set_partition_chunk: bad size"); return PFAAI_ERR_CONSTRUCT; }
+    c->blob_chunk_hint = blob_chunk_bytes;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_exchange_buffers(pfaai_gpu_ctx *h, pfaai_exchange_t *x) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !x || !c->partitioned) { set_error(c, "exchange_buffers: no partitioned build"); return PFAAI_ERR_CONSTRUCT; }
+    void *bufs[4] = {c->blob.p, c->stages.p, c->colT.p, c->stage_rng.p};
+    for (int k = 0; k < 4; k++) { x->buf_dev[k] = bufs[k]; x->chunk_bytes[k] = c->chunk_bytes[k]; x->used_bytes[k] = c->used_bytes[k]; }
+    x->shard = c->shard; x->n_shards = c->n_shards;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_finish_partitioned(pfaai_gpu_ctx *h) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !c->partitioned || !c->built) { set_error(c, "finish_partitioned: no partitioned build"); return PFAAI_ERR_CONSTRUCT; }
+    c->dict_ready = true;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_exchange_local(pfaai_gpu_ctx **hs, int n) {
+    if (!hs || n < 2) return PFAAI_ERR_CONSTRUCT;
+    std::vector<Ctx *> cs(n);
+    for (int i = 0; i < n; i++) {
+        cs[i] = reinterpret_cast<Ctx *>(hs[i]);
+        if (!cs[i] || !cs[i]->partitioned || cs[i]->n_shards != n) { set_error(cs[i], "exchange_local: every shard's context, after build_partitioned"); return PFAAI_ERR_CONSTRUCT; }
     }
-    PF_TRY(launch_scan(c, ptr<int32_t>(c->seg_len), nseg, ptr<int64_t>(c->seg_off), nullptr));
-    k_transpose_t<<<(unsigned)ceil_div64(nseg, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->seg_len), P, G,
-                                                                          c->host_T ? nullptr : ptr<int32_t>(c->T),
-                                                                          ptr<int>(c->flags) + 1);
-    PF_LAUNCH_CHECK(c);
-    // K2b: stable LSD radix sort on (genome*P + protein), one onesweep kernel per 8-bit digit; the digit histograms
-    // of all passes come from the segment histogram; the last pass emits the tetramers only
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_S0], c->stream));
-    if (nF > 0) {
-        int keybits = 1;
-        while (keybits < 31 && ((int64_t)1 << keybits) < nseg) keybits++;
-        const int passes = (keybits + 7) / 8;
-        const int64_t n_tiles = ceil_div64(nF, OS_TILE);
-        const size_t control_bytes = sizeof(uint64_t) * (size_t)(8 + n_tiles * RS_RADIX);
-        PF_TRY(ensure(c, c->block_hist, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX));
-        PF_TRY(ensure(c, c->block_base, control_bytes));
-        PF_CUDA(c, cudaMemsetAsync(c->block_hist.p, 0, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX, c->stream));
-        k_digit_hist<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 256), (int64_t)c->sm_count * 2), 256, 0, c->stream>>>(
-            ptr<uint32_t>(c->seg_len), nseg, passes, ptr<unsigned long long>(c->block_hist));
-        PF_LAUNCH_CHECK(c);
-        k_digit_scan<<<passes, RS_RADIX, 0, c->stream>>>(ptr<unsigned long long>(c->block_hist));
-        PF_LAUNCH_CHECK(c);
-        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
-        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
-        uint64_t *src = ptr<uint64_t>(c->itemsA), *dst = ptr<uint64_t>(c->itemsB);
-        for (int pass = 0; pass < passes; pass++) {
-            const int shift = TET_BITS + 8 * pass;
-            const unsigned long long *base = ptr<unsigned long long>(c->block_hist) + (size_t)pass * RS_RADIX;
-            PF_CUDA(c, cudaMemsetAsync(c->block_base.p, 0, control_bytes, c->stream));
-            if (pass == passes - 1)
-                k_onesweep<true><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, nF, shift, base, ptr<uint64_t>(c->block_base),
-                                                                                        nullptr, ptr<uint32_t>(c->vals));
-            else
-                k_onesweep<false><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, nF, shift, base, ptr<uint64_t>(c->block_base),
-                                                                                         dst, nullptr);
-            PF_LAUNCH_CHECK(c);
-            std::swap(src, dst);
+    for (int i = 0; i < n; i++) {                       // the producers' builds must have finished
+        PF_CUDA(cs[i], cudaSetDevice(cs[i]->device));
+        PF_CUDA(cs[i], cudaStreamSynchronize(cs[i]->stream));
+    }
+    for (int d = 0; d < n; d++) {
+        Ctx *dst = cs[d];
+        PF_CUDA(dst, cudaSetDevice(dst->device));
+        void *db[4] = {dst->blob.p, dst->stages.p, dst->colT.p, dst->stage_rng.p};
+        for (int si = 0; si < n; si++) {
+            Ctx *src = cs[si];
+            if (src == dst) continue;
+            void *sb[4] = {src->blob.p, src->stages.p, src->colT.p, src->stage_rng.p};
+            for (int k = 0; k < 4; k++) {
+                if (src->chunk_bytes[k] != dst->chunk_bytes[k]) { set_error(dst, "exchange_local: shards disagree on the chunk sizes"); return PFAAI_ERR_CONSTRUCT; }
+                const size_t off = (size_t)src->shard * (size_t)src->chunk_bytes[k];
+                if (src->used_bytes[k] > 0)
+                    PF_CUDA(dst, cudaMemcpyPeerAsync(static_cast<char *>(db[k]) + off, dst->device, static_cast<char *>(sb[k]) + off, src->device,
+                                                     (size_t)src->used_bytes[k], dst->stream));
+            }
         }
     }
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_S1], c->stream));
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_B1], c->stream));
-    int fl[4];
-    PF_TRY(read_flags(c, fl));
-    if (fl[0] == 2) { set_error(c, "build: sum(Lc) != |F|"); return PFAAI_ERR_CONSTRUCT; }
-    if (fl[0]) { set_error(c, "build: posting with protein/genome id out of range"); return PFAAI_ERR_CONSTRUCT; }
-    c->max_len = fl[1];
-    c->tm.build_ms = ev_ms(c, EV_B0, EV_B1);
-    c->tm.sort_ms = ev_ms(c, EV_S0, EV_S1);
-    c->tm.n_launches = c->launches;
-    c->built = true;
+    for (int i = 0; i < n; i++) {
+        PF_CUDA(cs[i], cudaSetDevice(cs[i]->device));
+        PF_CUDA(cs[i], cudaStreamSynchronize(cs[i]->stream));
+        cs[i]->dict_ready = true;
+    }
     return PFAAI_OK;
 }
 
@@ -370,6 +485,138 @@ static int upload_i32(Ctx *c, DevBuf &b, const std::vector<int32_t> &v) {
     return PFAAI_OK;
 }
 
+// K4b: dictionaries of `n_groups` column blocks of the column list c->cols (cb_list: which blocks, NULL = 0..n_groups-1),
+// their T values and stage lists.  Group k gets slot slot_base + k; blobs go to [blob_base, blob_cap) of c->blob (blob_cap == 0:
+// the whole buffer, grown on demand), stages to [stage_base, stage_cap) of c->stages (stage_cap == 0: sized here).
+static int make_dictionaries(Ctx *c, int n_cols, const std::vector<int32_t> *cb_list, int n_groups, int slot_base, int64_t n_slots,
+                             size_t blob_base, size_t blob_cap, int64_t stage_base, int64_t stage_cap) {
+    const int P = c->P;
+    int max_sub = 1;
+    while (max_sub < MAX_SUB && (int64_t)(COLS_PER_TILE / max_sub) * c->max_len + 1 > MASK_CAP) max_sub *= 2;
+    const int64_t ndict = (int64_t)n_groups * P * NRANGE;
+    const bool growable = (blob_cap == 0);
+    PF_TRY(ensure(c, c->nsub, sizeof(int32_t) * (size_t)ndict));
+    PF_TRY(ensure(c, c->sub, sizeof(SubDesc) * (size_t)(ndict * max_sub)));
+    PF_TRY(ensure(c, c->colT, sizeof(int32_t) * (size_t)n_slots * P * COLS_PER_TILE));
+    PF_TRY(ensure(c, c->stage_off, sizeof(int64_t) * (size_t)(ndict + 1)));
+    PF_TRY(ensure(c, c->stage_rng, sizeof(int64_t) * 2 * (size_t)n_slots));
+    if (stage_cap == 0) {
+        PF_TRY(ensure(c, c->stages, sizeof(StageDesc) * (size_t)(ndict * max_sub)));
+        stage_cap = stage_base + ndict * max_sub;
+    }
+    if (growable) {
+        const int64_t col_postings = std::min<int64_t>(c->nF, (int64_t)n_cols * P * c->max_len);
+        const size_t guess = (size_t)ndict * (BM_BYTES + 16) + 8 * (size_t)col_postings;
+        if (c->blob.cap < guess) PF_TRY(ensure(c, c->blob, guess));
+    }
+    if (cb_list) {
+        PF_TRY(ensure(c, c->cb_list, sizeof(int32_t) * cb_list->size()));
+        if (!cb_list->empty())
+            PF_CUDA(c, cudaMemcpyAsync(c->cb_list.p, cb_list->data(), sizeof(int32_t) * cb_list->size(), cudaMemcpyHostToDevice, c->stream));
+    }
+    PF_CUDA(c, cudaFuncSetAttribute(k_dict_build, cudaFuncAttributeMaxDynamicSharedMemorySize, DB_SMEM));
+    PF_CUDA(c, cudaFuncSetAttribute(k_dict_build, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    unsigned long long *cursor = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->flags.p) + 32);
+    unsigned long long used = 0;
+    for (int attempt = 0;; attempt++) {
+        PF_CUDA(c, cudaMemsetAsync(reinterpret_cast<char *>(c->flags.p) + 8, 0, 56, c->stream));   // flags[2..], cursor
+        DictParams dp;
+        dp.seg_off = ptr<int64_t>(c->seg_off); dp.vals = ptr<uint32_t>(c->vals);
+        dp.cols = ptr<int32_t>(c->cols); dp.col_t = ptr<int32_t>(c->col_t); dp.n_cols = n_cols;
+        dp.T = ptr<int32_t>(c->T); dp.t_ld = c->G; dp.P = P; dp.max_sub = max_sub;
+        dp.blob = ptr<unsigned char>(c->blob); dp.blob_base = blob_base; dp.blob_cap = growable ? c->blob.cap : blob_cap; dp.cursor = cursor;
+        dp.cb_list = cb_list ? ptr<int32_t>(c->cb_list) : nullptr; dp.slot_base = slot_base;
+        dp.nsub = ptr<int32_t>(c->nsub); dp.sub = ptr<SubDesc>(c->sub); dp.colT = ptr<int32_t>(c->colT);
+        dp.err = ptr<int>(c->flags) + 3;
+        if (ndict > 0) {
+            k_dict_build<<<(unsigned)(n_groups * P), DB_THREADS, DB_SMEM, c->stream>>>(dp);
+            PF_LAUNCH_CHECK(c);
+        }
+        unsigned long long fl[4];   // {flags[2], flags[3]}, -, -, cursor at byte 32
+        PF_CUDA(c, cudaMemcpyAsync(fl, reinterpret_cast<char *>(c->flags.p) + 8, 32, cudaMemcpyDeviceToHost, c->stream));
+        PF_CUDA(c, cudaStreamSynchronize(c->stream));
+        used = fl[3];
+        const bool overflow = (fl[0] >> 32) != 0;
+        if (!overflow) break;
+        if (!growable) {
+            set_error(c, "build_partitioned: this shard's dictionaries need " + std::to_string(used) + " bytes, the agreed chunk holds " +
+                             std::to_string(blob_cap - blob_base) + " (unbalanced input: use pfaai_gpu_build)");
+            return PFAAI_ERR_CONSTRUCT;
+        }
+        if (attempt > 0) { set_error(c, "compute: dictionary buffer overflow after resize"); return PFAAI_ERR_CONSTRUCT; }
+        PF_TRY(ensure(c, c->blob, (size_t)fl[3] + 4096));
+    }
+    c->used_bytes[0] = (int64_t)used;
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->nsub), ndict, ptr<int64_t>(c->stage_off), nullptr));
+    if (ndict > 0) {
+        k_stage_fill<<<(unsigned)ceil_div64(ndict, 256), 256, 0, c->stream>>>(ptr<int32_t>(c->nsub), ptr<int64_t>(c->stage_off),
+                                                                            ptr<SubDesc>(c->sub), n_groups, P, max_sub,
+                                                                            ptr<StageDesc>(c->stages), ptr<int64_t>(c->stage_rng), slot_base,
+                                                                            stage_base, stage_cap, ptr<int>(c->flags) + 2);
+        PF_LAUNCH_CHECK(c);
+    }
+    return PFAAI_OK;
+}
+
+// Partitioned build, second half: the dictionaries of the column blocks inside this shard's own row blocks (all-vs-all: the
+// column genomes are the row genomes), written into this shard's chunk of the four exchange buffers.  Chunk sizes are a function
+// of (G, P, |F|, n_shards) only, so every shard computes the same layout without talking to the others.
+static int build_own_dictionaries(Ctx *c) {
+    const int P = c->P, G = c->G, n = c->n_shards;
+    const int ncb = (G + COLS_PER_TILE - 1) / COLS_PER_TILE, nrb = (G + TILE_ROWS - 1) / TILE_ROWS;
+    std::vector<int> nblk(n, 0);
+    std::vector<int32_t> own_cbs;
+    int64_t max_rows = 0;
+    std::vector<int64_t> rows_of(n, 0);
+    for (int I = 0; I < nrb; I++) {
+        const int o = fold_owner(I, n);
+        nblk[o]++;
+        rows_of[o] += std::min(TILE_ROWS, G - I * TILE_ROWS);
+        if (o == c->shard)
+            for (int j = 0; j < RB_CBS && I * RB_CBS + j < ncb; j++) own_cbs.push_back(I * RB_CBS + j);
+    }
+    for (int o = 0; o < n; o++) max_rows = std::max(max_rows, rows_of[o]);
+    const int max_blk = *std::max_element(nblk.begin(), nblk.end());
+    c->slot_cap = (int64_t)max_blk * RB_CBS;
+    const int64_t dict_cap = c->slot_cap * P * NRANGE;
+    // blob chunk: one bitmap (+ padding) per dictionary, 2x head room for column sub-splits on the first quarter, one mask per
+    // posting of the largest shard + 20 % (tetramers shared by several columns of a block need only one mask)
+    const int64_t mask_bytes = 8 * (int64_t)((double)c->nF * ((double)max_rows / (double)G) * 1.2) + 4096;
+    c->chunk_bytes[0] = ((dict_cap + dict_cap / 4) * (int64_t)(BM_BYTES + 16) + mask_bytes + 255) & ~(int64_t)255;
+    if (c->blob_chunk_hint > 0) c->chunk_bytes[0] = (c->blob_chunk_hint + 255) & ~(int64_t)255;
+    c->chunk_bytes[1] = (int64_t)sizeof(StageDesc) * dict_cap * 2;
+    c->chunk_bytes[2] = (int64_t)sizeof(int32_t) * c->slot_cap * P * COLS_PER_TILE;
+    c->chunk_bytes[3] = (int64_t)sizeof(int64_t) * 2 * c->slot_cap;
+    PF_TRY(ensure(c, c->blob, (size_t)c->chunk_bytes[0] * n));
+    PF_TRY(ensure(c, c->stages, (size_t)c->chunk_bytes[1] * n));
+    PF_TRY(ensure(c, c->colT, (size_t)c->chunk_bytes[2] * n));
+    PF_TRY(ensure(c, c->stage_rng, (size_t)c->chunk_bytes[3] * n));
+    // all-vs-all column plan: column j = genome j
+    std::vector<int32_t> ident(G);
+    for (int g = 0; g < G; g++) ident[g] = g;
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
+    PF_TRY(upload_i32(c, c->cols, ident)); PF_TRY(upload_i32(c, c->col_t, ident));
+    PF_CUDA(c, cudaMemsetAsync(static_cast<char *>(c->stage_rng.p) + (size_t)c->shard * c->chunk_bytes[3], 0, (size_t)c->chunk_bytes[3], c->stream));
+    const int64_t stage_base = (int64_t)c->shard * dict_cap * 2;
+    PF_TRY(make_dictionaries(c, G, &own_cbs, (int)own_cbs.size(), (int)(c->shard * c->slot_cap), c->slot_cap * n,
+                             (size_t)c->shard * (size_t)c->chunk_bytes[0], (size_t)(c->shard + 1) * (size_t)c->chunk_bytes[0],
+                             stage_base, stage_base + dict_cap * 2));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
+    int64_t n_stages = 0;
+    const int64_t ndict = (int64_t)own_cbs.size() * P * NRANGE;
+    int fl[4];
+    PF_CUDA(c, cudaMemcpyAsync(&n_stages, ptr<int64_t>(c->stage_off) + ndict, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+    PF_TRY(read_flags(c, fl));
+    if (fl[2]) { set_error(c, "build_partitioned: this shard's stage list exceeds the agreed chunk (many column sub-splits: use pfaai_gpu_build)"); return PFAAI_ERR_CONSTRUCT; }
+    c->used_bytes[1] = (int64_t)sizeof(StageDesc) * n_stages;
+    c->used_bytes[2] = (int64_t)sizeof(int32_t) * (int64_t)own_cbs.size() * P * COLS_PER_TILE;
+    c->used_bytes[3] = c->chunk_bytes[3];
+    c->tm.dict_ms = ev_ms(c, EV_K0, EV_K1);
+    c->tm.build_ms += c->tm.dict_ms;
+    c->tm.n_launches = c->launches;
+    return PFAAI_OK;
+}
+
 template <int NPL, int NPN>
 static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles) {
     auto kern = aji_tile_kernel<NPL, NPN>;
@@ -420,53 +667,19 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         PF_LAUNCH_CHECK(c);
     }
     PF_CUDA(c, cudaEventRecord(c->ev[EV_P1], c->stream));
-    // ---- K4b: column-block dictionaries + stage lists ----
+    // ---- K4b: column-block dictionaries + stage lists (a partitioned context already holds them: built by the shards that
+    //      own the column blocks and exchanged over NVLink before this call) ----
     const int nrb = (n_groups + TILE_WARPS - 1) / TILE_WARPS, ncb = (n_cols + COLS_PER_TILE - 1) / COLS_PER_TILE;
-    int max_sub = 1;
-    while (max_sub < MAX_SUB && (int64_t)(COLS_PER_TILE / max_sub) * c->max_len + 1 > MASK_CAP) max_sub *= 2;
-    const int64_t ndict = (int64_t)ncb * P * NRANGE;
-    PF_TRY(ensure(c, c->nsub, sizeof(int32_t) * (size_t)ndict));
-    PF_TRY(ensure(c, c->sub, sizeof(SubDesc) * (size_t)(ndict * max_sub)));
-    PF_TRY(ensure(c, c->colT, sizeof(int32_t) * (size_t)ncb * P * COLS_PER_TILE));
-    PF_TRY(ensure(c, c->stage_off, sizeof(int64_t) * (size_t)(ndict + 1)));
-    PF_TRY(ensure(c, c->stages, sizeof(StageDesc) * (size_t)(ndict * max_sub)));
-    PF_TRY(ensure(c, c->stage_begin, sizeof(int64_t) * (size_t)(ncb + 1)));
-    {
-        const int64_t col_postings = std::min<int64_t>(c->nF, (int64_t)n_cols * P * c->max_len);
-        const size_t guess = (size_t)ndict * (BM_BYTES + 16) + 8 * (size_t)col_postings;
-        if (c->blob.cap < guess) PF_TRY(ensure(c, c->blob, guess));
+    if (c->partitioned) {
+        if (mode != PFAAI_ALL_VS_ALL || c->n_shards < 2) { set_error(c, "compute: a partitioned build serves sharded all-vs-all only (use pfaai_gpu_build)"); return PFAAI_ERR_CONSTRUCT; }
+        if (!c->dict_ready) { set_error(c, "compute: partitioned build not finished (exchange the buffers, then pfaai_gpu_finish_partitioned)"); return PFAAI_ERR_CONSTRUCT; }
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
+    } else {
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
+        PF_TRY(make_dictionaries(c, n_cols, nullptr, ncb, 0, ncb, 0, 0, 0, 0));
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
     }
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
-    PF_CUDA(c, cudaFuncSetAttribute(k_dict_build, cudaFuncAttributeMaxDynamicSharedMemorySize, DB_SMEM));
-    PF_CUDA(c, cudaFuncSetAttribute(k_dict_build, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    unsigned long long *cursor = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->flags.p) + 32);
-    for (int attempt = 0;; attempt++) {
-        PF_CUDA(c, cudaMemsetAsync(reinterpret_cast<char *>(c->flags.p) + 8, 0, 56, c->stream));   // flags[2..], cursor
-        DictParams dp;
-        dp.seg_off = ptr<int64_t>(c->seg_off); dp.vals = ptr<uint32_t>(c->vals);
-        dp.cols = ptr<int32_t>(c->cols); dp.col_t = ptr<int32_t>(c->col_t); dp.n_cols = n_cols;
-        dp.T = ptr<int32_t>(c->T); dp.t_ld = c->G; dp.P = P; dp.max_sub = max_sub;
-        dp.blob = ptr<unsigned char>(c->blob); dp.blob_cap = c->blob.cap; dp.cursor = cursor;
-        dp.nsub = ptr<int32_t>(c->nsub); dp.sub = ptr<SubDesc>(c->sub); dp.colT = ptr<int32_t>(c->colT);
-        dp.err = ptr<int>(c->flags) + 3;
-        if (ndict > 0) {
-            k_dict_build<<<(unsigned)(ncb * P), DB_THREADS, DB_SMEM, c->stream>>>(dp);
-            PF_LAUNCH_CHECK(c);
-        }
-        unsigned long long fl[4];   // {flags[2], flags[3]}, -, -, cursor at byte 32
-        PF_CUDA(c, cudaMemcpyAsync(fl, reinterpret_cast<char *>(c->flags.p) + 8, 32, cudaMemcpyDeviceToHost, c->stream));
-        PF_CUDA(c, cudaStreamSynchronize(c->stream));
-        const bool overflow = (fl[0] >> 32) != 0;
-        if (!overflow) break;
-        if (attempt > 0) { set_error(c, "compute: dictionary buffer overflow after resize"); return PFAAI_ERR_CONSTRUCT; }
-        PF_TRY(ensure(c, c->blob, (size_t)fl[3] + 4096));
-    }
-    PF_TRY(launch_scan(c, ptr<int32_t>(c->nsub), ndict, ptr<int64_t>(c->stage_off), nullptr));
-    k_stage_fill<<<(unsigned)ceil_div64(ndict + 1, 256), 256, 0, c->stream>>>(ptr<int32_t>(c->nsub), ptr<int64_t>(c->stage_off),
-                                                                             ptr<SubDesc>(c->sub), ncb, P, max_sub,
-                                                                             ptr<StageDesc>(c->stages), ptr<int64_t>(c->stage_begin));
-    PF_LAUNCH_CHECK(c);
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
     // ---- tile list: row block x column block, I-major so that concurrently resident CTAs share the row
     //      block's slabs in L2; symmetric mode keeps only tiles that contain a cell with row < col.
     //      Sharding: row block I belongs to shard fold(I mod 2n) (folded assignment balances the
@@ -476,17 +689,28 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     std::vector<int4> tiles;
     c->owned_rows.clear();
     int local_rows = 0;
+    // slot of column block J (where its stage range / T values live): J itself, or -- partitioned -- the position inside the
+    // chunk of the shard that built it
+    std::vector<int32_t> slot_of(ncb);
+    for (int J = 0; J < ncb; J++) slot_of[J] = J;
+    if (c->partitioned) {
+        std::vector<int> nblk(c->n_shards, 0);
+        for (int I = 0; I * RB_CBS < ncb; I++) {
+            const int o = fold_owner(I, c->n_shards);
+            for (int j = 0; j < RB_CBS && I * RB_CBS + j < ncb; j++)
+                slot_of[I * RB_CBS + j] = (int32_t)(o * c->slot_cap + (int64_t)nblk[o] * RB_CBS + j);
+            nblk[o]++;
+        }
+    }
     for (int I = 0; I < nrb; I++) {
-        const int f = I % (2 * c->n_shards);
-        const int owner = f < c->n_shards ? f : 2 * c->n_shards - 1 - f;
-        if (owner != c->shard) continue;
+        if (fold_owner(I, c->n_shards) != c->shard) continue;
         const int row0 = I * TILE_ROWS, nr = std::min(TILE_ROWS, n_rows - row0);
         for (int J = 0; J < ncb; J++) {
             if (m.symmetric) {
                 const int col_max = std::min((J + 1) * COLS_PER_TILE, n_cols) - 1;
                 if (row0 >= col_max) continue;
             }
-            tiles.push_back(make_int4(I, J, sharded ? local_rows : row0, 0));
+            tiles.push_back(make_int4(I, J, sharded ? local_rows : row0, slot_of[J]));
         }
         for (int r = 0; r < nr; r++) c->owned_rows.push_back(row0 + r);
         local_rows += nr;
@@ -520,7 +744,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.ell = ptr<uint4>(c->ell); prm.ell_off = ptr<int64_t>(c->ell_off);
     prm.rows = ptr<int32_t>(c->rows); prm.row_t = ptr<int32_t>(c->row_t); prm.n_rows = n_rows; prm.n_groups = n_groups;
     prm.cols = ptr<int32_t>(c->cols); prm.n_cols = n_cols;
-    prm.stages = ptr<StageDesc>(c->stages); prm.stage_begin = ptr<int64_t>(c->stage_begin);
+    prm.stages = ptr<StageDesc>(c->stages); prm.stage_rng = ptr<int64_t>(c->stage_rng);
     prm.blob = ptr<unsigned char>(c->blob); prm.colT = ptr<int32_t>(c->colT);
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
     prm.out = direct_dev ? direct_dev : ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !sharded) ? 1 : 0;
@@ -541,7 +765,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
     c->tm.pack_ms = ev_ms(c, EV_P0, EV_P1);
-    c->tm.dict_ms = ev_ms(c, EV_K0, EV_K1);
+    if (!c->partitioned) c->tm.dict_ms = ev_ms(c, EV_K0, EV_K1);
     c->tm.tile_ms = ev_ms(c, EV_T0, EV_T1);
     c->tm.n_tiles = (int32_t)tiles.size();
     c->tm.n_launches = c->launches;   // build + this compute

@@ -117,10 +117,12 @@ struct DictParams {
     const int64_t *seg_off; const uint32_t *vals;
     const int32_t *cols, *col_t; int n_cols;
     const int32_t *T; int t_ld, P, max_sub;
-    unsigned char *blob; unsigned long long blob_cap; unsigned long long *cursor;
-    int32_t *nsub;     // [ncb*P*NRANGE]
-    SubDesc *sub;      // [ncb*P*NRANGE*max_sub]
-    int32_t *colT;     // [ncb*P*64]  T(p, column) of the block's columns (0 beyond the last column)
+    unsigned char *blob; unsigned long long blob_base, blob_cap; unsigned long long *cursor;   // blobs go to [blob_base, blob_cap)
+    const int32_t *cb_list;   // column block of the k-th dictionary group (NULL: k itself); a partitioned build lists the shard's own blocks
+    int slot_base;            // slot of group k = slot_base + k (colT / stage_rng are indexed by slot)
+    int32_t *nsub;     // [n_groups*P*NRANGE]
+    SubDesc *sub;      // [n_groups*P*NRANGE*max_sub]
+    int32_t *colT;     // [n_slots*P*64]  T(p, column) of the block's columns (0 beyond the last column)
     int *err;          // set to 1 when the dictionary buffer is too small (cursor still counts the need)
 };
 
@@ -224,7 +226,7 @@ __device__ __forceinline__ void dict_emit(const DictParams &prm, const DictSmem 
     }
     const uint32_t bytes = BM_BYTES + 8u * n_pad;
     if (tid == 0) {
-        unsigned long long off = atomicAdd(prm.cursor, (unsigned long long)bytes);
+        unsigned long long off = prm.blob_base + atomicAdd(prm.cursor, (unsigned long long)bytes);
         if (off + bytes > prm.blob_cap) { *prm.err = 1; off = ~0ull; }
         *s.s_off = off;
     }
@@ -257,7 +259,8 @@ __global__ void __launch_bounds__(DB_THREADS, 2) k_dict_build(const DictParams p
     s.s_off = reinterpret_cast<unsigned long long *>(s.wsum + 40);
     const int tid = threadIdx.x;
     const int P = prm.P;
-    const int cb = blockIdx.x / P, p = blockIdx.x % P;
+    const int kgrp = blockIdx.x / P, p = blockIdx.x % P;
+    const int cb = prm.cb_list ? prm.cb_list[kgrp] : kgrp;
     const int j0 = cb * COLS_PER_TILE, ncol = min(COLS_PER_TILE, prm.n_cols - j0);
     if (tid < COLS_PER_TILE) {
         int64_t beg = 0; int len = 0, split = 0, tv = 0;
@@ -269,7 +272,7 @@ __global__ void __launch_bounds__(DB_THREADS, 2) k_dict_build(const DictParams p
             tv = prm.T[(int64_t)p * prm.t_ld + prm.col_t[j0 + tid]];
         }
         s.col_beg[tid] = beg; s.col_len[tid] = len; s.col_split[tid] = split;
-        prm.colT[(int64_t)blockIdx.x * COLS_PER_TILE + tid] = tv;
+        prm.colT[((int64_t)(prm.slot_base + kgrp) * P + p) * COLS_PER_TILE + tid] = tv;
     }
     __syncthreads();
     for (int q = 0; q < NRANGE; q++) {
@@ -297,17 +300,24 @@ __global__ void __launch_bounds__(DB_THREADS, 2) k_dict_build(const DictParams p
     }
 }
 
-// flatten the sub-dictionaries into the per-column-block stage lists the tile kernel walks in order
+// flatten the sub-dictionaries into the per-column-block stage lists the tile kernel walks in order; group k (the k-th
+// column block of this build) owns slot slot_base + k, its stages are stored from stage_base on
 __global__ void k_stage_fill(const int32_t *__restrict__ nsub, const int64_t *__restrict__ stage_off, const SubDesc *__restrict__ sub,
-                             int ncb, int P, int max_sub, StageDesc *__restrict__ stages, int64_t *__restrict__ stage_begin) {
+                             int n_groups, int P, int max_sub, StageDesc *__restrict__ stages, int64_t *__restrict__ stage_rng,
+                             int slot_base, int64_t stage_base, int64_t stage_cap, int *__restrict__ err) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t n = (int64_t)ncb * P * NRANGE;
-    if (i > n) return;
-    if (i % ((int64_t)P * NRANGE) == 0) stage_begin[i / ((int64_t)P * NRANGE)] = stage_off[i];   // includes i == n
-    if (i == n) return;
+    const int64_t per = (int64_t)P * NRANGE, n = (int64_t)n_groups * per;
+    if (i >= n) return;
+    if (i == 0 && stage_base + stage_off[n] > stage_cap) *err = 1;
+    if (stage_base + stage_off[i + 1] > stage_cap) return;
+    if (i % per == 0) {
+        const int64_t k = i / per;
+        stage_rng[2 * (slot_base + k)] = stage_base + stage_off[i];
+        stage_rng[2 * (slot_base + k) + 1] = stage_base + stage_off[i + per];
+    }
     const int q = (int)(i % NRANGE), p = (int)((i / NRANGE) % P);
     const int ns = nsub[i];
-    const int64_t base = stage_off[i];
+    const int64_t base = stage_base + stage_off[i];
     for (int sidx = 0; sidx < ns; sidx++) {
         const SubDesc d = sub[i * max_sub + sidx];
         StageDesc st;

@@ -208,6 +208,58 @@ def test_sharded_row_blocks_assemble_to_the_full_matrix(pf, orc, n_shards):
     ctx.close()
 
 
+@pytest.mark.parametrize("n_shards,N,P", [(2, 1000, 3), (3, 1700, 2), (4, 900, 4)])
+def test_partitioned_build_matches_the_replicated_build(pf, orc, n_shards, N, P):
+    """pfaai_gpu_build_partitioned: every shard sorts only the postings of its own row blocks and builds only their
+    dictionaries; after the exchange (here: peer copies between contexts of one process) every shard's matrix must equal the
+    replicated-build shard matrix bit for bit, and the assembly the unsharded matrix.  N = 900 / 4 shards leaves a shard
+    without any row block (3 blocks of 384)."""
+    from parfastaai_b200 import sharding, synth
+    off, vals = synth.generate(N, P, seed=77)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ref = pf.PfaaiGpu(0)
+    ref.upload_index(P, N, F, Lc)
+    ref.build()
+    full = ref.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
+    ctxs = []
+    for s in range(n_shards):
+        c = pf.PfaaiGpu(0)
+        c.set_shard(s, n_shards)
+        c.upload_index(P, N, F, Lc)
+        c.build_partitioned()
+        with pytest.raises(pf.PfaaiError):          # not exchanged yet
+            c.compute(pf.ALL_VS_ALL, want_jac=False)
+        ctxs.append(c)
+    x = [c.exchange_buffers() for c in ctxs]
+    assert all([b[1] for b in xs] == [b[1] for b in x[0]] for xs in x)        # same chunk layout on every shard
+    assert all(b[2] <= b[1] for xs in x for b in xs)
+    pf.PfaaiGpu.exchange_local(ctxs)
+    parts, lay = [], []
+    for s, c in enumerate(ctxs):
+        ids = sharding.owned_indices(N, s, n_shards)
+        arr = c.get_arrays(want_lists=False)                                  # T: this shard's genomes only
+        assert np.array_equal(arr["T"][:, ids], T[:, ids])
+        assert not arr["T"][:, np.setdiff1d(np.arange(N), ids)].any()
+        part = c.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+        ref.set_shard(s, n_shards)
+        assert np.array_equal(part, ref.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"])
+        with pytest.raises(pf.PfaaiError):          # a partitioned index serves all-vs-all only
+            c.compute(pf.QUERY_SUBSET, qry_ids=np.array([1, 2], np.int32), want_jac=False)
+        parts.append(part.copy()); lay.append(ids)
+    assert np.array_equal(sharding.assemble(pf.ALL_VS_ALL, parts, lay, np.empty((N, N))), full)
+    # a second partitioned build on the same contexts (steady state: no reallocation) gives the same result
+    for c in ctxs:
+        c.build_partitioned()
+    pf.PfaaiGpu.exchange_local(ctxs)
+    for s, c in enumerate(ctxs):
+        assert np.array_equal(c.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], parts[s])
+        c.build()                                                              # back to the replicated build
+        assert np.array_equal(c.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], parts[s])
+        c.close()
+    ref.close()
+
+
 def test_pinned_host_matrix_is_stored_directly_and_identically(pf, orc):
     """pfaai_gpu_compute with a page-locked matrix: the tile kernel stores straight into host memory (no device copy
     of the matrix, no D2H call); the bytes must equal the staged path's in all three modes, ragged tile edges included."""
