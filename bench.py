@@ -398,14 +398,15 @@ def main():
             ctx.build()
             return
         ctx.build_partitioned()
-        x_ev[0].record(stream)
-        for ptr, chunk, _used in ctx.exchange_buffers():
-            key = (ptr, chunk)
-            if key not in xviews:
-                xviews[key] = torch.as_tensor(_DevMem(ptr, chunk * world), device=dev)
-            buf = xviews[key]
-            dist.all_gather_into_tensor(buf, buf[chunk * rank:chunk * (rank + 1)])
-        x_ev[1].record(stream)
+        with torch.cuda.stream(stream):          # the collectives must be ordered with the context's kernels: same stream
+            x_ev[0].record(stream)
+            for ptr, chunk, _used in ctx.exchange_buffers():
+                key = (ptr, chunk)
+                if key not in xviews:
+                    xviews[key] = torch.as_tensor(_DevMem(ptr, chunk * world), device=dev)
+                buf = xviews[key]
+                dist.all_gather_into_tensor(buf, buf[chunk * rank:chunk * (rank + 1)])
+            x_ev[1].record(stream)
         ctx.finish_partitioned()
 
     def step_device():
