@@ -256,6 +256,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--replicated-build", action="store_true",
                     help="N>1: every rank builds the whole index (the pre-partitioning path) instead of pfaai_gpu_build_partitioned")
+    ap.add_argument("--no-overlap", action="store_true", help="N>1: finish the dictionary exchange before the tile kernel starts")
     ap.add_argument("--verify", action="store_true", help="N>1: gather the shards on rank 0 and compare with an unsharded compute")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
@@ -389,6 +390,7 @@ def main():
 
     partitioned = world > 1 and not args.replicated_build
     xviews = {}
+    xstream = torch.cuda.Stream(device=dev) if world > 1 else None
     x_ev = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
 
     def build_index():
@@ -397,17 +399,25 @@ def main():
         if not partitioned:
             ctx.build()
             return
-        ctx.build_partitioned()
-        with torch.cuda.stream(stream):          # the collectives must be ordered with the context's kernels: same stream
-            x_ev[0].record(stream)
-            for ptr, chunk, _used in ctx.exchange_buffers():
+        ctx.build_partitioned()                  # returns with this shard's chunks complete (host-synchronous)
+        # the exchange runs on its own stream; the context is told the event that ends it, runs the tiles on its own dictionaries
+        # meanwhile and orders the remaining tiles behind the event (pfaai_gpu_finish_partitioned_async)
+        with torch.cuda.stream(xstream):
+            x_ev[0].record(xstream)
+            # small buffers first: their collectives are over before the tile kernel occupies every SM; the one that moves
+            # the dictionary blobs is then already resident and shares the GPU with the tiles on the rank's own dictionaries
+            for ptr, chunk, _used in sorted(ctx.exchange_buffers(), key=lambda b: b[1]):
                 key = (ptr, chunk)
                 if key not in xviews:
                     xviews[key] = torch.as_tensor(_DevMem(ptr, chunk * world), device=dev)
                 buf = xviews[key]
                 dist.all_gather_into_tensor(buf, buf[chunk * rank:chunk * (rank + 1)])
-            x_ev[1].record(stream)
-        ctx.finish_partitioned()
+            x_ev[1].record(xstream)
+        if args.no_overlap:
+            stream.wait_event(x_ev[1])
+            ctx.finish_partitioned()
+        else:
+            ctx.finish_partitioned_async(x_ev[1].cuda_event)
 
     def step_device():
         build_index()
@@ -519,7 +529,8 @@ def main():
                    "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); F replicated "
                                    f"on every GPU (N>1, inside the e2e region: every rank uploads its 1/N slice of F, NCCL all-gather over NVLink); "
                                    + ("partitioned index build: every rank sorts / builds the column dictionaries of its own row blocks, "
-                                      "the dictionaries are all-gathered over NVLink (NCCL, in place); " if partitioned else
+                                      "the dictionaries are all-gathered over NVLink (NCCL, in place, on a second stream) while the tiles on the rank's "
+                                      "own dictionaries are computed; " if partitioned else
                                       "index build replicated on every rank; ") +
                                    f"no reduction collective; every rank stores only its own upper-triangle rows into pinned host memory"),
                    "l2_policy": "inputs larger than L2 (F = %.2f GB, matrix = %.2f GB vs 126 MB L2)" % (8 * nF / 1e9, d2h / 1e9),

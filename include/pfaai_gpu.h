@@ -133,6 +133,11 @@ int  pfaai_gpu_build_partitioned(pfaai_gpu_ctx *ctx);
 int  pfaai_gpu_set_partition_chunk(pfaai_gpu_ctx *ctx, int64_t blob_chunk_bytes);
 int  pfaai_gpu_exchange_buffers(pfaai_gpu_ctx *ctx, pfaai_exchange_t *out);
 int  pfaai_gpu_finish_partitioned(pfaai_gpu_ctx *ctx);
+/* The same while the exchange is still running on another stream: cuda_event (a cudaEvent_t recorded behind the last exchange
+ * operation) marks its completion.  The next pfaai_gpu_compute* first runs the tiles that only need this shard's own
+ * dictionaries, then waits for the event on the context's stream and runs the rest: the transfer over NVLink overlaps the
+ * computation.  The event must stay valid until that compute returns. */
+int  pfaai_gpu_finish_partitioned_async(pfaai_gpu_ctx *ctx, void *cuda_event);
 /* exchange + finish for n_shards contexts of THIS process (any mix of devices), after each ran build_partitioned */
 int  pfaai_gpu_exchange_local(pfaai_gpu_ctx **ctxs, int n_shards);
 /* Parity hooks (any pointer may be NULL): Lc/Lp [160000], T [P x G], and the genome-major index:

@@ -28,7 +28,7 @@ EXPORTS = [
     "pfaai_gpu_matrix_shape", "pfaai_gpu_matrix_dev", "pfaai_gpu_download_matrix", "pfaai_gpu_compute",
     "pfaai_gpu_n_pairs", "pfaai_gpu_get_timings", "pfaai_gpu_shard_layout", "pfaai_gpu_index_device_buffers",
     "pfaai_gpu_build_partitioned", "pfaai_gpu_exchange_buffers", "pfaai_gpu_finish_partitioned", "pfaai_gpu_exchange_local",
-    "pfaai_gpu_set_partition_chunk",
+    "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
 ]
 
 
@@ -86,6 +86,7 @@ def load():
     L.pfaai_gpu_finish_partitioned.argtypes = [vp]
     L.pfaai_gpu_exchange_local.argtypes = [C.POINTER(vp), i32]
     L.pfaai_gpu_set_partition_chunk.argtypes = [vp, i64]
+    L.pfaai_gpu_finish_partitioned_async.argtypes = [vp, vp]
     _lib = L
     return L
 
@@ -178,6 +179,10 @@ class PfaaiGpu:
 
     def finish_partitioned(self):
         self._check(self._L.pfaai_gpu_finish_partitioned(self._h), "finish_partitioned")
+
+    def finish_partitioned_async(self, cuda_event_ptr):
+        """The exchange is still in flight on another stream; `cuda_event_ptr` (cudaEvent_t) fires when it is complete."""
+        self._check(self._L.pfaai_gpu_finish_partitioned_async(self._h, C.c_void_p(cuda_event_ptr)), "finish_partitioned_async")
 
     @staticmethod
     def exchange_local(ctxs):

@@ -61,6 +61,7 @@ struct TileParams {
     int32_t *counts_out;       // optional, [n_rows x n_cols x P]
     const int4 *tiles;         // (row block I, col block J, first output row of block I in this shard's matrix, slot of J)
     int n_tiles;
+    int *tile_counter;         // next tile to hand out (0 at launch)
 };
 
 // ---- PTX wrappers: mbarrier + bulk async copy (TMA) ----
@@ -216,7 +217,14 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                      &full[slot]);
     };
 
-    for (int t = blockIdx.x; t < prm.n_tiles; t += gridDim.x) {
+    // tiles are handed out in list order by a global counter (zeroed by the host): CTAs that start late -- e.g. behind the
+    // collective kernels of a dictionary exchange that is still running -- simply take fewer tiles
+    int *s_tile = reinterpret_cast<int *>(smem + 40);
+    for (;;) {
+        if (tid == 0) *s_tile = atomicAdd(prm.tile_counter, 1);
+        __syncthreads();
+        const int t = *s_tile;          // rewritten only after the barrier that ends this tile
+        if (t >= prm.n_tiles) break;
         const int4 tile = prm.tiles[t];
         const int cb = tile.y, cslot = tile.w;
         const int64_t sb = prm.stage_rng[2 * cslot];

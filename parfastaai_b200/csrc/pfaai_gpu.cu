@@ -40,6 +40,8 @@ struct Ctx {
     bool partitioned = false, dict_ready = false;
     int64_t nF_owned = 0;
     int64_t slot_cap = 0;                 // dictionary slots (column blocks) per shard chunk
+    void *exch_event = nullptr;           // pfaai_gpu_finish_partitioned_async: the exchange is complete when this cudaEvent_t fires
+    DevBuf tile_ctr;
     int64_t blob_chunk_hint = 0;          // pfaai_gpu_set_partition_chunk: agreed size of a shard's blob chunk (0: default bound)
     int64_t chunk_bytes[4] = {}, used_bytes[4] = {};   // exchange buffers: blob, stages, colT, stage_rng
     int64_t out_rows = 0, out_cols = 0;
@@ -121,7 +123,7 @@ static int build_internal(Ctx *c, bool partitioned) {
     const int P = c->P, G = c->G;
     const int64_t nF = c->nF, nseg = (int64_t)P * G;
     c->launches = 0;
-    c->built = false; c->partitioned = false; c->dict_ready = false;
+    c->built = false; c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr;
     PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
     PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->seg_len, sizeof(uint32_t) * (size_t)nseg));
@@ -267,7 +269,7 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
                      &c->tile_sums, &c->block_hist, &c->block_base, &c->flags, &c->rows, &c->row_t, &c->cols, &c->col_t,
                      &c->ell_nch, &c->ell_off, &c->ell, &c->tiles, &c->out, &c->S_out, &c->N_out, &c->counts_out,
                      &c->nsub, &c->sub, &c->colT, &c->blob, &c->stage_off, &c->stages, &c->stage_rng,
-                     &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list};
+                     &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
@@ -368,6 +370,15 @@ int pfaai_gpu_finish_partitioned(pfaai_gpu_ctx *h) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     if (!c || !c->partitioned || !c->built) { set_error(c, "finish_partitioned: no partitioned build"); return PFAAI_ERR_CONSTRUCT; }
     c->dict_ready = true;
+    c->exch_event = nullptr;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_finish_partitioned_async(pfaai_gpu_ctx *h, void *cuda_event) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !c->partitioned || !c->built || !cuda_event) { set_error(c, "finish_partitioned_async: no partitioned build / no event"); return PFAAI_ERR_CONSTRUCT; }
+    c->dict_ready = true;
+    c->exch_event = cuda_event;
     return PFAAI_OK;
 }
 
@@ -619,6 +630,7 @@ static int build_own_dictionaries(Ctx *c) {
 
 template <int NPL, int NPN>
 static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles) {
+    if (n_tiles <= 0) return PFAAI_OK;
     auto kern = aji_tile_kernel<NPL, NPN>;
     PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
     // persistent CTAs, one per SM; CTA b walks tiles b, b + grid, ... (row-block-major order keeps the
@@ -686,7 +698,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     //      triangular work); a sharded context stores only its own row blocks, compactly, in ascending order ----
     const bool sharded = c->n_shards > 1;
     if (sharded && (want_sn || want_counts)) { set_error(c, "compute: the JAC / counts hooks need an unsharded context"); return PFAAI_ERR_CONSTRUCT; }
-    std::vector<int4> tiles;
+    std::vector<int4> tiles, tiles_late;   // partitioned: tiles on this shard's own dictionaries first (they need no exchange)
     c->owned_rows.clear();
     int local_rows = 0;
     // slot of column block J (where its stage range / T values live): J itself, or -- partitioned -- the position inside the
@@ -710,11 +722,14 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
                 const int col_max = std::min((J + 1) * COLS_PER_TILE, n_cols) - 1;
                 if (row0 >= col_max) continue;
             }
-            tiles.push_back(make_int4(I, J, sharded ? local_rows : row0, slot_of[J]));
+            const bool own_dict = !c->partitioned || fold_owner(J / RB_CBS, c->n_shards) == c->shard;
+            (own_dict ? tiles : tiles_late).push_back(make_int4(I, J, sharded ? local_rows : row0, slot_of[J]));
         }
         for (int r = 0; r < nr; r++) c->owned_rows.push_back(row0 + r);
         local_rows += nr;
     }
+    const int n_early = (int)tiles.size();
+    tiles.insert(tiles.end(), tiles_late.begin(), tiles_late.end());
     PF_TRY(ensure(c, c->tiles, sizeof(int4) * tiles.size()));
     if (!tiles.empty()) PF_CUDA(c, cudaMemcpyAsync(c->tiles.p, tiles.data(), sizeof(int4) * tiles.size(), cudaMemcpyHostToDevice, c->stream));
     // ---- outputs: the kernel's row axis is the output's row axis in all-vs-all and its column axis otherwise ----
@@ -751,16 +766,24 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
     prm.N_out = want_sn ? ptr<int32_t>(c->N_out) : nullptr;
     prm.counts_out = want_counts ? ptr<int32_t>(c->counts_out) : nullptr;
-    prm.tiles = ptr<int4>(c->tiles); prm.n_tiles = (int)tiles.size();
+    PF_TRY(ensure(c, c->tile_ctr, 2 * sizeof(int)));
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
-    if (!tiles.empty() && c->nF > 0) {
-        if (lane_lookups <= 511) {
-            if (P <= 127) PF_TRY((launch_tiles<9, 7>(c, prm, (int)tiles.size())));
-            else PF_TRY((launch_tiles<9, 10>(c, prm, (int)tiles.size())));
-        } else {
-            if (P <= 127) PF_TRY((launch_tiles<12, 7>(c, prm, (int)tiles.size())));
-            else PF_TRY((launch_tiles<12, 10>(c, prm, (int)tiles.size())));
-        }
+    PF_CUDA(c, cudaMemsetAsync(c->tile_ctr.p, 0, 2 * sizeof(int), c->stream));
+    auto launch_range = [&](int first, int count, int ctr) -> int {
+        if (count <= 0 || c->nF <= 0) return PFAAI_OK;
+        prm.tiles = ptr<int4>(c->tiles) + first; prm.n_tiles = count; prm.tile_counter = ptr<int>(c->tile_ctr) + ctr;
+        if (lane_lookups <= 511) return (P <= 127) ? launch_tiles<9, 7>(c, prm, count) : launch_tiles<9, 10>(c, prm, count);
+        return (P <= 127) ? launch_tiles<12, 7>(c, prm, count) : launch_tiles<12, 10>(c, prm, count);
+    };
+    if (c->partitioned && c->exch_event) {
+        // the other shards' dictionaries may still be in flight (exchange on another stream): the tiles on our own column
+        // blocks run meanwhile, the rest is ordered behind the caller's event
+        PF_TRY(launch_range(0, n_early, 0));
+        PF_CUDA(c, cudaStreamWaitEvent(c->stream, reinterpret_cast<cudaEvent_t>(c->exch_event), 0));
+        PF_TRY(launch_range(n_early, (int)tiles.size() - n_early, 1));
+        c->exch_event = nullptr;   // consumed: later computes on this build find the dictionaries in place
+    } else {
+        PF_TRY(launch_range(0, (int)tiles.size(), 0));
     }
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -252,7 +252,13 @@ def test_partitioned_build_matches_the_replicated_build(pf, orc, n_shards, N, P)
     for c in ctxs:
         c.build_partitioned()
     pf.PfaaiGpu.exchange_local(ctxs)
+    import torch
     for s, c in enumerate(ctxs):
+        assert np.array_equal(c.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], parts[s])
+        # the overlapped variant: own-dictionary tiles first, the rest behind the caller's "exchange done" event
+        ev = torch.cuda.Event()
+        ev.record()
+        c.finish_partitioned_async(ev.cuda_event)
         assert np.array_equal(c.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], parts[s])
         c.build()                                                              # back to the replicated build
         assert np.array_equal(c.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], parts[s])
