@@ -17,8 +17,9 @@ genome-major lists) + row-slice packing + the tile kernel (counts -> Jaccard -> 
   cpu_baseline the UNMODIFIED reference binary (oracle/_ref, kind "reference") on a bounded synthetic
                SQLite DB with all host cores; falls back to the oracle port when the binary is unusable.
 
-Workloads: N=1 -> BASELINE config 4 (10,000 genomes x 122 SCPs all-vs-all); N>1 -> BASELINE config 5
-(50,000 x 122, output row blocks sharded over the ranks, no data-path collective: strong scaling).
+Workload at every N: BASELINE config 5 (50,000 genomes x 122 SCPs all-vs-all, the configuration the metric is quoted on at
+1/2/4/8 B200; it fits one GPU), output row blocks sharded over the ranks: strong scaling, the driver's per-N values are
+directly comparable.  `--genomes 10000` gives BASELINE config 4.
 `--impl reference` times the reference's own CPU implementation (rank 0 only).
 """
 from __future__ import annotations
@@ -191,7 +192,7 @@ def run_reference_arm(args, rank, emit):
     P = args.scps
     threads = os.cpu_count() or 1
     line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "int32+f64",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32+f64",
             "data": "synthetic"}
     with tempfile.TemporaryDirectory(prefix="pfaai_ref_") as tmp:
         n = args.ref_genomes
@@ -249,7 +250,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--genomes", type=int, default=0, help="override the workload size (default: 10000 at N=1, 50000 at N>1)")
+    ap.add_argument("--genomes", type=int, default=0, help="override the workload size (default: 50000 = BASELINE config 5 at every N)")
     ap.add_argument("--scps", type=int, default=122)
     ap.add_argument("--ref-genomes", type=int, default=64, help="size of the reference arm's bounded sample")
     ap.add_argument("--cpu-baseline-genomes", type=int, default=96)
@@ -293,7 +294,7 @@ def main():
     from parfastaai_b200 import sharding, synth
 
     P = args.scps
-    G = args.genomes or (10000 if world == 1 else 50000)
+    G = args.genomes or 50000
     pairs_total = G * (G - 1) // 2
 
     class _DevMem:   # raw device pointer of the C-ABI context -> torch tensor (for copies / NCCL on the index buffers)
@@ -336,10 +337,15 @@ def main():
     M_pin = torch.empty(my_rows * my_cols, dtype=torch.float64).pin_memory()
     M = M_pin.numpy().reshape(my_rows, my_cols)
     if world > 1:
-        # N > 1: the index is replicated by a broadcast over NVLink from the rank that holds the database
-        # (BASELINE north_star); the contexts expose their device index buffers for it
+        # N > 1: the contexts expose their device index buffers; F is sized for N equal slices (the last one padded) so that the
+        # all-gather of the e2e region lands directly in the context's buffer
+        per = (nF + world - 1) // world
+        per += (-per) % 2                                   # 16-byte aligned slices
+        f_ptr0, _, _ = ctx.index_device_buffers(P, G, per * world)
         f_ptr, lc_ptr, _ = ctx.index_device_buffers(P, G, nF)
-        F_dev = torch.as_tensor(_DevMem(f_ptr, max(8 * nF, 8)), device=dev)
+        assert f_ptr == f_ptr0, "the context reallocated its F buffer"
+        F_all = torch.as_tensor(_DevMem(f_ptr, 8 * per * world), device=dev)
+        F_dev = F_all[:max(8 * nF, 8)]
         Lc_dev = torch.as_tensor(_DevMem(lc_ptr, 4 * pf.NTETRA), device=dev)
 
     def barrier():
@@ -357,8 +363,6 @@ def main():
     if world > 1:
         # one-time, untimed: hand every rank its 1/N slice of F in its OWN pinned host memory (as a one-process-per-GPU loader
         # would hold it): rank 0 uploads F once, broadcasts it, every rank copies its slice back
-        per = (nF + world - 1) // world
-        per += (-per) % 2                                   # 16-byte aligned slices
         lo, hi = min(nF, rank * per), min(nF, (rank + 1) * per)
         with torch.cuda.stream(stream):
             if rank == 0:
@@ -371,8 +375,6 @@ def main():
             F_slice_pin[:8 * (hi - lo)].copy_(F_dev[8 * lo:8 * hi], non_blocking=True)
             Lc_pin_r.copy_(Lc_dev, non_blocking=True)
         stream.synchronize()
-        # all-gather staging: N equal slices (the last one padded) -> the context's F buffer
-        F_gather = torch.empty(8 * per * world, dtype=torch.uint8, device=dev)
         if rank == 0:
             del F_pin, F
         index_resident = True
@@ -383,10 +385,10 @@ def main():
         if world == 1:
             ctx.upload_index(P, G, F, Lc)
             return
-        F_gather[8 * per * rank:8 * per * (rank + 1)].copy_(F_slice_pin, non_blocking=True)
+        mine = F_all[8 * per * rank:8 * per * (rank + 1)]
+        mine.copy_(F_slice_pin, non_blocking=True)
         Lc_dev.copy_(Lc_pin_r, non_blocking=True)
-        dist.all_gather_into_tensor(F_gather, F_gather[8 * per * rank:8 * per * (rank + 1)])
-        F_dev.copy_(F_gather[:8 * nF], non_blocking=True)
+        dist.all_gather_into_tensor(F_all, mine)           # in place, straight into the context's F buffer
 
     partitioned = world > 1 and not args.replicated_build
     xviews = {}
@@ -508,7 +510,7 @@ def main():
     alg_bytes = int(tm["tile_alg_bytes"])
     achieved = alg_bytes / (tile_avg_ms / 1e3) / 1e9
     traffic = onchip = None
-    tp = os.path.join(ROOT, "profiles", "tile_kernel_traffic.json")
+    tp = os.path.join(ROOT, "profiles", f"tile_kernel_traffic_{G}.json")
     if os.path.exists(tp):
         try:
             with open(tp) as fh:
@@ -521,7 +523,7 @@ def main():
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "int32+f64", "data": "synthetic",
         "config": {"workload": f"synthetic {G} genomes x {P} SCPs all-vs-all (BASELINE config {'4' if G == 10000 else '5' if G == 50000 else 'custom'}; "
                                f"SURVEY 8(d) recipe, seed {SEED})",

@@ -62,6 +62,7 @@ struct TileParams {
     const int4 *tiles;         // (row block I, col block J, first output row of block I in this shard's matrix, slot of J)
     int n_tiles;
     int *tile_counter;         // next tile to hand out (0 at launch)
+    uint32_t k27, k16;         // 2^27, 2^16 (PF_IMAD_HI: shift-by-multiply constants)
 };
 
 // ---- PTX wrappers: mbarrier + bulk async copy (TMA) ----
@@ -147,15 +148,29 @@ __device__ __forceinline__ double jaccard_fast(uint32_t rcp32, int c, int den) {
 
 struct Mask64 { uint32_t lo, hi; };
 
+#ifndef PF_IMAD_HI
+#define PF_IMAD_HI 0
+#endif
+
 // x = slab_encode(v): bitmap word at byte offset x>>5; shifting it left by x&31 puts v's presence bit in
 // bit 31 and the presence bits of smaller tetramers below it (the rank half-word falls off the top).
 // A miss (57 % of the lookups on the synthetic family) adds the zero mask and issues no second load.
 // bm32 / masks32: 32-bit shared-space addresses of the stage's bitmap and mask array.
-__device__ __forceinline__ Mask64 dict_lookup(uint32_t bm32, uint32_t masks32, uint32_t x) {
+__device__ __forceinline__ Mask64 dict_lookup(uint32_t bm32, uint32_t masks32, uint32_t x, uint32_t k27 = 0u, uint32_t k16 = 0u) {
     uint32_t w;
+#if PF_IMAD_HI
+    // shifts done as the high half of a multiply-add: IMAD.HI runs on the FMA pipe, LEA.HI on the (half-rate, limiting) ALU pipe
+    uint32_t a;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(a) : "r"(x), "r"(k27), "r"(bm32));        // bm32 + (x >> 5), k27 = 2^27 (opaque to ptxas)
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(a));
+    const uint32_t t = __funnelshift_l(0u, w, x);                   // w << (x & 31)
+    uint32_t idx;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(idx) : "r"(w), "r"(k16), "r"(__popc(t))); // (w >> 16) + popc(t), k16 = 2^16
+#else
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(bm32 + (x >> 5)));
     const uint32_t t = __funnelshift_l(0u, w, x);                   // w << (x & 31)
     const uint32_t idx = (w >> 16) + __popc(t);                     // rank of the word + #present <= v  (>= 1 on a hit)
+#endif
     Mask64 r; r.lo = 0u; r.hi = 0u;
     if ((int32_t)t < 0)
         asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.lo), "=r"(r.hi) : "r"(masks32 + 8u * idx));
@@ -203,6 +218,10 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
     asm volatile("{\n.reg .u64 t64;\ncvta.to.shared.u64 t64, %1;\ncvt.u32.u64 %0, t64;\n}" : "=r"(stage32) : "l"(stage_mem));
     // this thread's 64 tensor-memory columns (32 doubles): lane quadrant warp%4, column block warp/4
     const uint32_t taddr = *tmem_slot + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * TMEM_COLS_PER_WARP);
+    uint32_t k27 = 0u, k16 = 0u;    // shift amounts as multipliers (PF_IMAD_HI), hidden from constant propagation
+#if PF_IMAD_HI
+    k27 = prm.k27; k16 = prm.k16;   // kernel parameters: ptxas cannot fold them back into shifts
+#endif
     uint32_t use_par = 0u;          // bit s = wait parity of slot s (flips per completed fill), identical in every thread
 
     auto issue = [&](const uint4 st, int slot, int cslot) {
@@ -327,8 +346,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
 #pragma unroll
                     for (int qq = 0; qq < 2; qq++) {
                         const uint4 v = qq ? cur1 : cur0;
-                        const Mask64 m0 = dict_lookup(bm, masks, v.x), m1 = dict_lookup(bm, masks, v.y);
-                        const Mask64 m2 = dict_lookup(bm, masks, v.z), m3 = dict_lookup(bm, masks, v.w);
+                        const Mask64 m0 = dict_lookup(bm, masks, v.x, k27, k16), m1 = dict_lookup(bm, masks, v.y, k27, k16);
+                        const Mask64 m2 = dict_lookup(bm, masks, v.z, k27, k16), m3 = dict_lookup(bm, masks, v.w, k27, k16);
                         uint32_t ta_lo, ta_hi, tb_lo, tb_hi;
                         PF_CSA(ta_lo, plo[0], plo[0], m0.lo, m1.lo); PF_CSA(ta_hi, phi[0], phi[0], m0.hi, m1.hi);
                         PF_CSA(tb_lo, plo[0], plo[0], m2.lo, m3.lo); PF_CSA(tb_hi, phi[0], phi[0], m2.hi, m3.hi);

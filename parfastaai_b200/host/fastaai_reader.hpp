@@ -189,9 +189,11 @@ class SQLiteSCPDataBase {
         return db;
     }
 
-  public:
-    explicit SQLiteSCPDataBase(const std::string &dbPath) : m_pathToDb(dbPath) {
-        m_sqltDbPtr = open_ro(dbPath, &m_dbErrorCode);
+    struct DeferOpen {};
+    SQLiteSCPDataBase(const std::string &dbPath, DeferOpen) : m_pathToDb(dbPath) {}   // a subclass decides whether SQLite is needed
+
+    void openAndReadNames() {
+        m_sqltDbPtr = open_ro(m_pathToDb, &m_dbErrorCode);
         if (m_dbErrorCode != SQLITE_OK) return;
         // same statements as db_helper.hpp:169-218 / 59-107 (protein order = first appearance)
         m_dbErrorCode = detail::query_strings(
@@ -200,6 +202,9 @@ class SQLiteSCPDataBase {
             m_dbErrorCode = detail::query_strings(
                 m_sqltDbPtr, "SELECT " + m_dbNames.GMTTAB_COLUMN_GNAME + " FROM " + m_dbNames.GMTTAB, m_dbMeta.genomeSet);
     }
+
+  public:
+    explicit SQLiteSCPDataBase(const std::string &dbPath) : m_pathToDb(dbPath) { openAndReadNames(); }
     SQLiteSCPDataBase(const SQLiteSCPDataBase &) = delete;
     SQLiteSCPDataBase &operator=(const SQLiteSCPDataBase &) = delete;
     virtual ~SQLiteSCPDataBase() { if (m_sqltDbPtr) closeDB(); }
@@ -220,7 +225,7 @@ class SQLiteSCPDataBase {
     }
 
     // == validate() (scp_db.hpp:111-118)
-    pfaai_status validate() const {
+    virtual pfaai_status validate() const {
         if (m_dbErrorCode != SQLITE_OK || m_sqltDbPtr == nullptr) {
             std::cerr << "Error in opening " << getDBPath() << std::endl;
             if (m_dbErrorCode != SQLITE_OK) std::cerr << "DB ERROR: " << sqlite3_errstr(m_dbErrorCode) << std::endl;
@@ -230,7 +235,7 @@ class SQLiteSCPDataBase {
     }
 
     // Lc, F, T of the whole database (B.6: subset mode indexes the whole DB as well).  Returns an SQLite rc.
-    int loadIndex(HostIndex &ix) const {
+    virtual int loadIndex(HostIndex &ix) const {
         const int P = (int)m_dbMeta.proteinSet.size(), G = (int)m_dbMeta.genomeSet.size();
         ix.nProteins = P; ix.nGenomes = G; ix.nTargets = G; ix.nQueries = G;
         ix.T.assign((size_t)P * G, 0);

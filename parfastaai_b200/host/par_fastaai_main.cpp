@@ -16,12 +16,14 @@
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
+#include <memory>
 #include <string>
 #include <unordered_set>
 #include <vector>
 
 #include "csv_writer.hpp"
 #include "fastaai_reader.hpp"
+#include "index_cache.hpp"
 #include "pfaai_driver.hpp"
 
 using namespace pfaai_host;
@@ -32,7 +34,7 @@ struct AppParams {
     std::string pathToDatabase, pathToQryDatabase, pathToQrySubsetFile, pathToOutputFile;
     std::string outFieldSeparator = ",";
     std::vector<std::string> qryGenomeSet;
-    std::string dumpIndexPrefix, formatDoublesFile;
+    std::string dumpIndexPrefix, formatDoublesFile, indexCachePath;
     int device = 0, nGpus = 1;
     bool refCompat = true, sameDevice = false;
 
@@ -53,6 +55,7 @@ struct AppParams {
            << "  --device INT [0]            first CUDA device ordinal\n"
            << "  --gpus INT [1]              number of GPUs (devices device..device+gpus-1); output row blocks are sharded over them\n"
            << "  --no-ref-compat             query-DB mode: corrected T lookup (default reproduces the reference)\n"
+           << "  --index-cache TEXT          single-DB modes: device-ready index cache of the input DB (read if valid, else written)\n"
            << "  --dump-index TEXT           host only: write PREFIX.{lc,f,t}.bin and exit\n";
     }
     // returns -1 to continue, otherwise the process exit code
@@ -96,7 +99,9 @@ struct AppParams {
                 nGpus = std::max(1, std::atoi(d.c_str()));
             } else if (a == "--same-device") sameDevice = true;   // test hook: all shards on one GPU
             else if (a == "--no-ref-compat") refCompat = false;
-            else if (a == "--dump-index") {
+            else if (a == "--index-cache") {
+                if (!need(indexCachePath)) return fail(114, "--index-cache: 1 required TEXT missing");
+            } else if (a == "--dump-index") {
                 if (!need(dumpIndexPrefix)) return fail(114, "--dump-index: 1 required TEXT missing");
             } else if (a == "--format-doubles") {
                 if (!need(formatDoublesFile)) return fail(114, "--format-doubles: 1 required TEXT missing");
@@ -206,8 +211,15 @@ int overlap_banner(const std::vector<std::string> &common) {
     return PFAAI_ERR_CONSTRUCT;
 }
 
+// the database object of the single-DB modes: plain SQLite, or SQLite behind the index cache (--index-cache)
+std::unique_ptr<SQLiteSCPDataBase> open_main_db(const AppParams &args) {
+    if (args.indexCachePath.empty()) return std::unique_ptr<SQLiteSCPDataBase>(new SQLiteSCPDataBase(args.pathToDatabase));
+    return std::unique_ptr<SQLiteSCPDataBase>(new CachedSCPDataBase(args.pathToDatabase, args.indexCachePath));
+}
+
 int parallel_fastaai(const AppParams &args) {                       // main.cpp:177-202
-    SQLiteSCPDataBase db(args.pathToDatabase);
+    std::unique_ptr<SQLiteSCPDataBase> dbp = open_main_db(args);
+    SQLiteSCPDataBase &db = *dbp;
     if (db.validate() != PFAAI_OK) return PFAAI_ERR_SQLITE_DB;
     if (!args.dumpIndexPrefix.empty()) {
         HostIndex ix;
@@ -219,7 +231,8 @@ int parallel_fastaai(const AppParams &args) {                       // main.cpp:
 }
 
 int parallel_subset_fastaai(const AppParams &args) {                // main.cpp:234-266
-    SQLiteSCPDataBase db(args.pathToDatabase);
+    std::unique_ptr<SQLiteSCPDataBase> dbp = open_main_db(args);
+    SQLiteSCPDataBase &db = *dbp;
     if (db.validate() != PFAAI_OK) return PFAAI_ERR_SQLITE_DB;
     const DBMetaData &meta = db.getMeta();
     std::unordered_set<std::string> have(meta.genomeSet.begin(), meta.genomeSet.end());

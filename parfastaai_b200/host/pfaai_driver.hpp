@@ -116,13 +116,16 @@ class DataStructBase {
         m_ctxs.assign(n, nullptr);
         std::vector<int> rcs(n, PFAAI_OK);
         std::vector<std::string> errs(n);
+        // several GPUs, all-vs-all: partitioned build -- every GPU sorts the postings and builds the column dictionaries of its
+        // own row blocks only, the parts are exchanged by peer copies (pfaai_gpu_exchange_local); otherwise replicated build
+        const bool partitioned = n > 1 && mode() == PFAAI_ALL_VS_ALL && !m_hostT;
         auto work = [&](int k) {
             int rc = pfaai_gpu_create(&m_ctxs[k], m_devices[k], 0);
             if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(nullptr); return; }
             rc = pfaai_gpu_upload_index(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(),
                                         m_hostT ? m_ix.T.data() : nullptr);
-            if (rc == PFAAI_OK) rc = pfaai_gpu_build(m_ctxs[k]);
             if (rc == PFAAI_OK) rc = pfaai_gpu_set_shard(m_ctxs[k], k, n);
+            if (rc == PFAAI_OK) rc = partitioned ? pfaai_gpu_build_partitioned(m_ctxs[k]) : pfaai_gpu_build(m_ctxs[k]);
             if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(m_ctxs[k]); }
         };
         {
@@ -138,12 +141,27 @@ class DataStructBase {
             }
         pfaai_gpu_ctx *m_ctx = m_ctxs[0];
         int rc;
+        if (partitioned && (rc = pfaai_gpu_exchange_local(m_ctxs.data(), n)) != PFAAI_OK) {
+            std::cerr << "Error in device index exchange ; " << pfaai_gpu_last_error(m_ctx) << std::endl;
+            return m_errorCode = (pfaai_status)rc;
+        }
         m_Lp.resize(NTETRAMERS);
         std::vector<int32_t> Tdev((size_t)m_ix.nProteins * m_ix.nGenomes);
         rc = pfaai_gpu_get_arrays(m_ctx, nullptr, m_Lp.data(), Tdev.data(), nullptr, nullptr);
         if (rc != PFAAI_OK) {
             std::cerr << "Error in device index read-back ; " << pfaai_gpu_last_error(m_ctx) << std::endl;
             return m_errorCode = (pfaai_status)rc;
+        }
+        if (partitioned) {      // every shard holds the T columns of its own genomes (zero elsewhere): the sum is T
+            std::vector<int32_t> Tk(Tdev.size());
+            for (int k = 1; k < n; k++) {
+                rc = pfaai_gpu_get_arrays(m_ctxs[k], nullptr, nullptr, Tk.data(), nullptr, nullptr);
+                if (rc != PFAAI_OK) {
+                    std::cerr << "Error in device index read-back ; " << pfaai_gpu_last_error(m_ctxs[k]) << std::endl;
+                    return m_errorCode = (pfaai_status)rc;
+                }
+                for (size_t i = 0; i < Tk.size(); i++) Tdev[i] += Tk[i];
+            }
         }
         if (!m_hostT && Tdev != m_ix.T) {
             // single-DB modes: the device T (histogram of F) must equal proteinTetramerCounts' T

@@ -90,6 +90,28 @@ def test_against_reference_binary_on_synthetic_db(cli, tmp_path):
         assert open(a, "rb").read() == open(b, "rb").read(), extra
 
 
+def test_index_cache_gives_identical_csv(cli, tmp_path):
+    """--index-cache: a run served from the cache (SQLite never opened) writes the same CSV bytes, in all-vs-all and in
+    query-subset mode (the cache holds the whole database)."""
+    import shutil
+    db = str(tmp_path / "s1.db")
+    shutil.copy(gu.db_path("xdb_subset1.db"), db)
+    cache = str(tmp_path / "s1.pfidx")
+    n = gu.names()
+    qfile = tmp_path / "q.txt"
+    qfile.write_text("\n".join(n["subset1_genomes"][:2]) + "\n")
+    for extra in ([], ["-q", str(qfile)]):
+        plain, first, second = (str(tmp_path / f) for f in ("plain.csv", "first.csv", "second.csv"))
+        run(cli, db, plain, *extra)
+        if os.path.exists(cache):
+            os.remove(cache)
+        r1 = run(cli, db, first, *extra, "--index-cache", cache)
+        r2 = run(cli, db, second, *extra, "--index-cache", cache)
+        assert "written" in r1.stdout and "SQLite not opened" in r2.stdout
+        assert open(plain, "rb").read() == open(first, "rb").read() == open(second, "rb").read()
+    assert open(plain, "rb").read() != b""
+
+
 def test_multi_gpu_sharded_cli_matches_single_gpu(cli, tmp_path):
     """--gpus N: output row blocks sharded over N contexts, host scatter + mirror; bytes must equal the 1-GPU CSV.
     On a single-GPU box the N contexts share the device (--same-device); with >= 2 GPUs both layouts are run."""

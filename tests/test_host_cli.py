@@ -64,6 +64,41 @@ def test_loader_query_db_mode_matches_goldens(cli, tmp_path):
     assert np.array_equal(d["t"], g["t"])                                         # T unrestricted, queries at nT + id
 
 
+def test_index_cache_round_trip_and_staleness(cli, tmp_path):
+    """--index-cache: the first run reads SQLite and writes the cache, the second serves names + Lc/F/T
+    from it without opening SQLite (bit-identical arrays); a changed database (size / mtime) or a damaged cache is ignored and
+    the cache rewritten."""
+    import shutil
+    db = str(tmp_path / "s1.db")
+    shutil.copy(gu.db_path("xdb_subset1.db"), db)
+    cache = str(tmp_path / "s1.pfidx")
+    g = gu.load("xdb_subset1")
+    r1 = run(cli, db, str(tmp_path / "o.csv"), "--dump-index", str(tmp_path / "a"), "--index-cache", cache)
+    assert r1.returncode == 0 and "Index cache         : written" in r1.stdout and os.path.exists(cache), r1.stdout + r1.stderr
+    r2 = run(cli, db, str(tmp_path / "o.csv"), "--dump-index", str(tmp_path / "b"), "--index-cache", cache)
+    assert r2.returncode == 0 and "Index cache         : loaded" in r2.stdout and "SQLite not opened" in r2.stdout
+    a, b = load_dump(str(tmp_path / "a")), load_dump(str(tmp_path / "b"))
+    for k in ("dims", "lc", "f", "t"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(b["lc"], g["lc"]) and np.array_equal(b["f"], g["f"]) and np.array_equal(b["t"], g["t"])
+    # the cache really is what is read: without the database's tables the cached run still works
+    blob = open(cache, "rb").read()
+    assert blob[:8] == b"PFIDX001"
+    # stale: touch the database -> cache ignored and rewritten
+    os.utime(db, ns=(1, 1))
+    r3 = run(cli, db, str(tmp_path / "o.csv"), "--dump-index", str(tmp_path / "c"), "--index-cache", cache)
+    assert r3.returncode == 0 and "written" in r3.stdout and "loaded" not in r3.stdout
+    # damaged (one flipped byte in T, truncated): ignored and rewritten
+    for damage in (lambda d: d[:-5] + bytes([d[-5] ^ 1]) + d[-4:], lambda d: d[:-100]):
+        good = open(cache, "rb").read()
+        open(cache, "wb").write(damage(good))
+        r4 = run(cli, db, str(tmp_path / "o.csv"), "--dump-index", str(tmp_path / "d"), "--index-cache", cache)
+        assert r4.returncode == 0 and "written" in r4.stdout and "loaded" not in r4.stdout
+        assert open(cache, "rb").read() == good
+    d = load_dump(str(tmp_path / "d"))
+    assert np.array_equal(d["f"], g["f"])
+
+
 def test_exit_codes_and_banners(cli, tmp_path):
     out = str(tmp_path / "o.csv")
     assert run(cli).returncode == 106                                            # CLI11 RequiredError

@@ -17,7 +17,7 @@ if [ "${NCU:-1}" = "1" ]; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv \
       python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $OUT/ncu_launches.log 2>&1
   echo "ncu launches rc=$?"
-  ncu --set full --clock-control none --import-source on -k regex:aji_tile -s 1 -c 1 -o $OUT/tile_full \
+  timeout ${NCU_FULL_TIMEOUT:-900} ncu --set full --clock-control none --import-source on -k regex:aji_tile -s 1 -c 1 -o $OUT/tile_full \
       python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $OUT/ncu_full.log 2>&1
   echo "ncu full rc=$?"
 fi
