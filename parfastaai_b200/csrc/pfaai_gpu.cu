@@ -1,6 +1,7 @@
 // pfaai_gpu.cu -- C-ABI (include/pfaai_gpu.h) and host orchestration of the sm_100a AJI path.
 // No CPU fallback: every entry point either runs the CUDA kernels or returns PFAAI_ERR_CONSTRUCT.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -629,13 +630,13 @@ static int build_own_dictionaries(Ctx *c) {
 }
 
 template <int NPL, int NPN>
-static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles) {
+static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles, int reserve_sms = 0) {
     if (n_tiles <= 0) return PFAAI_OK;
     auto kern = aji_tile_kernel<NPL, NPN>;
     PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
     // persistent CTAs, one per SM; CTA b walks tiles b, b + grid, ... (row-block-major order keeps the
     // concurrently processed tiles on the same row slabs, which stay L2-resident)
-    const int grid = std::min(n_tiles, c->sm_count);
+    const int grid = std::min(n_tiles, std::max(1, c->sm_count - reserve_sms));
     kern<<<(unsigned)grid, TILE_THREADS, SMEM_TOTAL, c->stream>>>(prm);
     PF_LAUNCH_CHECK(c);
     return PFAAI_OK;
@@ -770,21 +771,24 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     PF_TRY(ensure(c, c->tile_ctr, 2 * sizeof(int)));
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
     PF_CUDA(c, cudaMemsetAsync(c->tile_ctr.p, 0, 2 * sizeof(int), c->stream));
-    auto launch_range = [&](int first, int count, int ctr) -> int {
+    auto launch_range = [&](int first, int count, int ctr, int reserve) -> int {
         if (count <= 0 || c->nF <= 0) return PFAAI_OK;
         prm.tiles = ptr<int4>(c->tiles) + first; prm.n_tiles = count; prm.tile_counter = ptr<int>(c->tile_ctr) + ctr;
-        if (lane_lookups <= 511) return (P <= 127) ? launch_tiles<9, 7>(c, prm, count) : launch_tiles<9, 10>(c, prm, count);
-        return (P <= 127) ? launch_tiles<12, 7>(c, prm, count) : launch_tiles<12, 10>(c, prm, count);
+        if (lane_lookups <= 511) return (P <= 127) ? launch_tiles<9, 7>(c, prm, count, reserve) : launch_tiles<9, 10>(c, prm, count, reserve);
+        return (P <= 127) ? launch_tiles<12, 7>(c, prm, count, reserve) : launch_tiles<12, 10>(c, prm, count, reserve);
     };
     if (c->partitioned && c->exch_event) {
         // the other shards' dictionaries may still be in flight (exchange on another stream): the tiles on our own column
         // blocks run meanwhile, the rest is ordered behind the caller's event
-        PF_TRY(launch_range(0, n_early, 0));
+        // A tile CTA fills its SM (227 KB of shared memory), so the exchange's collective kernels can only run on SMs the early
+        // launch leaves free: a late-arriving collective would otherwise wait for the whole early launch to drain.
+        static const int reserve = [] { const char *e = getenv("PFAAI_EXCHANGE_SMS"); return e ? std::max(0, atoi(e)) : 40; }();
+        PF_TRY(launch_range(0, n_early, 0, reserve));
         PF_CUDA(c, cudaStreamWaitEvent(c->stream, reinterpret_cast<cudaEvent_t>(c->exch_event), 0));
-        PF_TRY(launch_range(n_early, (int)tiles.size() - n_early, 1));
+        PF_TRY(launch_range(n_early, (int)tiles.size() - n_early, 1, 0));
         c->exch_event = nullptr;   // consumed: later computes on this build find the dictionaries in place
     } else {
-        PF_TRY(launch_range(0, (int)tiles.size(), 0));
+        PF_TRY(launch_range(0, (int)tiles.size(), 0, 0));
     }
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
