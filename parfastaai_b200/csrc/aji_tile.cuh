@@ -151,6 +151,9 @@ struct Mask64 { uint32_t lo, hi; };
 #ifndef PF_IMAD_HI
 #define PF_IMAD_HI 0
 #endif
+#ifndef PF_WALK_UNROLL
+#define PF_WALK_UNROLL 0     // 1: 16 lookups per walk-loop iteration, ping-pong chunk registers (A/B variant)
+#endif
 
 // x = slab_encode(v): bitmap word at byte offset x>>5; shifting it left by x&31 puts v's presence bit in
 // bit 31 and the presence bits of smaller tetramers below it (the rank half-word falls off the top).
@@ -337,6 +340,62 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                     rp += 64;
                 }
                 o_fetched = o_cur + n_cur;
+#if PF_WALK_UNROLL
+                // 8 lookups (two 512-byte chunks v0, v1) -> one carry of weight 8 in (e_lo, e_hi)
+#define PF_STEP8(v0, v1, e_lo, e_hi)                                                                                         \
+                    do {                                                                                                     \
+                        uint32_t f_lo[2], f_hi[2];                                                                           \
+                        _Pragma("unroll") for (int qq = 0; qq < 2; qq++) {                                                   \
+                            const uint4 v = qq ? (v1) : (v0);                                                                \
+                            const Mask64 m0 = dict_lookup(bm, masks, v.x, k27, k16), m1 = dict_lookup(bm, masks, v.y, k27, k16); \
+                            const Mask64 m2 = dict_lookup(bm, masks, v.z, k27, k16), m3 = dict_lookup(bm, masks, v.w, k27, k16); \
+                            uint32_t ta_lo, ta_hi, tb_lo, tb_hi;                                                             \
+                            PF_CSA(ta_lo, plo[0], plo[0], m0.lo, m1.lo); PF_CSA(ta_hi, phi[0], phi[0], m0.hi, m1.hi);        \
+                            PF_CSA(tb_lo, plo[0], plo[0], m2.lo, m3.lo); PF_CSA(tb_hi, phi[0], phi[0], m2.hi, m3.hi);        \
+                            PF_CSA(f_lo[qq], plo[1], plo[1], ta_lo, tb_lo); PF_CSA(f_hi[qq], phi[1], phi[1], ta_hi, tb_hi);  \
+                        }                                                                                                    \
+                        PF_CSA(e_lo, plo[2], plo[2], f_lo[0], f_lo[1]); PF_CSA(e_hi, phi[2], phi[2], f_hi[0], f_hi[1]);      \
+                    } while (0)
+                // two eights -> plane 3, the sixteens carry ripples into planes 4..
+#define PF_FOLD16(a_lo, a_hi, b_lo, b_hi)                                                                                    \
+                    do {                                                                                                     \
+                        uint32_t cl, ch;                                                                                     \
+                        PF_CSA(cl, plo[3], plo[3], a_lo, b_lo); PF_CSA(ch, phi[3], phi[3], a_hi, b_hi);                      \
+                        _Pragma("unroll") for (int kk = 4; kk < NPL; kk++) {                                                 \
+                            const uint32_t tl = plo[kk] & cl, th = phi[kk] & ch;                                             \
+                            plo[kk] ^= cl; phi[kk] ^= ch; cl = tl; ch = th;                                                  \
+                        }                                                                                                    \
+                    } while (0)
+                int c = 0;
+                if (pending && n_cur > 0) {          // warp-uniform: pair the carry left over by the previous stage
+                    const uint4 nx0 = __ldg(rp), nx1 = __ldg(rp + 32);
+                    rp += 64;
+                    uint32_t e_lo, e_hi;
+                    PF_STEP8(cur0, cur1, e_lo, e_hi);
+                    PF_FOLD16(pe_lo, pe_hi, e_lo, e_hi);
+                    pending = false;
+                    cur0 = nx0; cur1 = nx1;
+                    c = 2;
+                }
+                for (; c + 4 <= n_cur; c += 4) {     // 16 lookups per iteration, chunk registers ping-pong (no moves, no flag)
+                    const uint4 nx0 = __ldg(rp), nx1 = __ldg(rp + 32);
+                    uint32_t e1_lo, e1_hi, e2_lo, e2_hi;
+                    PF_STEP8(cur0, cur1, e1_lo, e1_hi);
+                    cur0 = __ldg(rp + 64); cur1 = __ldg(rp + 96);
+                    rp += 128;
+                    PF_STEP8(nx0, nx1, e2_lo, e2_hi);
+                    PF_FOLD16(e1_lo, e1_hi, e2_lo, e2_hi);
+                }
+                if (c < n_cur) {                     // one step left: its carry waits for the next stage (or the SCP's end)
+                    const uint4 nx0 = __ldg(rp), nx1 = __ldg(rp + 32);
+                    rp += 64;
+                    PF_STEP8(cur0, cur1, pe_lo, pe_hi);
+                    pending = true;
+                    cur0 = nx0; cur1 = nx1;
+                }
+#undef PF_STEP8
+#undef PF_FOLD16
+#else
                 for (int c = 0; c < n_cur; c += 2) {
                     // prefetch the next step (possibly the next stage's first chunks; the slab buffer is padded at its end)
                     const uint4 nx0 = __ldg(rp), nx1 = __ldg(rp + 32);
@@ -369,6 +428,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                     }
                     cur0 = nx0; cur1 = nx1;
                 }
+#endif
             }
             // ================= release the slot; the last warp to leave refills it =================
             __syncwarp();
