@@ -62,6 +62,9 @@ struct TileParams {
     const int4 *tiles;         // (row block I, col block J, first output row of block I in this shard's matrix, slot of J)
     int n_tiles;
     int *tile_counter;         // next tile to hand out (0 at launch)
+    const int4 *tiles2;        // optional second list, taken up when the first one is exhausted (its own counter)
+    int n_tiles2;
+    int *tile_counter2;
     uint32_t k27, k16;         // 2^27, 2^16 (PF_IMAD_HI: shift-by-multiply constants)
 };
 
@@ -210,6 +213,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         mbar_init(&full[0], 1);
         mbar_init(&full[1], 1);
         done[0] = 0u; done[1] = 0u;
+        reinterpret_cast<int *>(smem + 40)[1] = 0;   // tile list in use
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -241,13 +245,24 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
 
     // tiles are handed out in list order by a global counter (zeroed by the host): CTAs that start late -- e.g. behind the
     // collective kernels of a dictionary exchange that is still running -- simply take fewer tiles
-    int *s_tile = reinterpret_cast<int *>(smem + 40);
+    int *s_tile = reinterpret_cast<int *>(smem + 40);      // [0] tile code: index | list << 30, or -1 = done; [1] current list
     for (;;) {
-        if (tid == 0) *s_tile = atomicAdd(prm.tile_counter, 1);
+        if (tid == 0) {
+            int code = -1;
+            if (s_tile[1] == 0) {
+                const int t = atomicAdd(prm.tile_counter, 1);
+                if (t < prm.n_tiles) code = t; else s_tile[1] = 1;
+            }
+            if (code < 0 && prm.n_tiles2 > 0) {
+                const int t = atomicAdd(prm.tile_counter2, 1);
+                if (t < prm.n_tiles2) code = t | (1 << 30);
+            }
+            s_tile[0] = code;
+        }
         __syncthreads();
-        const int t = *s_tile;          // rewritten only after the barrier that ends this tile
-        if (t >= prm.n_tiles) break;
-        const int4 tile = prm.tiles[t];
+        const int code = s_tile[0];     // rewritten only after the barrier that ends this tile
+        if (code < 0) break;
+        const int4 tile = (code >> 30) ? prm.tiles2[code & 0x3fffffff] : prm.tiles[code];
         const int cb = tile.y, cslot = tile.w;
         const int64_t sb = prm.stage_rng[2 * cslot];
         const int nst = (int)(prm.stage_rng[2 * cslot + 1] - sb);

@@ -24,6 +24,7 @@ struct Ctx {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;      // second instance of the tile kernel behind a dictionary exchange (compute_internal)
     bool own_stream = false;
     std::string err;
     int shard = 0, n_shards = 1;
@@ -51,7 +52,7 @@ struct Ctx {
     std::vector<int32_t> owned_rows;   // kernel rows of this shard, in the order they are stored
     int shard_axis = 0;
     // events / stats
-    cudaEvent_t ev[14] = {};
+    cudaEvent_t ev[16] = {};
     pfaai_timings_t tm = {};
     int launches = 0;
 };
@@ -79,7 +80,7 @@ template <typename T> static inline T *ptr(DevBuf &b) { return reinterpret_cast<
 #define PF_TRY(call) do { int rc__ = (call); if (rc__ != PFAAI_OK) return rc__; } while (0)
 #define PF_LAUNCH_CHECK(c) do { (c)->launches++; PF_CUDA((c), cudaGetLastError()); } while (0)
 
-enum { EV_H2D0, EV_H2D1, EV_B0, EV_S0, EV_S1, EV_B1, EV_P0, EV_P1, EV_T0, EV_T1, EV_D0, EV_D1, EV_K0, EV_K1 };
+enum { EV_H2D0, EV_H2D1, EV_B0, EV_S0, EV_S1, EV_B1, EV_P0, EV_P1, EV_T0, EV_T1, EV_D0, EV_D1, EV_K0, EV_K1, EV_FORK, EV_JOIN };
 
 static inline int fold_owner(int block, int n_shards) {   // pfaai_gpu_set_shard: block b belongs to shard f(b mod 2n)
     const int f = block % (2 * n_shards);
@@ -253,6 +254,7 @@ int pfaai_gpu_create(pfaai_gpu_ctx **out, int device, unsigned /*flags*/) {
     c->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { g_create_error = "cudaStreamCreate failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
     c->own_stream = true;
+    if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { g_create_error = "cudaStreamCreate failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
     for (auto &ev : c->ev)
         if (cudaEventCreate(&ev) != cudaSuccess) { g_create_error = "cudaEventCreate failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
     if (cudaMalloc(&c->flags.p, 64) != cudaSuccess) { g_create_error = "cudaMalloc failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
@@ -273,6 +275,7 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
                      &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -630,14 +633,15 @@ static int build_own_dictionaries(Ctx *c) {
 }
 
 template <int NPL, int NPN>
-static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles, int reserve_sms = 0) {
+static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles, int reserve_sms = 0, cudaStream_t stream = nullptr) {
     if (n_tiles <= 0) return PFAAI_OK;
+    if (!stream) stream = c->stream;
     auto kern = aji_tile_kernel<NPL, NPN>;
     PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
     // persistent CTAs, one per SM; CTA b walks tiles b, b + grid, ... (row-block-major order keeps the
     // concurrently processed tiles on the same row slabs, which stay L2-resident)
     const int grid = std::min(n_tiles, std::max(1, c->sm_count - reserve_sms));
-    kern<<<(unsigned)grid, TILE_THREADS, SMEM_TOTAL, c->stream>>>(prm);
+    kern<<<(unsigned)grid, TILE_THREADS, SMEM_TOTAL, stream>>>(prm);
     PF_LAUNCH_CHECK(c);
     return PFAAI_OK;
 }
@@ -771,25 +775,36 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     PF_TRY(ensure(c, c->tile_ctr, 2 * sizeof(int)));
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
     PF_CUDA(c, cudaMemsetAsync(c->tile_ctr.p, 0, 2 * sizeof(int), c->stream));
-    auto launch_range = [&](int first, int count, int ctr, int reserve) -> int {
-        if (count <= 0 || c->nF <= 0) return PFAAI_OK;
-        prm.tiles = ptr<int4>(c->tiles) + first; prm.n_tiles = count; prm.tile_counter = ptr<int>(c->tile_ctr) + ctr;
-        if (lane_lookups <= 511) return (P <= 127) ? launch_tiles<9, 7>(c, prm, count, reserve) : launch_tiles<9, 10>(c, prm, count, reserve);
-        return (P <= 127) ? launch_tiles<12, 7>(c, prm, count, reserve) : launch_tiles<12, 10>(c, prm, count, reserve);
+    // list 1 = tiles [0, n1), list 2 (optional) = tiles [n1, n1 + n2): a CTA moves on to list 2 when list 1 is exhausted
+    auto launch_lists = [&](int n1, int n2, int reserve, cudaStream_t st) -> int {
+        if (n1 + n2 <= 0 || c->nF <= 0) return PFAAI_OK;
+        prm.tiles = ptr<int4>(c->tiles); prm.n_tiles = n1; prm.tile_counter = ptr<int>(c->tile_ctr);
+        prm.tiles2 = ptr<int4>(c->tiles) + n1; prm.n_tiles2 = n2; prm.tile_counter2 = ptr<int>(c->tile_ctr) + 1;
+        const int count = n1 + n2;
+        if (lane_lookups <= 511) return (P <= 127) ? launch_tiles<9, 7>(c, prm, count, reserve, st) : launch_tiles<9, 10>(c, prm, count, reserve, st);
+        return (P <= 127) ? launch_tiles<12, 7>(c, prm, count, reserve, st) : launch_tiles<12, 10>(c, prm, count, reserve, st);
     };
-    if (c->partitioned && c->exch_event) {
-        // the other shards' dictionaries may still be in flight (exchange on another stream): the tiles on our own column
-        // blocks run meanwhile, the rest is ordered behind the caller's event
-        // A tile CTA fills its SM (227 KB of shared memory), so the exchange's collective kernels can only run on SMs the early
-        // launch leaves free: a late-arriving collective would otherwise wait for the whole early launch to drain.
+    const int n_late = (int)tiles.size() - n_early;
+    if (c->partitioned && c->exch_event && n_late > 0) {
+        // The other shards' dictionaries may still be in flight (exchange on the caller's stream).  Instance 1 of the kernel
+        // starts now and takes only the tiles on our own column blocks; it leaves some SMs free, because a tile CTA fills its
+        // SM (227 KB of shared memory) and would otherwise lock the exchange's collective kernels out.  Instance 2, on a second
+        // stream behind the caller's event, helps with whatever is left of those tiles and then runs the rest: both draw from
+        // the same counters, so no SM idles at a kernel boundary.
         static const int reserve = [] { const char *e = getenv("PFAAI_EXCHANGE_SMS"); return e ? std::max(0, atoi(e)) : 40; }();
-        PF_TRY(launch_range(0, n_early, 0, reserve));
-        PF_CUDA(c, cudaStreamWaitEvent(c->stream, reinterpret_cast<cudaEvent_t>(c->exch_event), 0));
-        PF_TRY(launch_range(n_early, (int)tiles.size() - n_early, 1, 0));
-        c->exch_event = nullptr;   // consumed: later computes on this build find the dictionaries in place
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_FORK], c->stream));
+        PF_TRY(launch_lists(n_early, 0, reserve, c->stream));
+        PF_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev[EV_FORK], 0));
+        PF_CUDA(c, cudaStreamWaitEvent(c->stream2, reinterpret_cast<cudaEvent_t>(c->exch_event), 0));
+        PF_TRY(launch_lists(n_early, n_late, 0, c->stream2));
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_JOIN], c->stream2));
+        PF_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev[EV_JOIN], 0));
     } else {
-        PF_TRY(launch_range(0, (int)tiles.size(), 0, 0));
+        if (c->partitioned && c->exch_event)
+            PF_CUDA(c, cudaStreamWaitEvent(c->stream, reinterpret_cast<cudaEvent_t>(c->exch_event), 0));
+        PF_TRY(launch_lists((int)tiles.size(), 0, 0, c->stream));
     }
+    c->exch_event = nullptr;   // consumed: later computes on this build find the dictionaries in place
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
     c->tm.pack_ms = ev_ms(c, EV_P0, EV_P1);
