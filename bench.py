@@ -257,6 +257,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--replicated-build", action="store_true",
                     help="N>1: every rank builds the whole index (the pre-partitioning path) instead of pfaai_gpu_build_partitioned")
+    ap.add_argument("--sliced-index", action="store_true",
+                    help="N>1: routed build -- every rank keeps only its 1/N slice of F resident, the postings travel to the rank that "
+                         "owns their genome by an NCCL all-to-all (no all-gather of F, no filter passes)")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: finish the dictionary exchange before the tile kernel starts")
     ap.add_argument("--verify", action="store_true", help="N>1: gather the shards on rank 0 and compare with an unsharded compute")
     args = ap.parse_args()
@@ -375,15 +378,30 @@ def main():
             F_slice_pin[:8 * (hi - lo)].copy_(F_dev[8 * lo:8 * hi], non_blocking=True)
             Lc_pin_r.copy_(Lc_dev, non_blocking=True)
         stream.synchronize()
-        if rank == 0:
+        if rank == 0 and not (args.verify and args.sliced_index):
             del F_pin, F
-        index_resident = True
+        sliced = args.sliced_index and not args.replicated_build
+        if sliced:
+            # from here on the context holds only this rank's slice of F (the buffer of the full F is reused)
+            fs_ptr, lcs_ptr = ctx.index_slice_buffers(P, G, nF, lo, hi - lo)
+            Fs_dev = torch.as_tensor(_DevMem(fs_ptr, max(8 * (hi - lo), 8)), device=dev)
+            Lcs_dev = torch.as_tensor(_DevMem(lcs_ptr, 4 * pf.NTETRA), device=dev)
+            with torch.cuda.stream(stream):
+                Fs_dev[:8 * (hi - lo)].copy_(F_slice_pin[:8 * (hi - lo)], non_blocking=True)
+                Lcs_dev.copy_(Lc_pin_r, non_blocking=True)
+            stream.synchronize()
+    else:
+        sliced = False
 
     def replicate_index():
         """host -> every GPU.  N = 1: pfaai_gpu_upload_index.  N > 1: every rank copies ITS slice of F H2D over its own
         PCIe link, the slices are all-gathered over NVLink / NVSwitch (NCCL) into every context's index buffer."""
         if world == 1:
             ctx.upload_index(P, G, F, Lc)
+            return
+        if sliced:                                         # only the rank's own slice, over its own PCIe link
+            Fs_dev[:8 * (hi - lo)].copy_(F_slice_pin[:8 * (hi - lo)], non_blocking=True)
+            Lcs_dev.copy_(Lc_pin_r, non_blocking=True)
             return
         mine = F_all[8 * per * rank:8 * per * (rank + 1)]
         mine.copy_(F_slice_pin, non_blocking=True)
@@ -395,13 +413,38 @@ def main():
     xstream = torch.cuda.Stream(device=dev) if world > 1 else None
     x_ev = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
 
+    rviews = {}
+
+    def route_and_build():
+        """Routed build: group the slice's items by owner, all-to-all over NVLink, sort + own dictionaries on the receiver."""
+        send_ptr, offs = ctx.route_prepare()
+        with torch.cuda.stream(stream):
+            cnt = torch.tensor([offs[d + 1] - offs[d] for d in range(world)], dtype=torch.int64, device=dev)
+            allc = torch.empty(world * world, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(allc, cnt)
+            allc = allc.view(world, world).cpu()             # [source, destination]
+            send_counts = [int(x) for x in allc[rank]]
+            recv_counts = [int(allc[s_, rank]) for s_ in range(world)]
+            total = sum(recv_counts)
+            recv_ptr = ctx.route_recv_buffer(total)
+            for key in ((send_ptr, offs[-1]), (recv_ptr, total)):
+                if key not in rviews:
+                    rviews[key] = torch.as_tensor(_DevMem(key[0], max(8 * key[1], 8)), device=dev)
+            send, recv = rviews[(send_ptr, offs[-1])][:8 * offs[-1]], rviews[(recv_ptr, total)][:8 * total]
+            dist.all_to_all_single(recv, send, output_split_sizes=[8 * x for x in recv_counts],
+                                   input_split_sizes=[8 * x for x in send_counts])
+        ctx.build_routed(total)
+
     def build_index():
         """N = 1 (or --replicated-build): pfaai_gpu_build.  N > 1: every rank sorts the postings and builds the column
         dictionaries of ITS OWN row blocks only; the four result buffers are all-gathered in place over NVLink (NCCL)."""
         if not partitioned:
             ctx.build()
             return
-        ctx.build_partitioned()                  # returns with this shard's chunks complete (host-synchronous)
+        if sliced:
+            route_and_build()
+        else:
+            ctx.build_partitioned()              # returns with this shard's chunks complete (host-synchronous)
         # the exchange runs on its own stream; the context is told the event that ends it, runs the tiles on its own dictionaries
         # meanwhile and orders the remaining tiles behind the event (pfaai_gpu_finish_partitioned_async)
         with torch.cuda.stream(xstream):
@@ -458,7 +501,10 @@ def main():
         # untimed, once: size the shards' dictionary chunks to what this database needs (max over the ranks + 2 %), so that
         # the in-place all-gather of the timed steps moves almost no padding
         with torch.cuda.stream(stream):
-            ctx.build_partitioned()
+            if sliced:
+                route_and_build()
+            else:
+                ctx.build_partitioned()
             used = torch.tensor([float(ctx.exchange_buffers()[0][2])], dtype=torch.float64, device=dev)
             dist.all_reduce(used, op=dist.ReduceOp.MAX)
             ctx.set_partition_chunk(int(used.item() * 1.02) + 4096)
@@ -500,6 +546,8 @@ def main():
             dist.send(torch.from_numpy(M).to(dev), dst=0)
         if rank == 0:
             ctx.set_shard(0, 1)
+            if sliced:
+                ctx.upload_index(P, G, F, Lc)             # rank 0 kept the whole F for this check
             ctx.build()                                   # the replicated, unsharded path on the same F
             ref = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
             ctx.set_shard(rank, world)
@@ -530,6 +578,8 @@ def main():
                    "genomes": G, "scps": P, "postings": nF, "pairs": pairs_total, "mode": "all-vs-all",
                    "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); F replicated "
                                    f"on every GPU (N>1, inside the e2e region: every rank uploads its 1/N slice of F, NCCL all-gather over NVLink); "
+                                   + ("routed build: every rank keeps only its 1/N slice of F, the postings go to the rank that owns their genome by "
+                                      "an NCCL all-to-all; " if sliced else "")
                                    + ("partitioned index build: every rank sorts / builds the column dictionaries of its own row blocks, "
                                       "the dictionaries are all-gathered over NVLink (NCCL, in place, on a second stream) while the tiles on the rank's "
                                       "own dictionaries are computed; " if partitioned else

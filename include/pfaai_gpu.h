@@ -140,6 +140,31 @@ int  pfaai_gpu_finish_partitioned(pfaai_gpu_ctx *ctx);
 int  pfaai_gpu_finish_partitioned_async(pfaai_gpu_ctx *ctx, void *cuda_event);
 /* exchange + finish for n_shards contexts of THIS process (any mix of devices), after each ran build_partitioned */
 int  pfaai_gpu_exchange_local(pfaai_gpu_ctx **ctxs, int n_shards);
+/* Routed build (sharded ALL_VS_ALL): no GPU ever holds the whole F.  Shard s is given postings [slice_begin, slice_begin + n_slice)
+ * of F (any cut of the array into consecutive slices, in shard order) and the full Lc:
+ *   pfaai_gpu_upload_index_slice / index_slice_buffers   host / device hand-over of the slice;
+ *   pfaai_gpu_route_prepare   turns the slice into sort items tagged with the shard that owns their genome and groups them by
+ *                             destination (one radix pass, input order kept): shard d gets items
+ *                             [send_offset[d], send_offset[d+1]) of send_dev (8 bytes each);
+ *   the caller moves them -- an all-to-all (NCCL over NVLink; counts from send_offset) into the buffer of
+ *   pfaai_gpu_route_recv_buffer, sources concatenated in shard order -- or pfaai_gpu_route_local for contexts of one process;
+ *   pfaai_gpu_build_routed    histogram, T, sort and the shard's own dictionaries from the received items; from here on the
+ *                             context is in the same state as after pfaai_gpu_build_partitioned (exchange, finish, compute).
+ * Per GPU this moves |F|/n postings in and out instead of holding all of F, and removes the filter passes over F. */
+typedef struct {
+    void   *send_dev;          /* device pointer: the slice's items grouped by destination shard                       */
+    int64_t send_offset[17];   /* shard d receives items [send_offset[d], send_offset[d+1])                            */
+    int32_t shard, n_shards;
+} pfaai_route_t;
+int  pfaai_gpu_upload_index_slice(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes, const pfaai_pg_t *F_slice, const int32_t *Lc,
+                                  int64_t nF_total, int64_t slice_begin, int64_t n_slice);
+int  pfaai_gpu_index_slice_buffers(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes, int64_t nF_total, int64_t slice_begin,
+                                   int64_t n_slice, void **F_slice_dev, void **Lc_dev);
+int  pfaai_gpu_route_prepare(pfaai_gpu_ctx *ctx, pfaai_route_t *out);
+int  pfaai_gpu_route_recv_buffer(pfaai_gpu_ctx *ctx, int64_t n_items, void **recv_dev);
+int  pfaai_gpu_build_routed(pfaai_gpu_ctx *ctx, int64_t n_items);
+/* prepare + peer copies + build_routed for the n_shards contexts (shards 0..n-1, in order) of THIS process */
+int  pfaai_gpu_route_local(pfaai_gpu_ctx **ctxs, int n_shards);
 /* Parity hooks (any pointer may be NULL): Lc/Lp [160000], T [P x G], and the genome-major index:
  * seg_off [G*P+1] (int64, segment g*P+p) and seg_vals [nF] (tetramers, ascending inside a segment). */
 int  pfaai_gpu_get_arrays(pfaai_gpu_ctx *ctx, int32_t *Lc, int32_t *Lp, int32_t *T,

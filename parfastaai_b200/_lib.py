@@ -29,6 +29,8 @@ EXPORTS = [
     "pfaai_gpu_n_pairs", "pfaai_gpu_get_timings", "pfaai_gpu_shard_layout", "pfaai_gpu_index_device_buffers",
     "pfaai_gpu_build_partitioned", "pfaai_gpu_exchange_buffers", "pfaai_gpu_finish_partitioned", "pfaai_gpu_exchange_local",
     "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
+    "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
+    "pfaai_gpu_build_routed", "pfaai_gpu_route_local",
 ]
 
 
@@ -45,6 +47,11 @@ class Exchange(C.Structure):
     """pfaai_exchange_t: the four buffers a partitioned build leaves to be all-gathered across the shards."""
     _fields_ = [("buf_dev", C.c_void_p * 4), ("chunk_bytes", C.c_int64 * 4), ("used_bytes", C.c_int64 * 4),
                 ("shard", C.c_int32), ("n_shards", C.c_int32)]
+
+
+class Route(C.Structure):
+    """pfaai_route_t: a slice's sort items grouped by destination shard."""
+    _fields_ = [("send_dev", C.c_void_p), ("send_offset", C.c_int64 * 17), ("shard", C.c_int32), ("n_shards", C.c_int32)]
 
 
 _lib = None
@@ -87,6 +94,12 @@ def load():
     L.pfaai_gpu_exchange_local.argtypes = [C.POINTER(vp), i32]
     L.pfaai_gpu_set_partition_chunk.argtypes = [vp, i64]
     L.pfaai_gpu_finish_partitioned_async.argtypes = [vp, vp]
+    L.pfaai_gpu_upload_index_slice.argtypes = [vp, i32, i32, vp, vp, i64, i64, i64]
+    L.pfaai_gpu_index_slice_buffers.argtypes = [vp, i32, i32, i64, i64, i64, C.POINTER(vp), C.POINTER(vp)]
+    L.pfaai_gpu_route_prepare.argtypes = [vp, C.POINTER(Route)]
+    L.pfaai_gpu_route_recv_buffer.argtypes = [vp, i64, C.POINTER(vp)]
+    L.pfaai_gpu_build_routed.argtypes = [vp, i64]
+    L.pfaai_gpu_route_local.argtypes = [C.POINTER(vp), i32]
     _lib = L
     return L
 
@@ -163,6 +176,44 @@ class PfaaiGpu:
 
     def build(self):
         self._check(self._L.pfaai_gpu_build(self._h), "build")
+
+    # ---- routed build: the context holds a slice of F, postings travel to the shard that owns their genome ----
+    def upload_index_slice(self, P, G, F_slice, Lc, nF_total, slice_begin):
+        F_slice = np.ascontiguousarray(F_slice, dtype=PG_DTYPE)
+        Lc = np.ascontiguousarray(Lc, dtype=np.int32)
+        self.P, self.G, self.nF = P, G, nF_total
+        self._check(self._L.pfaai_gpu_upload_index_slice(self._h, P, G, _p(F_slice), _p(Lc), nF_total, slice_begin, F_slice.shape[0]),
+                    "upload_index_slice")
+
+    def index_slice_buffers(self, P, G, nF_total, slice_begin, n_slice):
+        f, lc = C.c_void_p(), C.c_void_p()
+        self._check(self._L.pfaai_gpu_index_slice_buffers(self._h, P, G, nF_total, slice_begin, n_slice, C.byref(f), C.byref(lc)),
+                    "index_slice_buffers")
+        self.P, self.G, self.nF = P, G, nF_total
+        return f.value, lc.value
+
+    def route_prepare(self):
+        """-> (send device pointer, offsets [n_shards + 1]): shard d receives items [off[d], off[d+1]) (8 bytes each)."""
+        r = Route()
+        self._check(self._L.pfaai_gpu_route_prepare(self._h, C.byref(r)), "route_prepare")
+        return r.send_dev, [int(r.send_offset[d]) for d in range(r.n_shards + 1)]
+
+    def route_recv_buffer(self, n_items):
+        p = C.c_void_p()
+        self._check(self._L.pfaai_gpu_route_recv_buffer(self._h, int(n_items), C.byref(p)), "route_recv_buffer")
+        return p.value
+
+    def build_routed(self, n_items):
+        self._check(self._L.pfaai_gpu_build_routed(self._h, int(n_items)), "build_routed")
+
+    @staticmethod
+    def route_local(ctxs):
+        """route_prepare + peer copies + build_routed for the shards' contexts of this process (shards 0..n-1 in order)."""
+        L = load()
+        arr = (C.c_void_p * len(ctxs))(*[c._h for c in ctxs])
+        rc = L.pfaai_gpu_route_local(arr, len(ctxs))
+        if rc != 0:
+            raise PfaaiError(f"route_local rc={rc}: " + "; ".join(L.pfaai_gpu_last_error(c._h).decode() for c in ctxs))
 
     def build_partitioned(self):
         """Sharded all-vs-all: index part + dictionaries of this shard's own row blocks only (exchange, then finish)."""

@@ -207,6 +207,81 @@ __global__ void __launch_bounds__(MI_THREADS) k_make_items(const pfaai_pg_t *__r
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Routed build (pfaai_gpu_route_prepare): the context holds only a SLICE of F, postings [slice_begin, slice_begin + n) of
+// the global array.  Every posting becomes an item tagged with the shard that owns its genome,
+//     item = owner << 60 | (genome*P + protein) << 18 | tetramer,
+// and the number of items per owner is counted (one ballot round per shard, one atomic per warp and owner).  One onesweep
+// pass on the owner digit (shift 60) then groups the slice by destination, in input order; after the all-to-all every shard
+// holds exactly the items of its own genomes, in global posting order (sources arrive in slice order).
+// ------------------------------------------------------------------------------------------------
+constexpr int ROUTE_SHIFT = 60;
+constexpr int ROUTE_MAX_SHARDS = 16;
+constexpr uint64_t ROUTE_ITEM_MASK = (1ull << ROUTE_SHIFT) - 1;
+
+__global__ void __launch_bounds__(MI_THREADS) k_make_items_routed(const pfaai_pg_t *__restrict__ F, const int64_t *__restrict__ Lp,
+                                                                   int64_t slice_begin, int64_t n, int64_t nF_total, int P, int G,
+                                                                   const uint8_t *__restrict__ owner, int n_shards,
+                                                                   uint64_t *__restrict__ items,
+                                                                   unsigned long long *__restrict__ owner_cnt /*[256]*/,
+                                                                   int *__restrict__ err) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * MI_THREADS + threadIdx.x) >> 5;
+    const int64_t l0 = warp * (32 * MI_ITEMS);                 // local index of the warp's first posting
+    if (l0 == 0 && lane == 0 && Lp[NTETRA] != nF_total) *err = 2;   // sum(Lc) must equal |F|
+    if (l0 >= n) return;
+    const int64_t w0 = slice_begin + l0;                       // global posting index
+    const int64_t last = min(w0 + 32 * MI_ITEMS - 1, slice_begin + n - 1);
+    const int t0 = tetramer_of(Lp, 0, NTETRA - 1, w0);
+    const int tb = min(t0 + 1 + lane, NTETRA);
+    const int64_t bnd = Lp[tb];
+    const bool local = __shfl_sync(0xffffffffu, bnd, 31) > last || t0 + 32 >= NTETRA;
+    const int t_hi = local ? 0 : tetramer_of(Lp, t0, NTETRA - 1, last);
+    uint32_t cnt = 0;                                          // lane o accumulates the count of owner o
+#pragma unroll 4
+    for (int k = 0; k < MI_ITEMS; k++) {
+        const int64_t li = l0 + k * 32 + lane, i = slice_begin + li;
+        const bool valid = li < n;
+        int t;
+        if (local) {
+            int pos = 0;
+#pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) {
+                const int64_t b = __shfl_sync(0xffffffffu, bnd, pos + sft - 1);
+                if (b <= i) pos += sft;
+            }
+            t = min(t0 + pos, NTETRA - 1);
+        } else {
+            t = valid ? tetramer_of(Lp, t0, t_hi, i) : 0;
+        }
+        int o = -1;
+        if (valid) {
+            const pfaai_pg_t e = F[li];
+            uint32_t seg = (uint32_t)e.genome * (uint32_t)P + (uint32_t)e.protein;
+            o = 0;
+            // a bad id fails the build; the item still travels (to shard 0, segment 0) so that all counts stay consistent
+            if ((unsigned)e.protein >= (unsigned)P || (unsigned)e.genome >= (unsigned)G) { *err = 1; seg = 0u; }
+            else o = __ldg(owner + (e.genome >> OWN_SHIFT));
+            items[li] = ((uint64_t)o << ROUTE_SHIFT) | ((uint64_t)seg << TET_BITS) | (uint32_t)t;
+        }
+        for (int s = 0; s < n_shards; s++) {
+            const uint32_t b = __ballot_sync(0xffffffffu, o == s);
+            if (lane == s) cnt += __popc(b);
+        }
+    }
+    if (lane < n_shards && cnt) atomicAdd(&owner_cnt[lane], (unsigned long long)cnt);
+}
+
+// (genome, SCP) histogram of the routed items a shard received
+__global__ void __launch_bounds__(256) k_seg_hist(const uint64_t *__restrict__ items, int64_t n, int64_t nseg,
+                                                   uint32_t *__restrict__ seg_len, int *__restrict__ err) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint64_t seg = (items[i] & ROUTE_ITEM_MASK) >> TET_BITS;
+        if ((int64_t)seg >= nseg) { *err = 1; continue; }
+        atomicAdd(&seg_len[seg], 1u);
+    }
+}
+
 // T[p*G + g] = seg_len[g*P + p]; also the longest segment (sizes the bit-plane counters of the tile kernel)
 __global__ void k_transpose_t(const uint32_t *__restrict__ seg_len, int P, int G, int32_t *__restrict__ T,
                               int *__restrict__ max_len) {

@@ -44,6 +44,12 @@ struct Ctx {
     int64_t slot_cap = 0;                 // dictionary slots (column blocks) per shard chunk
     void *exch_event = nullptr;           // pfaai_gpu_finish_partitioned_async: the exchange is complete when this cudaEvent_t fires
     DevBuf tile_ctr;
+    // routed build: this context holds postings [slice_begin, slice_begin + n_slice) of F only
+    bool sliced = false;
+    int64_t slice_begin = 0, n_slice = 0, nF_total = 0;
+    int64_t route_off[17] = {};
+    float route_ms = 0.f;
+    DevBuf route_hist, recv;
     int64_t blob_chunk_hint = 0;          // pfaai_gpu_set_partition_chunk: agreed size of a shard's blob chunk (0: default bound)
     int64_t chunk_bytes[4] = {}, used_bytes[4] = {};   // exchange buffers: blob, stages, colT, stage_rng
     int64_t out_rows = 0, out_cols = 0;
@@ -115,12 +121,65 @@ static int read_flags(Ctx *c, int *flags_host /*[4]*/) {
     return PFAAI_OK;
 }
 
+// K2b + end of the build: sort the n_items items in `src` (ping-pong buffer `dst`) into c->vals, read the flags back
+static int sort_and_finish(Ctx *c, uint64_t *src, uint64_t *dst, int64_t n_items, bool partitioned) {
+    const int64_t nseg = (int64_t)c->P * c->G;
+    // K2b: stable LSD radix sort on (genome*P + protein), one onesweep kernel per 8-bit digit; the digit histograms
+    // of all passes come from the segment histogram; the last pass emits the tetramers only
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_S0], c->stream));
+    if (n_items > 0) {
+        int keybits = 1;
+        while (keybits < 31 && ((int64_t)1 << keybits) < nseg) keybits++;
+        const int passes = (keybits + 7) / 8;
+        const int64_t n_tiles = ceil_div64(n_items, OS_TILE);
+        const size_t control_bytes = sizeof(uint64_t) * (size_t)(8 + n_tiles * RS_RADIX);
+        PF_TRY(ensure(c, c->block_hist, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX));
+        PF_TRY(ensure(c, c->block_base, control_bytes));
+        PF_CUDA(c, cudaMemsetAsync(c->block_hist.p, 0, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX, c->stream));
+        k_digit_hist<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 256), (int64_t)c->sm_count * 2), 256, 0, c->stream>>>(
+            ptr<uint32_t>(c->seg_len), nseg, passes, ptr<unsigned long long>(c->block_hist));
+        PF_LAUNCH_CHECK(c);
+        k_digit_scan<<<passes, RS_RADIX, 0, c->stream>>>(ptr<unsigned long long>(c->block_hist));
+        PF_LAUNCH_CHECK(c);
+        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
+        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
+        for (int pass = 0; pass < passes; pass++) {
+            const int shift = TET_BITS + 8 * pass;
+            const unsigned long long *base = ptr<unsigned long long>(c->block_hist) + (size_t)pass * RS_RADIX;
+            PF_CUDA(c, cudaMemsetAsync(c->block_base.p, 0, control_bytes, c->stream));
+            if (pass == passes - 1)
+                k_onesweep<true><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, n_items, shift, base, ptr<uint64_t>(c->block_base),
+                                                                                        nullptr, ptr<uint32_t>(c->vals));
+            else
+                k_onesweep<false><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, n_items, shift, base, ptr<uint64_t>(c->block_base),
+                                                                                         dst, nullptr);
+            PF_LAUNCH_CHECK(c);
+            std::swap(src, dst);
+        }
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_S1], c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B1], c->stream));
+    int fl[4];
+    PF_TRY(read_flags(c, fl));
+    if (fl[0] == 2) { set_error(c, "build: sum(Lc) != |F|"); return PFAAI_ERR_CONSTRUCT; }
+    if (fl[0]) { set_error(c, "build: posting with protein/genome id out of range"); return PFAAI_ERR_CONSTRUCT; }
+    c->max_len = fl[1];
+    c->tm.build_ms = ev_ms(c, EV_B0, EV_B1);
+    c->tm.sort_ms = ev_ms(c, EV_S0, EV_S1);
+    c->tm.n_launches = c->launches;
+    c->built = true;
+    c->partitioned = partitioned;
+    return PFAAI_OK;
+}
+
+
 // K1-K3 + K2b.  partitioned: only the postings of the genomes this shard owns (the genomes of its row blocks) are turned into
 // sort items (order-preserving compaction in two passes over F), so histogram atomics, sort and the genome-major lists shrink
 // by the number of shards; seg_off / T keep their global indexing (non-owned segments are empty, non-owned T columns 0).
 static int build_internal(Ctx *c, bool partitioned) {
     if (!c) return PFAAI_ERR_CONSTRUCT;
     if (!c->uploaded) { set_error(c, "build: no index uploaded"); return PFAAI_ERR_CONSTRUCT; }
+    if (c->sliced) { set_error(c, "build: the context holds a slice of F (use pfaai_gpu_route_prepare / pfaai_gpu_build_routed)"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
     const int P = c->P, G = c->G;
     const int64_t nF = c->nF, nseg = (int64_t)P * G;
@@ -173,53 +232,7 @@ static int build_internal(Ctx *c, bool partitioned) {
                                                                           c->host_T ? nullptr : ptr<int32_t>(c->T),
                                                                           ptr<int>(c->flags) + 1);
     PF_LAUNCH_CHECK(c);
-    // K2b: stable LSD radix sort on (genome*P + protein), one onesweep kernel per 8-bit digit; the digit histograms
-    // of all passes come from the segment histogram; the last pass emits the tetramers only
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_S0], c->stream));
-    if (n_items > 0) {
-        int keybits = 1;
-        while (keybits < 31 && ((int64_t)1 << keybits) < nseg) keybits++;
-        const int passes = (keybits + 7) / 8;
-        const int64_t n_tiles = ceil_div64(n_items, OS_TILE);
-        const size_t control_bytes = sizeof(uint64_t) * (size_t)(8 + n_tiles * RS_RADIX);
-        PF_TRY(ensure(c, c->block_hist, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX));
-        PF_TRY(ensure(c, c->block_base, control_bytes));
-        PF_CUDA(c, cudaMemsetAsync(c->block_hist.p, 0, sizeof(unsigned long long) * MAX_PASSES * RS_RADIX, c->stream));
-        k_digit_hist<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 256), (int64_t)c->sm_count * 2), 256, 0, c->stream>>>(
-            ptr<uint32_t>(c->seg_len), nseg, passes, ptr<unsigned long long>(c->block_hist));
-        PF_LAUNCH_CHECK(c);
-        k_digit_scan<<<passes, RS_RADIX, 0, c->stream>>>(ptr<unsigned long long>(c->block_hist));
-        PF_LAUNCH_CHECK(c);
-        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
-        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
-        uint64_t *src = ptr<uint64_t>(c->itemsA), *dst = ptr<uint64_t>(c->itemsB);
-        for (int pass = 0; pass < passes; pass++) {
-            const int shift = TET_BITS + 8 * pass;
-            const unsigned long long *base = ptr<unsigned long long>(c->block_hist) + (size_t)pass * RS_RADIX;
-            PF_CUDA(c, cudaMemsetAsync(c->block_base.p, 0, control_bytes, c->stream));
-            if (pass == passes - 1)
-                k_onesweep<true><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, n_items, shift, base, ptr<uint64_t>(c->block_base),
-                                                                                        nullptr, ptr<uint32_t>(c->vals));
-            else
-                k_onesweep<false><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(src, n_items, shift, base, ptr<uint64_t>(c->block_base),
-                                                                                         dst, nullptr);
-            PF_LAUNCH_CHECK(c);
-            std::swap(src, dst);
-        }
-    }
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_S1], c->stream));
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_B1], c->stream));
-    int fl[4];
-    PF_TRY(read_flags(c, fl));
-    if (fl[0] == 2) { set_error(c, "build: sum(Lc) != |F|"); return PFAAI_ERR_CONSTRUCT; }
-    if (fl[0]) { set_error(c, "build: posting with protein/genome id out of range"); return PFAAI_ERR_CONSTRUCT; }
-    c->max_len = fl[1];
-    c->tm.build_ms = ev_ms(c, EV_B0, EV_B1);
-    c->tm.sort_ms = ev_ms(c, EV_S0, EV_S1);
-    c->tm.n_launches = c->launches;
-    c->built = true;
-    c->partitioned = partitioned;
-    return PFAAI_OK;
+    return sort_and_finish(c, ptr<uint64_t>(c->itemsA), ptr<uint64_t>(c->itemsB), n_items, partitioned);
 }
 
 static int build_own_dictionaries(Ctx *c);
@@ -272,7 +285,7 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
                      &c->tile_sums, &c->block_hist, &c->block_base, &c->flags, &c->rows, &c->row_t, &c->cols, &c->col_t,
                      &c->ell_nch, &c->ell_off, &c->ell, &c->tiles, &c->out, &c->S_out, &c->N_out, &c->counts_out,
                      &c->nsub, &c->sub, &c->colT, &c->blob, &c->stage_off, &c->stages, &c->stage_rng,
-                     &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr};
+                     &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr, &c->route_hist, &c->recv};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
@@ -310,7 +323,7 @@ int pfaai_gpu_upload_index(pfaai_gpu_ctx *h, int P, int G, const pfaai_pg_t *F, 
     if (P <= 0 || G <= 0 || nF < 0 || !Lc || (nF > 0 && !F)) { set_error(c, "upload_index: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
     if ((int64_t)P * G >= (1ll << 31)) { set_error(c, "upload_index: P*G too large"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
-    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false;
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false;
     PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
@@ -330,7 +343,7 @@ int pfaai_gpu_index_device_buffers(pfaai_gpu_ctx *h, int P, int G, int64_t nF, i
     if (!c) return PFAAI_ERR_CONSTRUCT;
     if (P <= 0 || G <= 0 || nF < 0 || (int64_t)P * G >= (1ll << 31)) { set_error(c, "index_device_buffers: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
-    c->P = P; c->G = G; c->nF = nF; c->host_T = (host_T != 0); c->built = false; c->uploaded = false;
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (host_T != 0); c->built = false; c->uploaded = false; c->sliced = false;
     PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
@@ -422,6 +435,169 @@ int pfaai_gpu_exchange_local(pfaai_gpu_ctx **hs, int n) {
     return PFAAI_OK;
 }
 
+// ---- routed build: every shard holds a slice of F; postings travel to the shard that owns their genome ------------------
+int pfaai_gpu_index_slice_buffers(pfaai_gpu_ctx *h, int P, int G, int64_t nF_total, int64_t slice_begin, int64_t n_slice,
+                                  void **F_slice_dev, void **Lc_dev) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (P <= 0 || G <= 0 || nF_total < 0 || slice_begin < 0 || n_slice < 0 || slice_begin + n_slice > nF_total || (int64_t)P * G >= (1ll << 31)) {
+        set_error(c, "index_slice_buffers: bad arguments"); return PFAAI_ERR_CONSTRUCT;
+    }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    c->P = P; c->G = G; c->nF = nF_total; c->nF_total = nF_total; c->host_T = false; c->built = false; c->uploaded = false;
+    c->sliced = true; c->slice_begin = slice_begin; c->n_slice = n_slice;
+    PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)n_slice));
+    PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
+    if (F_slice_dev) *F_slice_dev = c->F.p;
+    if (Lc_dev) *Lc_dev = c->Lc.p;
+    c->tm.h2d_ms = 0.f;
+    c->uploaded = true;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_upload_index_slice(pfaai_gpu_ctx *h, int P, int G, const pfaai_pg_t *F_slice, const int32_t *Lc, int64_t nF_total,
+                                 int64_t slice_begin, int64_t n_slice) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !Lc || (n_slice > 0 && !F_slice)) { set_error(c, "upload_index_slice: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
+    PF_TRY(pfaai_gpu_index_slice_buffers(h, P, G, nF_total, slice_begin, n_slice, nullptr, nullptr));
+    c->uploaded = false;
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D0], c->stream));
+    if (n_slice > 0) PF_CUDA(c, cudaMemcpyAsync(c->F.p, F_slice, sizeof(pfaai_pg_t) * (size_t)n_slice, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(c->Lc.p, Lc, sizeof(int32_t) * NTETRA, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D1], c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->tm.h2d_ms = ev_ms(c, EV_H2D0, EV_H2D1);
+    c->uploaded = true;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_route_prepare(pfaai_gpu_ctx *h, pfaai_route_t *out) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !out) return PFAAI_ERR_CONSTRUCT;
+    if (!c->uploaded || !c->sliced) { set_error(c, "route_prepare: no index slice uploaded"); return PFAAI_ERR_CONSTRUCT; }
+    if (c->n_shards < 2 || c->n_shards > ROUTE_MAX_SHARDS) { set_error(c, "route_prepare: needs 2..16 shards (pfaai_gpu_set_shard)"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    const int P = c->P, G = c->G, n = c->n_shards;
+    const int64_t ns = c->n_slice;
+    c->launches = 0;
+    c->built = false; c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr;
+    PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
+    PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->itemsA, sizeof(uint64_t) * (size_t)ns));
+    PF_TRY(ensure(c, c->itemsB, sizeof(uint64_t) * (size_t)ns));
+    PF_TRY(ensure(c, c->route_hist, sizeof(unsigned long long) * RS_RADIX));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B0], c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->flags.p, 0, 64, c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->route_hist.p, 0, sizeof(unsigned long long) * RS_RADIX, c->stream));
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->Lc), NTETRA, ptr<int64_t>(c->Lp64), ptr<int32_t>(c->Lp32)));
+    const int ngran = (G + (1 << OWN_SHIFT) - 1) >> OWN_SHIFT;
+    std::vector<uint8_t> own(ngran);
+    for (int i = 0; i < ngran; i++) own[i] = (uint8_t)fold_owner((int)(((int64_t)i << OWN_SHIFT) / TILE_ROWS), n);
+    PF_TRY(ensure(c, c->owner_tbl, (size_t)ngran));
+    PF_CUDA(c, cudaMemcpyAsync(c->owner_tbl.p, own.data(), (size_t)ngran, cudaMemcpyHostToDevice, c->stream));
+    unsigned long long base[RS_RADIX] = {};
+    if (ns > 0) {
+        k_make_items_routed<<<(unsigned)ceil_div64(ns, (int64_t)MI_THREADS * MI_ITEMS), MI_THREADS, 0, c->stream>>>(
+            ptr<pfaai_pg_t>(c->F), ptr<int64_t>(c->Lp64), c->slice_begin, ns, c->nF_total, P, G, ptr<uint8_t>(c->owner_tbl), n,
+            ptr<uint64_t>(c->itemsA), ptr<unsigned long long>(c->route_hist), ptr<int>(c->flags));
+        PF_LAUNCH_CHECK(c);
+        k_digit_scan<<<1, RS_RADIX, 0, c->stream>>>(ptr<unsigned long long>(c->route_hist));     // counts -> exclusive bases
+        PF_LAUNCH_CHECK(c);
+        // stable partition by owner: one onesweep pass on the owner digit
+        const int64_t n_tiles = ceil_div64(ns, OS_TILE);
+        const size_t control_bytes = sizeof(uint64_t) * (size_t)(8 + n_tiles * RS_RADIX);
+        PF_TRY(ensure(c, c->block_base, control_bytes));
+        PF_CUDA(c, cudaMemsetAsync(c->block_base.p, 0, control_bytes, c->stream));
+        PF_CUDA(c, cudaFuncSetAttribute(k_onesweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_SMEM));
+        k_onesweep<false><<<(unsigned)n_tiles, OS_THREADS, OS_SMEM, c->stream>>>(ptr<uint64_t>(c->itemsA), ns, ROUTE_SHIFT,
+                                                                                 ptr<unsigned long long>(c->route_hist),
+                                                                                 ptr<uint64_t>(c->block_base), ptr<uint64_t>(c->itemsB), nullptr);
+        PF_LAUNCH_CHECK(c);
+        PF_CUDA(c, cudaMemcpyAsync(base, c->route_hist.p, sizeof(base), cudaMemcpyDeviceToHost, c->stream));
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B1], c->stream));
+    int fl[4];
+    PF_TRY(read_flags(c, fl));
+    if (fl[0] == 2) { set_error(c, "route_prepare: sum(Lc) != |F|"); return PFAAI_ERR_CONSTRUCT; }
+    if (fl[0]) { set_error(c, "route_prepare: posting with protein/genome id out of range"); return PFAAI_ERR_CONSTRUCT; }
+    for (int d = 0; d < n; d++) c->route_off[d] = (int64_t)base[d];
+    c->route_off[n] = ns;
+    c->route_ms = ev_ms(c, EV_B0, EV_B1);
+    out->send_dev = c->itemsB.p; out->n_shards = n; out->shard = c->shard;
+    for (int d = 0; d <= ROUTE_MAX_SHARDS; d++) out->send_offset[d] = d <= n ? c->route_off[d] : ns;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_route_recv_buffer(pfaai_gpu_ctx *h, int64_t n_items, void **recv_dev) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || n_items < 0 || !recv_dev) { set_error(c, "route_recv_buffer: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    PF_TRY(ensure(c, c->recv, sizeof(uint64_t) * (size_t)n_items));
+    *recv_dev = c->recv.p;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_build_routed(pfaai_gpu_ctx *h, int64_t n_items) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !c->sliced || !c->uploaded || n_items < 0) { set_error(c, "build_routed: no routed items"); return PFAAI_ERR_CONSTRUCT; }
+    if (c->recv.cap < sizeof(uint64_t) * (size_t)n_items) { set_error(c, "build_routed: more items than the receive buffer holds"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    const int P = c->P, G = c->G;
+    const int64_t nseg = (int64_t)P * G;
+    PF_TRY(ensure(c, c->seg_len, sizeof(uint32_t) * (size_t)nseg));
+    PF_TRY(ensure(c, c->seg_off, sizeof(int64_t) * (size_t)(nseg + 1)));
+    PF_TRY(ensure(c, c->itemsA, sizeof(uint64_t) * (size_t)n_items));
+    PF_TRY(ensure(c, c->vals, sizeof(uint32_t) * (size_t)n_items));
+    c->nF_owned = n_items;
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B0], c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->flags.p, 0, 64, c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->seg_len.p, 0, sizeof(uint32_t) * (size_t)nseg, c->stream));
+    if (n_items > 0) {
+        k_seg_hist<<<(unsigned)std::min<int64_t>(ceil_div64(n_items, 256), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
+            ptr<uint64_t>(c->recv), n_items, nseg, ptr<uint32_t>(c->seg_len), ptr<int>(c->flags));
+        PF_LAUNCH_CHECK(c);
+    }
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->seg_len), nseg, ptr<int64_t>(c->seg_off), nullptr));
+    k_transpose_t<<<(unsigned)ceil_div64(nseg, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->seg_len), P, G, ptr<int32_t>(c->T),
+                                                                          ptr<int>(c->flags) + 1);
+    PF_LAUNCH_CHECK(c);
+    PF_TRY(sort_and_finish(c, ptr<uint64_t>(c->recv), ptr<uint64_t>(c->itemsA), n_items, true));
+    c->tm.build_ms += c->route_ms;
+    PF_TRY(build_own_dictionaries(c));
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_route_local(pfaai_gpu_ctx **hs, int n) {
+    if (!hs || n < 2 || n > ROUTE_MAX_SHARDS) return PFAAI_ERR_CONSTRUCT;
+    std::vector<Ctx *> cs(n);
+    std::vector<pfaai_route_t> rt(n);
+    for (int i = 0; i < n; i++) {
+        cs[i] = reinterpret_cast<Ctx *>(hs[i]);
+        if (!cs[i] || cs[i]->n_shards != n || cs[i]->shard != i) { set_error(cs[i], "route_local: contexts must be the shards 0..n-1 in order"); return PFAAI_ERR_CONSTRUCT; }
+        PF_TRY(pfaai_gpu_route_prepare(hs[i], &rt[i]));
+    }
+    for (int d = 0; d < n; d++) {
+        Ctx *dst = cs[d];
+        int64_t total = 0;
+        for (int si = 0; si < n; si++) total += rt[si].send_offset[d + 1] - rt[si].send_offset[d];
+        void *recv = nullptr;
+        PF_TRY(pfaai_gpu_route_recv_buffer(hs[d], total, &recv));
+        int64_t at = 0;
+        for (int si = 0; si < n; si++) {                    // sources in slice order: global posting order is preserved
+            const int64_t cnt = rt[si].send_offset[d + 1] - rt[si].send_offset[d];
+            if (cnt > 0)
+                PF_CUDA(dst, cudaMemcpyPeerAsync(static_cast<uint64_t *>(recv) + at, dst->device,
+                                                 static_cast<uint64_t *>(rt[si].send_dev) + rt[si].send_offset[d], cs[si]->device,
+                                                 sizeof(uint64_t) * (size_t)cnt, dst->stream));
+            at += cnt;
+        }
+        PF_CUDA(dst, cudaStreamSynchronize(dst->stream));
+        PF_TRY(pfaai_gpu_build_routed(hs[d], total));
+    }
+    return PFAAI_OK;
+}
+
 int pfaai_gpu_get_arrays(pfaai_gpu_ctx *h, int32_t *Lc, int32_t *Lp, int32_t *T, int64_t *seg_off, int32_t *seg_vals) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     if (!c || !c->built) { set_error(c, "get_arrays: index not built"); return PFAAI_ERR_CONSTRUCT; }
@@ -431,8 +607,9 @@ int pfaai_gpu_get_arrays(pfaai_gpu_ctx *h, int32_t *Lc, int32_t *Lp, int32_t *T,
     if (Lp) PF_CUDA(c, cudaMemcpyAsync(Lp, c->Lp32.p, sizeof(int32_t) * NTETRA, cudaMemcpyDeviceToHost, c->stream));
     if (T) PF_CUDA(c, cudaMemcpyAsync(T, c->T.p, sizeof(int32_t) * nseg, cudaMemcpyDeviceToHost, c->stream));
     if (seg_off) PF_CUDA(c, cudaMemcpyAsync(seg_off, c->seg_off.p, sizeof(int64_t) * (nseg + 1), cudaMemcpyDeviceToHost, c->stream));
-    if (seg_vals && c->nF > 0)
-        PF_CUDA(c, cudaMemcpyAsync(seg_vals, c->vals.p, sizeof(int32_t) * (size_t)c->nF, cudaMemcpyDeviceToHost, c->stream));
+    const int64_t n_vals = c->partitioned ? c->nF_owned : c->nF;   // a partitioned / routed context holds its own genomes' lists only
+    if (seg_vals && n_vals > 0)
+        PF_CUDA(c, cudaMemcpyAsync(seg_vals, c->vals.p, sizeof(int32_t) * (size_t)n_vals, cudaMemcpyDeviceToHost, c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
     return PFAAI_OK;
 }

@@ -266,6 +266,58 @@ def test_partitioned_build_matches_the_replicated_build(pf, orc, n_shards, N, P)
     ref.close()
 
 
+@pytest.mark.parametrize("n_shards,N,P,cuts", [(2, 1000, 3, None), (3, 1700, 2, [0.1, 0.75]), (4, 900, 4, None)])
+def test_routed_build_matches_the_replicated_build(pf, orc, n_shards, N, P, cuts):
+    """Routed build: every shard is given a slice of F only; the items are grouped by owner, moved (peer copies here, an NCCL
+    all-to-all in bench.py) and sorted by the shard that owns the genome.  The genome-major lists, T and every shard matrix must
+    equal the replicated build's, for equal and for ragged slices (incl. an empty shard: 900 genomes / 4 shards)."""
+    from parfastaai_b200 import sharding, synth
+    off, vals = synth.generate(N, P, seed=91)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    nF = F.shape[0]
+    bounds = [0] + ([int(c * nF) for c in cuts] if cuts else [nF * (s + 1) // n_shards for s in range(n_shards - 1)]) + [nF]
+    ref = pf.PfaaiGpu(0)
+    ref.upload_index(P, N, F, Lc)
+    ref.build()
+    ra = ref.get_arrays()
+    ctxs = []
+    for s in range(n_shards):
+        c = pf.PfaaiGpu(0)
+        c.set_shard(s, n_shards)
+        c.upload_index_slice(P, N, F[bounds[s]:bounds[s + 1]], Lc, nF, bounds[s])
+        with pytest.raises(pf.PfaaiError):          # a slice cannot be built without routing
+            c.build()
+        ctxs.append(c)
+    _, offs = ctxs[0].route_prepare()
+    assert offs[0] == 0 and offs[-1] == bounds[1] - bounds[0] and all(a <= b for a, b in zip(offs, offs[1:]))
+    pf.PfaaiGpu.route_local(ctxs)
+    pf.PfaaiGpu.exchange_local(ctxs)
+    parts, lay = [], []
+    for s, c in enumerate(ctxs):
+        ids = sharding.owned_indices(N, s, n_shards)
+        arr = c.get_arrays()
+        assert np.array_equal(arr["Lp"], ra["Lp"])
+        assert np.array_equal(arr["T"][:, ids], T[:, ids]) and not arr["T"][:, np.setdiff1d(np.arange(N), ids)].any()
+        # the shard's genome-major lists: same segments, same tetramers in the same order as the replicated sort
+        so, sv = arr["seg_off"], arr["seg_vals"]
+        for g in ids[:: max(1, len(ids) // 40)]:
+            for p in range(P):
+                k = g * P + p
+                assert np.array_equal(sv[so[k]:so[k + 1]], ra["seg_vals"][ra["seg_off"][k]:ra["seg_off"][k + 1]])
+        assert so[-1] == sum(int(ra["seg_off"][(g + 1) * P] - ra["seg_off"][g * P]) for g in ids)
+        part = c.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+        ref.set_shard(s, n_shards)
+        assert np.array_equal(part, ref.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"])
+        parts.append(part.copy()); lay.append(ids)
+    ref.set_shard(0, 1)
+    full = ref.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+    assert np.array_equal(sharding.assemble(pf.ALL_VS_ALL, parts, lay, np.empty((N, N))), full)
+    for c in ctxs:
+        c.close()
+    ref.close()
+
+
 def test_pinned_host_matrix_is_stored_directly_and_identically(pf, orc):
     """pfaai_gpu_compute with a page-locked matrix: the tile kernel stores straight into host memory (no device copy
     of the matrix, no D2H call); the bytes must equal the staged path's in all three modes, ragged tile edges included."""
