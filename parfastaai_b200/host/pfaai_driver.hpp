@@ -116,16 +116,23 @@ class DataStructBase {
         m_ctxs.assign(n, nullptr);
         std::vector<int> rcs(n, PFAAI_OK);
         std::vector<std::string> errs(n);
-        // several GPUs, all-vs-all: partitioned build -- every GPU sorts the postings and builds the column dictionaries of its
-        // own row blocks only, the parts are exchanged by peer copies (pfaai_gpu_exchange_local); otherwise replicated build
+        // several GPUs, all-vs-all: routed + partitioned build -- every GPU gets a slice of F, sorts the postings and builds the
+        // column dictionaries of its own row blocks only; postings and dictionaries move by peer copies; otherwise replicated build
         const bool partitioned = n > 1 && mode() == PFAAI_ALL_VS_ALL && !m_hostT;
         auto work = [&](int k) {
             int rc = pfaai_gpu_create(&m_ctxs[k], m_devices[k], 0);
             if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(nullptr); return; }
-            rc = pfaai_gpu_upload_index(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(),
-                                        m_hostT ? m_ix.T.data() : nullptr);
-            if (rc == PFAAI_OK) rc = pfaai_gpu_set_shard(m_ctxs[k], k, n);
-            if (rc == PFAAI_OK) rc = partitioned ? pfaai_gpu_build_partitioned(m_ctxs[k]) : pfaai_gpu_build(m_ctxs[k]);
+            rc = pfaai_gpu_set_shard(m_ctxs[k], k, n);
+            if (rc == PFAAI_OK && partitioned) {
+                // routed build: GPU k receives only the k-th slice of F (|F| bytes cross PCIe once, not once per GPU); the
+                // postings are routed to the GPU that owns their genome afterwards (pfaai_gpu_route_local)
+                const int64_t nF = (int64_t)m_ix.F.size(), lo = nF * k / n, hi = nF * (k + 1) / n;
+                rc = pfaai_gpu_upload_index_slice(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, m_ix.F.data() + lo, m_ix.Lc.data(), nF, lo, hi - lo);
+            } else if (rc == PFAAI_OK) {
+                rc = pfaai_gpu_upload_index(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(),
+                                            m_hostT ? m_ix.T.data() : nullptr);
+                if (rc == PFAAI_OK) rc = pfaai_gpu_build(m_ctxs[k]);
+            }
             if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(m_ctxs[k]); }
         };
         {
@@ -141,9 +148,15 @@ class DataStructBase {
             }
         pfaai_gpu_ctx *m_ctx = m_ctxs[0];
         int rc;
-        if (partitioned && (rc = pfaai_gpu_exchange_local(m_ctxs.data(), n)) != PFAAI_OK) {
-            std::cerr << "Error in device index exchange ; " << pfaai_gpu_last_error(m_ctx) << std::endl;
-            return m_errorCode = (pfaai_status)rc;
+        if (partitioned) {
+            rc = pfaai_gpu_route_local(m_ctxs.data(), n);                       // group by owner, peer copies, sort + own dictionaries
+            if (rc == PFAAI_OK) rc = pfaai_gpu_exchange_local(m_ctxs.data(), n);  // dictionaries to every GPU
+            if (rc != PFAAI_OK) {
+                std::string msg;
+                for (int k = 0; k < n; k++) { const char *e = pfaai_gpu_last_error(m_ctxs[k]); if (e && *e) { msg = e; break; } }
+                std::cerr << "Error in device index routing / exchange ; " << msg << std::endl;
+                return m_errorCode = (pfaai_status)rc;
+            }
         }
         m_Lp.resize(NTETRAMERS);
         std::vector<int32_t> Tdev((size_t)m_ix.nProteins * m_ix.nGenomes);
