@@ -168,6 +168,115 @@ def test_synthetic_subset_and_query_db_vs_oracle(pf, orc):
     ctx.close()
 
 
+def _lists_to_arrays(lists, N, P):
+    """lists[g][p] = ascending unique tetramers -> genome-major (seg_off, vals)"""
+    lens = np.array([len(lists[g][p]) for g in range(N) for p in range(P)], np.int64)
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    vals = np.concatenate([np.asarray(lists[g][p], np.int32) for g in range(N) for p in range(P)] + [np.zeros(0, np.int32)])
+    return off, vals.astype(np.int32)
+
+
+def test_ragged_and_empty_inputs_vs_oracle(pf, orc):
+    """Edge cases of the domain: genomes without any posting, SCPs missing from some genomes, a genome that shares no tetramer
+    with anyone (N = 0 -> AJI 0), empty lists next to long ones; all three modes against the oracle."""
+    from parfastaai_b200 import synth
+    rng = np.random.default_rng(5)
+    N, P = 90, 6
+    lists = [[np.unique(rng.integers(0, 3000, rng.integers(0, 400))).astype(np.int32) for p in range(P)] for g in range(N)]
+    for g in (3, 17):
+        lists[g] = [np.zeros(0, np.int32)] * P
+    for g in range(0, N, 5):
+        lists[g][2] = np.zeros(0, np.int32)
+    lists[40] = [np.arange(100000 + 10 * p, 100000 + 10 * p + 5, dtype=np.int32) for p in range(P)]
+    off, vals = _lists_to_arrays(lists, N, P)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    a = ctx.get_arrays()
+    assert np.array_equal(a["T"], T) and np.array_equal(a["seg_off"], off) and np.array_equal(a["seg_vals"], vals)
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, N, P, Lc, F, T)
+    assert (ref["jac"]["N"] == 0).sum() >= 89 + 88          # the isolated genome and the empty ones
+    assert np.array_equal(res["counts"], ref["counts"]) and np.array_equal(res["jac"]["N"], ref["jac"]["N"])
+    assert np.array_equal(res["aji"], ref["aji"]) and np.array_equal(res["matrix"], ref["matrix"])
+    # isolated, empty and ragged genomes as queries; in database order (the reference's genomePairToIndex, ds_impl.hpp:251-263,
+    # is only defined for query lists whose order agrees with the genome ids)
+    qids = np.array([0, 3, 5, 40, 89], np.int32)
+    res = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.QUERY_SUBSET, N, P, Lc, F, T, nQ=len(qids), qry_ids=qids)
+    assert np.array_equal(res["counts"], ref["counts"]) and np.array_equal(res["matrix"], ref["matrix"])
+    ctx.close()
+
+
+def test_empty_index_and_bad_input_fail_or_zero(pf, orc):
+    """|F| = 0 gives an all-zero matrix; a posting with an id out of range or sum(Lc) != |F| fails the build loudly."""
+    from parfastaai_b200 import synth
+    N, P = 10, 3
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, np.zeros(0, pf.PG_DTYPE), np.zeros(pf.NTETRA, np.int32))
+    ctx.build()
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True)
+    assert not res["matrix"].any() and not res["jac"]["N"].any() and not res["aji"].any()
+    off, vals = synth.generate(N, P, seed=2)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    bad = F.copy(); bad["genome"][7] = N
+    ctx.upload_index(P, N, bad, Lc)
+    with pytest.raises(pf.PfaaiError, match="out of range"):
+        ctx.build()
+    bad = F.copy(); bad["protein"][11] = -1
+    ctx.upload_index(P, N, bad, Lc)
+    with pytest.raises(pf.PfaaiError, match="out of range"):
+        ctx.build()
+    Lc2 = Lc.copy(); Lc2[int(np.flatnonzero(Lc)[0])] += 1
+    ctx.upload_index(P, N, F, Lc2)
+    with pytest.raises(pf.PfaaiError, match="sum"):
+        ctx.build()
+    with pytest.raises(pf.PfaaiError):                       # nothing built: compute refuses
+        ctx.compute(pf.ALL_VS_ALL, want_jac=False)
+    ctx.upload_index(P, N, F, Lc)                            # and the context recovers
+    ctx.build()
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, N, P, Lc, F, synth.t_matrix(N, P, off))
+    assert np.array_equal(ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], ref["matrix"])
+    ctx.close()
+
+
+def test_long_lists_and_many_scps_take_the_wide_kernel_variants(pf, orc):
+    """Maximum sizes: lists beyond 1022 tetramers select the 12-plane counters, more than 127 SCPs the 10-plane N counter
+    (aji_tile_kernel<12,7> / <9,10>); both against the oracle, counts included."""
+    from parfastaai_b200 import synth
+    rng = np.random.default_rng(9)
+    N, P = 70, 2                                             # lists of 1100-2500 tetramers sharing a common core
+    core = [np.unique(rng.integers(0, 160000, 2400)) for p in range(P)]
+    lists = [[np.unique(np.concatenate([core[p][rng.random(core[p].shape[0]) < 0.8], rng.integers(0, 160000, 300)])).astype(np.int32)
+              for p in range(P)] for g in range(N)]
+    assert max(len(x) for l in lists for x in l) > 1100
+    off, vals = _lists_to_arrays(lists, N, P)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, N, P, Lc, F, T)
+    assert ref["counts"].max() > 1022
+    assert np.array_equal(res["counts"], ref["counts"]) and np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    N, P = 66, 140                                           # > 127 SCPs
+    off, vals = synth.generate(N, P, seed=14)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True)
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, N, P, Lc, F, T)
+    assert ref["jac"]["N"].max() > 127
+    assert np.array_equal(res["jac"]["N"], ref["jac"]["N"]) and np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    ctx.close()
+
+
 @pytest.mark.parametrize("n_shards", [2, 3])
 def test_sharded_row_blocks_assemble_to_the_full_matrix(pf, orc, n_shards):
     """Row-block sharding: every shard stores only its own blocks of 384 target genomes, compactly; the host
