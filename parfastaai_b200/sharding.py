@@ -43,6 +43,34 @@ def pair_count(mode: int, n_genomes: int, n_qry: int, shard: int, n_shards: int,
     return r * c
 
 
+# ---- partitioned / routed build (include/pfaai_gpu.h, pfaai_gpu_build_partitioned): where a column block's dictionary lives ----
+COLS = 64            # == COLS_PER_TILE: genomes per column block
+RB_CBS = BLOCK // COLS   # column blocks per row block
+
+
+def slots_per_shard(n_genomes: int, n_shards: int) -> int:
+    """Dictionary slots in one shard's chunk of the exchange buffers: the largest number of row blocks any shard owns x 6."""
+    nb = (n_genomes + BLOCK - 1) // BLOCK
+    per = [0] * n_shards
+    for b in range(nb):
+        per[owner(b, n_shards)] += 1
+    return max(per) * RB_CBS
+
+
+def slot_of_column_block(J: int, n_genomes: int, n_shards: int) -> int:
+    """Slot (index into the all-gathered stage-range / column-T tables) of column block J: the shard that owns J's row block
+    built it, as the k-th column block of its own list (ascending), into chunk `owner` of every exchange buffer."""
+    I = J // RB_CBS
+    o = owner(I, n_shards)
+    before = sum(1 for b in range(I) if owner(b, n_shards) == o)
+    return o * slots_per_shard(n_genomes, n_shards) + before * RB_CBS + (J - I * RB_CBS)
+
+
+def owned_column_blocks(n_genomes: int, shard: int, n_shards: int):
+    ncb = (n_genomes + COLS - 1) // COLS
+    return [J for J in range(ncb) if owner(J // RB_CBS, n_shards) == shard]
+
+
 def assemble(mode: int, parts, layouts, out: np.ndarray) -> np.ndarray:
     """Scatter the shards' compact matrices into the dense output `out` (zero-initialised by the caller or not: every
     cell is written).  parts[i] is shard i's matrix, layouts[i] its global indices along the sharded axis."""

@@ -47,6 +47,54 @@ def _worker(rank, world, port, N, q):
     dist.destroy_process_group()
 
 
+def _exchange_worker(rank, world, port, G, q):
+    """The in-place chunk all-gather of the partitioned build, on CPU: every rank fills its chunk of a slot table with the ids of
+    the column blocks it built (position k of its own list), all_gather_into_tensor-style exchange, then every column block must
+    be found at slot_of_column_block() on every rank."""
+    import torch
+    import torch.distributed as dist
+    from parfastaai_b200 import sharding
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cap = sharding.slots_per_shard(G, world)
+    mine = sharding.owned_column_blocks(G, rank, world)
+    chunk = torch.full((cap,), -1, dtype=torch.int64)
+    chunk[:len(mine)] = torch.tensor(mine, dtype=torch.int64)
+    table = [torch.empty(cap, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(table, chunk)
+    table = torch.cat(table).numpy()
+    ncb = (G + sharding.COLS - 1) // sharding.COLS
+    ok = all(table[sharding.slot_of_column_block(J, G, world)] == J for J in range(ncb))
+    ok = ok and int((table >= 0).sum()) == ncb
+    q.put(bool(ok))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_partitioned_slot_layout_after_the_chunk_exchange():
+    import torch.multiprocessing as mp
+    from parfastaai_b200 import sharding
+    # the layout rule itself: slots are a bijection of the column blocks, inside the owner's chunk, for ragged sizes too
+    for n in (2, 3, 4, 8):
+        for G in (900, 1000, 6000, 50000):
+            ncb = (G + sharding.COLS - 1) // sharding.COLS
+            cap = sharding.slots_per_shard(G, n)
+            slots = [sharding.slot_of_column_block(J, G, n) for J in range(ncb)]
+            assert len(set(slots)) == ncb
+            assert all(s // cap == sharding.owner(J // sharding.RB_CBS, n) for J, s in enumerate(slots))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_exchange_worker, args=(r, 2, port, 5000, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True and q.get(timeout=5) is True
+
+
 def test_ownership_rule():
     from parfastaai_b200 import sharding
     for n in (1, 2, 3, 4, 8):
