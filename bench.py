@@ -174,6 +174,77 @@ def port_baseline(P, off, vals, T, n_rows, n_cols, gpu_matrix=None):
     return res
 
 
+def verify_rectangles(G, rank, world):
+    """Rectangles (name, rows, cols) of THIS rank's share of the all-vs-all matrix that the oracle re-computes after the timed
+    steps: a diagonal tile (triangular skipping, zero diagonal, both triangles), a tile whose column dictionary was built by
+    another rank (it travelled through the exchange), the ragged last row block and the last column block."""
+    from parfastaai_b200 import sharding
+    B = sharding.BLOCK
+    nb = (G + B - 1) // B
+    mine = [b for b in range(nb) if sharding.owner(b, world) == rank]
+    rects = []
+    if not mine:
+        return rects
+    I0 = mine[0]
+    r0 = I0 * B
+    rects.append(("diagonal", np.arange(r0, min(r0 + 24, G)), np.arange(r0, min(r0 + 96, G))))
+    # a row block of ours with a later row block (its column dictionaries) owned by someone else
+    late = None
+    for I in reversed(mine):
+        cands = [J for J in range(I + 1, nb) if world == 1 or sharding.owner(J, world) != rank]
+        if cands:
+            late = (I, cands[len(cands) // 2])
+            break
+    if late is not None:
+        I, J = late
+        ra = min(I * B + 200, G - 1)
+        ca = min(J * B + 40, G - 1)
+        rects.append(("late_list", np.arange(ra, min(ra + 24, (I + 1) * B, G)), np.arange(ca, min(ca + 112, G))))
+    if sharding.owner(nb - 1, world) == rank:
+        rects.append(("ragged_last_row_block", np.arange(max(0, G - 16), G), np.arange(max(0, G - 150), G)))
+    ra = min(r0 + 100, G - 1)
+    rects.append(("last_column_block", np.arange(ra, min(ra + 16, G)), np.arange(max(0, G - 64), G)))
+    return [(n, r.astype(np.int32), c.astype(np.int32)) for n, r, c in rects if r.size and c.size]
+
+
+def verify_against_oracle(G, P, dense, rects, read_cells, lower_valid):
+    """Re-generate the lists of the rectangles' genomes (every synthetic list is a pure function of seed, G, genome, SCP), run
+    the oracle's definition-level port on them and compare with the cells the GPU path stored.  read_cells(rows, cols) returns
+    the stored values; lower_valid = cells with row genome > column genome were stored too (mirror images)."""
+    from oracle import pfaai_oracle as orc
+    from parfastaai_b200 import synth
+    out = {"max_abs_diff": 0.0, "cells": 0, "rects": []}
+    if not rects:
+        return out
+    ids = np.unique(np.concatenate([np.concatenate([r, c]) for _n, r, c in rects])).astype(np.int32)
+    pos = {int(g): k for k, g in enumerate(ids)}
+    off, vals = synth.generate_subset(G, P, SEED, ids, dense=dense)
+    T = synth.t_matrix(ids.shape[0], P, off)
+    for name, rows, cols in rects:
+        lr = np.array([pos[int(g)] for g in rows], np.int32)
+        lc = np.array([pos[int(g)] for g in cols], np.int32)
+        want = orc.direct_aji(P, ids.shape[0], off, vals, T, lr, lc)["aji"]
+        got = read_cells(rows, cols)
+        mask = np.ones(want.shape, bool) if lower_valid else (rows[:, None] < cols[None, :])
+        d = float(np.abs(got - want)[mask].max()) if mask.any() else 0.0
+        if lower_valid and name == "late_list":      # the mirror images M[j][i] of an off-diagonal tile
+            d = max(d, float(np.abs(read_cells(cols, rows) - want.T).max()))
+        if "hit_rate" not in out and cols.shape[0] >= 64 and not np.intersect1d(rows, cols).size:
+            # by-product for the on-chip ceiling: the fraction of a row's tetramers found in a 64-column dictionary
+            hits = tot = 0
+            for p in range(P):
+                blk = np.unique(np.concatenate([vals[off[k * P + p]:off[k * P + p + 1]] for k in lc[:64]]))
+                for k in lr:
+                    x = vals[off[k * P + p]:off[k * P + p + 1]]
+                    hits += int(np.isin(x, blk, assume_unique=True).sum()); tot += int(x.shape[0])
+            out["hit_rate"] = hits / max(tot, 1)
+        out["max_abs_diff"] = max(out["max_abs_diff"], d)
+        out["cells"] += int(mask.sum())
+        out["rects"].append({"name": name, "rows": [int(rows[0]), int(rows[-1])], "cols": [int(cols[0]), int(cols[-1])],
+                             "max_abs_diff": d})
+    return out
+
+
 def reference_baseline(P, n_genomes, threads, tmpdir):
     db = make_ref_db(n_genomes, P, tmpdir)
     phases, wall = run_ref_once(db, threads, tmpdir)
@@ -255,6 +326,7 @@ def main():
     ap.add_argument("--ref-genomes", type=int, default=64, help="size of the reference arm's bounded sample")
     ap.add_argument("--cpu-baseline-genomes", type=int, default=96)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ceiling", action="store_true", help="skip the on-chip ceiling micro-benchmark (pfaai_gpu_microbench)")
     ap.add_argument("--replicated-build", action="store_true",
                     help="N>1: every rank builds the whole index (the pre-partitioning path) instead of pfaai_gpu_build_partitioned")
     ap.add_argument("--sliced-index", action="store_true",
@@ -262,6 +334,12 @@ def main():
                          "owns their genome by an NCCL all-to-all (no all-gather of F, no filter passes)")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: finish the dictionary exchange before the tile kernel starts")
     ap.add_argument("--verify", action="store_true", help="N>1: gather the shards on rank 0 and compare with an unsharded compute")
+    ap.add_argument("--dense", action="store_true",
+                    help="the dense (real-like) synthetic family of SURVEY 8(d): 4 clades, d_k ~ U(0, 0.05), e_g ~ U(0, 0.01)")
+    ap.add_argument("--no-shared-matrix", action="store_true",
+                    help="N>1: keep compact per-rank matrices (upper-triangle cells only) instead of one shared host matrix")
+    ap.add_argument("--path", default="auto", choices=["auto", "lists", "mma"],
+                    help="tile path: lists = dictionary walk (K4), mma = dense tcgen05 contraction + patches (K5), auto = by density")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         log("[bench] note: fewer than 3 warm-up steps requested; the timing rules ask for W >= 3")
@@ -316,7 +394,7 @@ def main():
                 ctypes.CDLL("libgomp.so.1").omp_set_num_threads(max(1, (os.cpu_count() or 1)))
             except OSError:
                 pass
-        off, vals = synth.generate(G, P, seed=SEED)
+        off, vals = synth.generate(G, P, seed=SEED, dense=args.dense)
         nF = int(off[-1])
         F_pin = torch.empty(nF * 2, dtype=torch.int32).pin_memory()
         Lc_pin = torch.empty(pf.NTETRA, dtype=torch.int32).pin_memory()
@@ -337,8 +415,42 @@ def main():
     ctx.set_shard(rank, world)
     my_rows, my_cols = sharding.shard_shape(pf.ALL_VS_ALL, G, 0, rank, world)
     my_pairs = sharding.pair_count(pf.ALL_VS_ALL, G, 0, rank, world)
-    M_pin = torch.empty(my_rows * my_cols, dtype=torch.float64).pin_memory()
-    M = M_pin.numpy().reshape(my_rows, my_cols)
+    # N > 1: ONE G x G host matrix shared by all ranks (POSIX shared memory, page-locked in every process with
+    # cudaHostRegister): every rank's tile kernel stores its cells AND their mirror images straight into it
+    # (pfaai_gpu_set_global_matrix), so the e2e step ends with the complete symmetric matrix in host memory exactly as at N = 1
+    # -- equal work, equal bytes (8*G*G) at every N, no gather and no host mirror pass.
+    shared_matrix, shm_path, shm_note = False, None, None
+    if world > 1 and not args.no_shared_matrix:
+        shm_path = "/dev/shm/pfaai_bench_M_%s.bin" % os.environ.get("MASTER_PORT", "0")
+        ok = torch.ones(1, dtype=torch.int32, device=dev)
+        need = 8 * G * G
+        try:
+            if rank == 0:
+                st = os.statvfs("/dev/shm")
+                if st.f_bavail * st.f_frsize < need + (1 << 30):
+                    raise RuntimeError("/dev/shm has %.1f GB free, the matrix needs %.1f GB" % (st.f_bavail * st.f_frsize / 1e9, need / 1e9))
+                with open(shm_path, "wb") as fh:
+                    fh.truncate(need)
+        except Exception as e:   # noqa: BLE001
+            shm_note = str(e)
+            ok[0] = 0
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 1:
+            M_sh = torch.from_file(shm_path, shared=True, size=G * G, dtype=torch.float64)
+            rc = int(torch.cuda.cudart().cudaHostRegister(M_sh.data_ptr(), need, 1 | 2))   # portable | mapped
+            ok[0] = 1 if rc == 0 else 0
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 1:
+                shared_matrix = True
+                M = M_sh.numpy().reshape(G, G)     # addressed globally only by the e2e steps (set_global_matrix below)
+            else:
+                shm_note = "cudaHostRegister of the shared matrix failed on some rank"
+                del M_sh
+        if not shared_matrix:
+            log(f"[rank {rank}] shared host matrix unavailable ({shm_note}); compact per-rank matrices (upper-triangle cells only)")
+    if not shared_matrix:
+        M_pin = torch.empty(my_rows * my_cols, dtype=torch.float64).pin_memory()
+        M = M_pin.numpy().reshape(my_rows, my_cols)
     if world > 1:
         # N > 1: the contexts expose their device index buffers; F is sized for N equal slices (the last one padded) so that the
         # all-gather of the e2e region lands directly in the context's buffer
@@ -515,24 +627,62 @@ def main():
     exchange_bytes = sum(ch for _p, ch, _u in ctx.exchange_buffers()) * world if partitioned else 0
     value = pairs_total * args.steps / (ms_dev / 1e3)
     # ---- end to end through the host-buffer C-ABI ----
+    if shared_matrix:
+        ctx.set_global_matrix(True)
     for _ in range(min(args.warmup, 2)):
         with torch.cuda.stream(stream):
             step_e2e()
     ms_e2e, _, _, _, tm_e2e = timed(step_e2e, args.steps)
     e2e_value = pairs_total * args.steps / (ms_e2e / 1e3)
     h2d = 8 * nF + 4 * pf.NTETRA * world              # all ranks together (N > 1: every rank uploads 1/N of F)
-    d2h = 8 * my_rows * my_cols                       # bytes all ranks copy back per step
-    if world > 1:
-        d2h_t = torch.tensor([8.0 * my_rows * my_cols], dtype=torch.float64, device=dev)
-        dist.all_reduce(d2h_t)
-        d2h = int(d2h_t.item())
+    # bytes the tile kernels actually store into host memory per step, all ranks together: N = 1 and the shared matrix hold
+    # both triangles + the diagonal (8*G*G); compact per-rank matrices hold the upper-triangle cells + the diagonal only
+    if world == 1 or shared_matrix:
+        d2h = 8 * G * G
+    else:
+        d2h = 8 * (pairs_total + G)
     launches = int(max_over_ranks(float(launches)))
+
+    # ---- parity evidence on the path that was timed (every rank, every N): the oracle re-computes rectangles of this rank's
+    #      share from re-generated lists and compares them with what the last e2e step stored in host memory ----
+    own_ids = sharding.owned_indices(G, rank, world)
+    if world == 1 or shared_matrix:
+        def read_cells(rows, cols):
+            return M[np.ix_(rows, cols)]
+    else:
+        local_of = {int(g): k for k, g in enumerate(own_ids)}
+
+        def read_cells(rows, cols):
+            return M[np.ix_([local_of[int(g)] for g in rows], cols)]
+    t0 = time.perf_counter()
+    try:
+        import ctypes
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(max(1, (os.cpu_count() or 1) // world))
+    except OSError:
+        pass
+    vq = verify_against_oracle(G, P, args.dense, verify_rectangles(G, rank, world), read_cells,
+                               lower_valid=(world == 1 or shared_matrix))
+    vq["seconds"] = time.perf_counter() - t0
+    if world > 1:
+        vt = torch.tensor([vq["max_abs_diff"]], dtype=torch.float64, device=dev)
+        dist.all_reduce(vt, op=dist.ReduceOp.MAX)
+        ct = torch.tensor([float(vq["cells"]), vq["seconds"]], dtype=torch.float64, device=dev)
+        cmax = ct.clone()
+        dist.all_reduce(ct)
+        dist.all_reduce(cmax, op=dist.ReduceOp.MAX)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, vq["rects"])
+        vq = {"max_abs_diff": float(vt.item()), "cells": int(ct[0].item()), "seconds": float(cmax[1].item()),
+              "rects": {f"rank{r}": g for r, g in enumerate(gathered)}, "hit_rate": vq.get("hit_rate")}
+    vq.update(ranks=world, against="oracle pfo_direct_aji on lists re-generated per rank (seed, genome, SCP)",
+              matrix="the host matrix of the last e2e step" + (" (shared by all ranks, mirror images included)" if shared_matrix else ""))
+    log(f"[rank {rank}] verify: max |AJI - oracle| = {vq['max_abs_diff']:.3g} over {vq['cells']} cells in {vq['seconds']:.1f} s")
 
     verify = None
     if args.verify:
         # gather the shards' compact matrices on rank 0, assemble (mirror) and compare with an unsharded compute
         lay = sharding.owned_indices(G, rank, world)
-        if world == 1:
+        if world == 1 or shared_matrix:
             full = M
         elif rank == 0:
             parts, lays = [M.copy()], [lay]
@@ -545,6 +695,8 @@ def main():
         else:
             dist.send(torch.from_numpy(M).to(dev), dst=0)
         if rank == 0:
+            full = np.array(full, copy=True)
+            ctx.set_global_matrix(False)
             ctx.set_shard(0, 1)
             if sliced:
                 ctx.upload_index(P, G, F, Lc)             # rank 0 kept the whole F for this check
@@ -552,6 +704,20 @@ def main():
             ref = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
             ctx.set_shard(rank, world)
             verify = {"max_abs_diff_vs_unsharded": float(np.abs(full - ref).max()), "identical": bool(np.array_equal(full, ref))}
+
+    # ---- on-chip ceiling of the list path's access pattern, measured on this GPU (rank 0): the walk loop alone against a
+    #      shared-memory-resident dictionary at the workload's hit rate ----
+    ceiling = None
+    if rank == 0 and not args.no_ceiling:
+        hr = vq.get("hit_rate") or 0.43
+        try:
+            c0, c1 = ctx.microbench(0, hr, 30000), ctx.microbench(1, hr, 30000)
+            ceiling = {"lookups_per_s": c0["lookups_per_s"], "lookups_per_s_no_bank_conflicts": c1["lookups_per_s"],
+                       "hit_rate": hr, "warps_per_sm": c0["warps_per_sm"], "ms": [c0["ms"], c1["ms"]],
+                       "what": "pfaai_gpu_microbench: the tile kernel's walk loop (LDS.32 bitmap probe + rank + predicated LDS.64 mask + "
+                               "carry-save adds, ids by LDG.128 from L2) on a resident dictionary; no bulk copies, no epilogue, no stores"}
+        except Exception as e:   # noqa: BLE001
+            ceiling = {"error": str(e)}
 
     peak, peak_src = measured_peaks()
     tile_avg_ms = float(np.mean(tile_ms))
@@ -574,7 +740,8 @@ def main():
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "int32+f64", "data": "synthetic",
         "config": {"workload": f"synthetic {G} genomes x {P} SCPs all-vs-all (BASELINE config {'4' if G == 10000 else '5' if G == 50000 else 'custom'}; "
-                               f"SURVEY 8(d) recipe, seed {SEED})",
+                               f"SURVEY 8(d) recipe, {'DENSE real-like family, ' if args.dense else ''}seed {SEED})",
+                   "family": "dense" if args.dense else "sparse",
                    "genomes": G, "scps": P, "postings": nF, "pairs": pairs_total, "mode": "all-vs-all",
                    "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); F replicated "
                                    f"on every GPU (N>1, inside the e2e region: every rank uploads its 1/N slice of F, NCCL all-gather over NVLink); "
@@ -584,7 +751,11 @@ def main():
                                       "the dictionaries are all-gathered over NVLink (NCCL, in place, on a second stream) while the tiles on the rank's "
                                       "own dictionaries are computed; " if partitioned else
                                       "index build replicated on every rank; ") +
-                                   f"no reduction collective; every rank stores only its own upper-triangle rows into pinned host memory"),
+                                   "no reduction collective; " + ("every rank's tile kernel stores its cells and their mirror images straight into ONE page-locked "
+                                                                "host matrix shared by all ranks (POSIX shared memory + cudaHostRegister): the e2e step ends with "
+                                                                "the complete symmetric matrix in host memory, as at N = 1" if shared_matrix else
+                                                                "every rank stores only its own upper-triangle rows into pinned host memory"
+                                                                if world > 1 else "the tile kernel stores both triangles straight into pinned host memory")),
                    "l2_policy": "inputs larger than L2 (F = %.2f GB, matrix = %.2f GB vs 126 MB L2)" % (8 * nF / 1e9, d2h / 1e9),
                    "step": "index build (scan + histogram + radix sort) + row-slab packing + column dictionaries"
                            + (" + dictionary all-gather" if partitioned else "") + " + tile kernel"},
@@ -602,14 +773,18 @@ def main():
         "roofline_onchip": {"lookups_per_s": float(tm["n_tiles"]) * 384 * (nF / G) / (tile_avg_ms / 1e3),
                             "pair_scp_updates_per_s": (my_pairs if world > 1 else pairs_total) * P / (tile_avg_ms / 1e3),
                             "lookup": "one row tetramer against one 64-column dictionary (LDS.32 + rank + LDS.64 + bit-sliced add)",
+                            "ceiling": ceiling,
+                            "frac": ((float(tm["n_tiles"]) * 384 * (nF / G) / (tile_avg_ms / 1e3)) / ceiling["lookups_per_s"]
+                                     if ceiling and ceiling.get("lookups_per_s") else None),
                             "ncu": onchip},
         "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
                       "exchange": exchange_ms, "exchange_bytes_per_rank": exchange_bytes,
                       "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"]},
     }
 
+    line["verify"] = vq
     if verify is not None:
-        line["verify"] = verify
+        line["verify_unsharded"] = verify
     # ---- CPU baseline (rank 0, N=1 only): the reference itself on a bounded sample, plus our OpenMP port ----
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T = synth.t_matrix(G, P, off)
@@ -632,6 +807,13 @@ def main():
     ctx.close()
     if world > 1:
         dist.barrier()
+        if shared_matrix:
+            torch.cuda.cudart().cudaHostUnregister(M_sh.data_ptr())
+            if rank == 0:
+                try:
+                    os.remove(shm_path)
+                except OSError:
+                    pass
         dist.destroy_process_group()
     if rank == 0:
         emit(line)

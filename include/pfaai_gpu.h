@@ -83,6 +83,13 @@ int  pfaai_gpu_set_stream(pfaai_gpu_ctx *ctx, void *cuda_stream);
  *   QUERY_SUBSET / QUERY_DB   [n_qry x owned targets].
  * The JAC / counts hooks of pfaai_gpu_compute need an unsharded context. */
 int  pfaai_gpu_set_shard(pfaai_gpu_ctx *ctx, int shard, int n_shards);
+/* ALL_VS_ALL on a sharded context, alternative output addressing: every shard is handed the SAME full G x G matrix (one
+ * page-locked host buffer that all contexts of a process -- or, through shared memory registered with cudaHostRegister, all
+ * processes of a box -- can address) and stores its cells AND their mirror images M[j][i] straight into it.  The shards' cell
+ * sets are disjoint and together cover the whole matrix (zero diagonal included), so when the last shard returns the matrix is
+ * complete in host memory: no gather, no host-side mirror pass (src/main.cpp:143-154 done by the kernels' own stores).
+ * pfaai_gpu_matrix_shape then reports G x G.  Off (default): compact per-shard matrices as described above. */
+int  pfaai_gpu_set_global_matrix(pfaai_gpu_ctx *ctx, int on);
 /* layout of the last compute: axis (0 = rows, 1 = columns) that is sharded, the number of owned indices along it and
  * (ids != NULL) their global indices in storage order.  Unsharded: n = the full extent, ids = 0..n-1. */
 int  pfaai_gpu_shard_layout(const pfaai_gpu_ctx *ctx, int *axis, int64_t *n, int32_t *ids);
@@ -197,6 +204,16 @@ int  pfaai_gpu_compute(pfaai_gpu_ctx *ctx, int mode, const int32_t *qry_ids, int
 int64_t pfaai_gpu_n_pairs(int mode, int n_genomes, int n_qry);
 
 int  pfaai_gpu_get_timings(const pfaai_gpu_ctx *ctx, pfaai_timings_t *out);
+
+/* Measurement hook: the on-chip ceiling of the list path's access pattern on THIS GPU.  Runs the walk loop of
+ * the tile kernel (random LDS.32 bitmap probe + rank + predicated LDS.64 mask read + bit-sliced carry-save adds, 24 warps per SM,
+ * ids streamed by coalesced LDG.128 from an L2-resident buffer) against a dictionary that stays in shared memory: no bulk
+ * copies, no epilogue, no output.  variant 0: random ids, presence density = hit_rate (bank conflicts as in the real walk);
+ * variant 1: all lanes of a warp look the same id up (no bank conflicts: the issue-bound ceiling).  steps = walk-loop iterations
+ * (8 lookups per lane each).  Replaces nothing in the reference; it is what turns "% of the shared-memory pipe" into "% of what
+ * this access pattern can reach". */
+typedef struct { double lookups_per_s; int64_t lookups; float ms; int32_t warps_per_sm; int32_t variant; int32_t reserved_; } pfaai_microbench_t;
+int  pfaai_gpu_microbench(pfaai_gpu_ctx *ctx, int variant, double hit_rate, int steps, pfaai_microbench_t *out);
 
 #ifdef __cplusplus
 }

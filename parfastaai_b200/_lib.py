@@ -30,7 +30,7 @@ EXPORTS = [
     "pfaai_gpu_build_partitioned", "pfaai_gpu_exchange_buffers", "pfaai_gpu_finish_partitioned", "pfaai_gpu_exchange_local",
     "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
     "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
-    "pfaai_gpu_build_routed", "pfaai_gpu_route_local",
+    "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench",
 ]
 
 
@@ -41,6 +41,11 @@ class Timings(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class Microbench(C.Structure):
+    _fields_ = [("lookups_per_s", C.c_double), ("lookups", C.c_int64), ("ms", C.c_float), ("warps_per_sm", C.c_int32),
+                ("variant", C.c_int32), ("reserved_", C.c_int32)]
 
 
 class Exchange(C.Structure):
@@ -100,6 +105,8 @@ def load():
     L.pfaai_gpu_route_recv_buffer.argtypes = [vp, i64, C.POINTER(vp)]
     L.pfaai_gpu_build_routed.argtypes = [vp, i64]
     L.pfaai_gpu_route_local.argtypes = [C.POINTER(vp), i32]
+    L.pfaai_gpu_set_global_matrix.argtypes = [vp, i32]
+    L.pfaai_gpu_microbench.argtypes = [vp, i32, C.c_double, i32, C.POINTER(Microbench)]
     _lib = L
     return L
 
@@ -145,6 +152,11 @@ class PfaaiGpu:
     def set_shard(self, shard, n_shards):
         self._check(self._L.pfaai_gpu_set_shard(self._h, shard, n_shards), "set_shard")
         self._n_shards, self._shard = n_shards, shard
+
+    def set_global_matrix(self, on=True):
+        """Sharded all-vs-all: address the full G x G matrix (shared by all shards) and store the mirror images too."""
+        self._check(self._L.pfaai_gpu_set_global_matrix(self._h, int(bool(on))), "set_global_matrix")
+        self._global = bool(on)
 
     def upload_index(self, P, G, F, Lc, T=None):
         F = np.ascontiguousarray(F, dtype=PG_DTYPE)
@@ -292,6 +304,8 @@ class PfaaiGpu:
                 raise PfaaiError("the JAC / counts hooks need an unsharded context")
             from . import sharding
             shape = sharding.shard_shape(mode, self.G, nq, self._shard, ns)
+            if getattr(self, "_global", False) and mode == ALL_VS_ALL:
+                shape = (self.G, self.G)
             M = matrix_out if matrix_out is not None else np.zeros(shape, np.float64)
             if M.shape != tuple(shape):
                 raise ValueError(f"matrix_out must have the shard's shape {shape}")
@@ -304,6 +318,12 @@ class PfaaiGpu:
         cnt = np.zeros((npairs, self.P), np.int32) if want_counts else None
         self._check(self._L.pfaai_gpu_compute(self._h, mode, _p(q), nq, flags, _p(M), _p(jac), _p(aji), _p(cnt)), "compute")
         return {"matrix": M, "jac": jac, "aji": aji, "counts": cnt}
+
+    def microbench(self, variant=0, hit_rate=0.43, steps=20000):
+        """On-chip ceiling of the list path's walk loop on this GPU (pfaai_gpu_microbench) -> dict."""
+        m = Microbench()
+        self._check(self._L.pfaai_gpu_microbench(self._h, variant, float(hit_rate), int(steps), C.byref(m)), "microbench")
+        return {k: getattr(m, k) for k, _ in m._fields_ if k != "reserved_"}
 
     def timings(self):
         t = Timings()

@@ -45,7 +45,7 @@ constexpr uint32_t PAD_ID = RANGE_T;         // padding value of packed row slic
 // a range-local id v is stored in the row slabs as  x = (v>>4) << 7 | (31 - (v&15)):  x>>5 is the byte offset of
 // its bitmap word, x&31 the left shift that moves its presence bit to bit 31 (and drops the rank half-word)
 __host__ __device__ __forceinline__ uint32_t slab_encode(uint32_t v) { return ((v >> 4) << 7) | (31u - (v & 15u)); }
-constexpr int MAX_SUB = 64;                   // a (block, SCP, range) dictionary is split into <= 8 column sub-ranges
+constexpr int MAX_SUB = 64;                   // a (block, SCP, range) dictionary is split into <= 64 column sub-ranges (1 column each)
 
 // shared memory of the tile kernel: [misc 2 KB][reciprocal table 16 KB][stage 0][stage 1]
 constexpr int SMEM_TOTAL = 227 * 1024;                       // 232448

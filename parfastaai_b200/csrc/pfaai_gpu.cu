@@ -9,6 +9,7 @@
 #include "aji_tile.cuh"
 #include "common.cuh"
 #include "index_build.cuh"
+#include "microbench.cuh"
 #include "tile_index.cuh"
 
 namespace pfaai {
@@ -28,6 +29,7 @@ struct Ctx {
     bool own_stream = false;
     std::string err;
     int shard = 0, n_shards = 1;
+    bool global_out = false;              // pfaai_gpu_set_global_matrix: a sharded context addresses the full G x G matrix
     // index
     int P = 0, G = 0;
     int64_t nF = 0;
@@ -311,8 +313,16 @@ int pfaai_gpu_set_stream(pfaai_gpu_ctx *h, void *s) {
 
 int pfaai_gpu_set_shard(pfaai_gpu_ctx *h, int shard, int n_shards) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
-    if (!c || n_shards < 1 || shard < 0 || shard >= n_shards) { set_error(c, "bad shard"); return PFAAI_ERR_CONSTRUCT; }
+    // the ownership table of the partitioned / routed builds holds one byte per 128 genomes
+    if (!c || n_shards < 1 || n_shards > 255 || shard < 0 || shard >= n_shards) { set_error(c, "bad shard (1 <= n_shards <= 255)"); return PFAAI_ERR_CONSTRUCT; }
     c->shard = shard; c->n_shards = n_shards;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_set_global_matrix(pfaai_gpu_ctx *h, int on) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    c->global_out = (on != 0);
     return PFAAI_OK;
 }
 
@@ -683,6 +693,9 @@ static int upload_i32(Ctx *c, DevBuf &b, const std::vector<int32_t> &v) {
 static int make_dictionaries(Ctx *c, int n_cols, const std::vector<int32_t> *cb_list, int n_groups, int slot_base, int64_t n_slots,
                              size_t blob_base, size_t blob_cap, int64_t stage_base, int64_t stage_cap) {
     const int P = c->P;
+    // the same bound compute_internal applies (bit-plane capacity of the walk); it also guarantees that a dictionary fits a
+    // stage at the finest column sub-split (max_len + 1 <= MASK_CAP), which k_dict_build relies on
+    if (c->max_len / 2 + 16 > 4095) { set_error(c, "dictionaries: a (SCP, genome) tetramer list exceeds 8158 entries"); return PFAAI_ERR_CONSTRUCT; }
     int max_sub = 1;
     while (max_sub < MAX_SUB && (int64_t)(COLS_PER_TILE / max_sub) * c->max_len + 1 > MASK_CAP) max_sub *= 2;
     const int64_t ndict = (int64_t)n_groups * P * NRANGE;
@@ -879,6 +892,10 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     //      Sharding: row block I belongs to shard fold(I mod 2n) (folded assignment balances the
     //      triangular work); a sharded context stores only its own row blocks, compactly, in ascending order ----
     const bool sharded = c->n_shards > 1;
+    // compact: the shard's matrix holds only its own row blocks (upper-triangle cells in all-vs-all).  Not compact
+    // (pfaai_gpu_set_global_matrix, all-vs-all): every shard addresses the SAME full G x G matrix and stores its cells and their
+    // mirror images into it -- the shards' cell sets are disjoint and together cover the matrix
+    const bool compact = sharded && !(c->global_out && m.symmetric);
     if (sharded && (want_sn || want_counts)) { set_error(c, "compute: the JAC / counts hooks need an unsharded context"); return PFAAI_ERR_CONSTRUCT; }
     std::vector<int4> tiles, tiles_late;   // partitioned: tiles on this shard's own dictionaries first (they need no exchange)
     c->owned_rows.clear();
@@ -902,10 +919,10 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         for (int J = 0; J < ncb; J++) {
             if (m.symmetric) {
                 const int col_max = std::min((J + 1) * COLS_PER_TILE, n_cols) - 1;
-                if (row0 >= col_max) continue;
+                if (row0 > col_max) continue;      // row0 == col_max: the tile still holds the diagonal cell (stored as 0)
             }
             const bool own_dict = !c->partitioned || fold_owner(J / RB_CBS, c->n_shards) == c->shard;
-            (own_dict ? tiles : tiles_late).push_back(make_int4(I, J, sharded ? local_rows : row0, slot_of[J]));
+            (own_dict ? tiles : tiles_late).push_back(make_int4(I, J, compact ? local_rows : row0, slot_of[J]));
         }
         for (int r = 0; r < nr; r++) c->owned_rows.push_back(row0 + r);
         local_rows += nr;
@@ -916,7 +933,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     if (!tiles.empty()) PF_CUDA(c, cudaMemcpyAsync(c->tiles.p, tiles.data(), sizeof(int4) * tiles.size(), cudaMemcpyHostToDevice, c->stream));
     // ---- outputs: the kernel's row axis is the output's row axis in all-vs-all and its column axis otherwise ----
     c->shard_axis = m.symmetric ? 0 : 1;
-    if (sharded) {
+    if (compact) {
         if (m.symmetric) m.out_rows = local_rows;                    // [owned rows x G], row stride G
         else { m.out_cols = local_rows; m.cs = local_rows; }         // [nQ x owned targets]
     }
@@ -944,7 +961,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.stages = ptr<StageDesc>(c->stages); prm.stage_rng = ptr<int64_t>(c->stage_rng);
     prm.blob = ptr<unsigned char>(c->blob); prm.colT = ptr<int32_t>(c->colT);
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
-    prm.out = direct_dev ? direct_dev : ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !sharded) ? 1 : 0;
+    prm.out = direct_dev ? direct_dev : ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !compact) ? 1 : 0;
     prm.k27 = 1u << 27; prm.k16 = 1u << 16;
     prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
     prm.N_out = want_sn ? ptr<int32_t>(c->N_out) : nullptr;
@@ -953,6 +970,9 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
     PF_CUDA(c, cudaMemsetAsync(c->tile_ctr.p, 0, 2 * sizeof(int), c->stream));
     // list 1 = tiles [0, n1), list 2 (optional) = tiles [n1, n1 + n2): a CTA moves on to list 2 when list 1 is exhausted
+    if (direct_dev && (tiles.empty() || c->nF <= 0))
+        // nothing will be launched: the caller's pinned matrix (no staging buffer, no memset) would stay untouched
+        PF_CUDA(c, cudaMemsetAsync(direct_dev, 0, sizeof(double) * ncell, c->stream));
     auto launch_lists = [&](int n1, int n2, int reserve, cudaStream_t st) -> int {
         if (n1 + n2 <= 0 || c->nF <= 0) return PFAAI_OK;
         prm.tiles = ptr<int4>(c->tiles); prm.n_tiles = n1; prm.tile_counter = ptr<int>(c->tile_ctr);
@@ -1097,6 +1117,33 @@ int pfaai_gpu_compute(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_
         for (int q = 0; q < n_qry; q++) for (int t = 0; t < nT; t++)
             emit(quirk ? q : nT + q, quirk ? n_qry + t : t, (size_t)t * n_cols + q);
     }
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_microbench(pfaai_gpu_ctx *h, int variant, double hit_rate, int steps, pfaai_microbench_t *out) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !out || steps <= 0 || hit_rate < 0.0 || hit_rate > 1.0 || variant < 0 || variant > 1) { set_error(c, "microbench: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    const int64_t n_chunks = 1 << 13;                              // 8192 chunks x 512 B = 4 MB, L2-resident
+    DevBuf ids, sink;
+    PF_TRY(ensure(c, ids, sizeof(uint4) * 32 * (size_t)n_chunks));
+    PF_TRY(ensure(c, sink, 16));
+    k_ceiling_ids<<<(unsigned)ceil_div64(n_chunks * 32, 256), 256, 0, c->stream>>>(ptr<uint4>(ids), n_chunks * 32, variant);
+    auto kern = k_walk_ceiling<9>;
+    PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
+    const uint32_t hit_q16 = (uint32_t)(hit_rate * 65536.0);
+    for (int rep = 0; rep < 2; rep++) {                            // rep 0 = warm-up
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
+        kern<<<(unsigned)c->sm_count, TILE_THREADS, SMEM_TOTAL, c->stream>>>(ptr<uint4>(ids), (uint32_t)(n_chunks - 1), steps, hit_q16, ptr<uint32_t>(sink));
+        PF_CUDA(c, cudaGetLastError());
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
+        PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    out->ms = ev_ms(c, EV_T0, EV_T1);
+    out->lookups = (int64_t)c->sm_count * TILE_THREADS * (int64_t)steps * 8;
+    out->lookups_per_s = out->ms > 0.f ? (double)out->lookups / ((double)out->ms * 1e-3) : 0.0;
+    out->warps_per_sm = TILE_WARPS; out->variant = variant;
+    release(ids); release(sink);
     return PFAAI_OK;
 }
 

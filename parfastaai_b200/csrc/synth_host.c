@@ -101,6 +101,29 @@ void pfs_fill(int N, int P, uint64_t seed, int dense, const int64_t *seg_off, in
     }
 }
 
+/* The same two passes for a SUBSET of the genomes of the N-genome database (ids[k] in [0, N)): list (k, p) of the result is list
+ * (ids[k], p) of the full database.  Lets a checker rebuild a few rows / columns of a large synthetic workload on its own. */
+int64_t pfs_count_subset(int N, int P, uint64_t seed, int dense, const int32_t *ids, int n, int64_t *seg_off /*[n*P+1]*/) {
+    seg_off[0] = 0;
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int k = 0; k < n; k++) {
+        int32_t buf[600];
+        for (int p = 0; p < P; p++) seg_off[(size_t)k * P + p + 1] = gen_list(seed, N, dense, p, ids[k], buf);
+    }
+    for (size_t s = 0; s < (size_t)n * P; s++) seg_off[s + 1] += seg_off[s];
+    return seg_off[(size_t)n * P];
+}
+void pfs_fill_subset(int N, int P, uint64_t seed, int dense, const int32_t *ids, int n, const int64_t *seg_off, int32_t *vals) {
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int k = 0; k < n; k++) {
+        int32_t buf[600];
+        for (int p = 0; p < P; p++) {
+            int m = gen_list(seed, N, dense, p, ids[k], buf);
+            memcpy(vals + seg_off[(size_t)k * P + p], buf, sizeof(int32_t) * (size_t)m);
+        }
+    }
+}
+
 /* genome-major lists -> the reference's arrays: Lc[160000] and F in (tetramer, protein, genome) order
  * (what DataBaseInterface::tetramerOccCounts / proteinSetGPPairs deliver, scp_db.hpp:121-216). */
 void pfs_to_reference(int N, int P, const int64_t *seg_off, const int32_t *vals, int32_t *Lc, pg_t *F) {

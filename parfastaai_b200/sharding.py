@@ -1,9 +1,12 @@
 """Host side of the multi-GPU row-block sharding (include/pfaai_gpu.h, pfaai_gpu_set_shard).
 
-Every GPU holds the whole index and computes only the blocks of 384 target genomes it owns; there is no data-path
-collective.  This module restates the ownership rule (so that hosts can plan buffers before any GPU work) and
-assembles the shards' compact matrices into the reference's dense output (src/main.cpp:143-154), mirroring the
-upper triangle in all-vs-all mode -- the one place where the "final matrix is gathered to the host writer".
+Every GPU computes only the blocks of 384 target genomes it owns.  With the replicated build every GPU holds the whole index and
+there is no data-path collective; with the partitioned / routed builds every GPU sorts the postings and
+builds the column dictionaries of its own row blocks only and the dictionaries are all-gathered over NVLink -- the one exchange
+step of the path.  This module restates the ownership rule and the slot layout of that exchange (so that hosts can plan buffers
+before any GPU work) and assembles the shards' compact matrices into the reference's dense output (src/main.cpp:143-154),
+mirroring the upper triangle in all-vs-all mode.  (With pfaai_gpu_set_global_matrix the shards store straight into one shared
+G x G matrix, mirror images included, and no assembly is needed.)
 """
 from __future__ import annotations
 

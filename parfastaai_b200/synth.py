@@ -28,6 +28,10 @@ def _load():
         L.pfs_count.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p]
         L.pfs_fill.restype = None
         L.pfs_fill.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
+        L.pfs_count_subset.restype = C.c_int64
+        L.pfs_count_subset.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        L.pfs_fill_subset.restype = None
+        L.pfs_fill_subset.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.pfs_to_reference.restype = None
         L.pfs_to_reference.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pfs_protein_length.restype = C.c_int
@@ -43,6 +47,19 @@ def generate(N, P=122, seed=1234, dense=False):
     nF = L.pfs_count(N, P, seed, int(dense), seg_off.ctypes.data)
     vals = np.empty(nF, np.int32)
     L.pfs_fill(N, P, seed, int(dense), seg_off.ctypes.data, vals.ctypes.data)
+    return seg_off, vals
+
+
+def generate_subset(N, P, seed, genomes, dense=False):
+    """The lists of `genomes` (ids of the N-genome database generate(N, P, seed, dense) would produce), renumbered 0..n-1:
+    -> (seg_off [n*P+1], vals).  Every list is a pure function of (seed, N, dense, genome, SCP)."""
+    L = _load()
+    ids = np.ascontiguousarray(genomes, dtype=np.int32)
+    n = int(ids.shape[0])
+    seg_off = np.zeros(n * P + 1, np.int64)
+    nF = L.pfs_count_subset(N, P, seed, int(dense), ids.ctypes.data, n, seg_off.ctypes.data)
+    vals = np.empty(nF, np.int32)
+    L.pfs_fill_subset(N, P, seed, int(dense), ids.ctypes.data, n, seg_off.ctypes.data, vals.ctypes.data)
     return seg_off, vals
 
 

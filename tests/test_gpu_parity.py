@@ -450,3 +450,80 @@ def test_pinned_host_matrix_is_stored_directly_and_identically(pf, orc):
         with pytest.raises(pf.PfaaiError):
             ctx.download_matrix()
     ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N", [385, 769])
+def test_pinned_matrix_last_diagonal_cell_is_written(pf, orc, N):
+    """G = 384k + 1: the last row block's only tile is (row0 == col_max), i.e. the diagonal cell alone.  With a pinned
+    (directly stored, never memset) matrix every cell -- (G-1, G-1) included -- must be written (pfaai_gpu.cu:905)."""
+    import torch
+    from parfastaai_b200 import synth
+    P = 3
+    off, vals = synth.generate(N, P, seed=5)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    staged = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
+    pin = torch.full((N, N), -7.0, dtype=torch.float64).pin_memory()
+    direct = ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=pin.numpy())["matrix"]
+    assert direct[N - 1, N - 1] == 0.0
+    assert not np.any(direct == -7.0)
+    assert np.array_equal(direct, staged)
+    assert np.array_equal(direct, direct.T) and not np.any(np.diag(direct))
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_pinned_matrix_of_an_empty_index_is_zeroed(pf):
+    """|F| = 0: no tile kernel is launched; a pinned matrix must still come back as zeros, not untouched."""
+    import torch
+    ctx = pf.PfaaiGpu(0)
+    G, P = 9, 2
+    ctx.upload_index(P, G, np.zeros(0, pf.PG_DTYPE), np.zeros(pf.NTETRA, np.int32))
+    ctx.build()
+    pin = torch.full((G, G), -7.0, dtype=torch.float64).pin_memory()
+    direct = ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=pin.numpy())["matrix"]
+    assert not np.any(direct)
+    ctx.close()
+
+
+@pytest.mark.parametrize("n_shards,N", [(2, 1000), (3, 1153), (4, 900)])
+def test_global_matrix_shards_fill_one_pinned_matrix_completely(pf, orc, n_shards, N):
+    """pfaai_gpu_set_global_matrix: all shards store their cells and the mirror images into ONE pinned G x G matrix; their
+    cell sets are disjoint and cover the matrix (poisoned buffer), the result equals the unsharded matrix bit for bit
+    (N = 1153 = 3 * 384 + 1: the last row block is the diagonal cell alone; N = 900 / 4 shards: one shard owns nothing)."""
+    import torch
+    from parfastaai_b200 import synth
+    P = 3
+    off, vals = synth.generate(N, P, seed=91)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    full = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
+    pin = torch.full((N, N), -7.0, dtype=torch.float64).pin_memory()
+    M = pin.numpy()
+    ctx.set_global_matrix(True)
+    written = np.zeros((N, N), bool)
+    for s in range(n_shards):
+        ctx.set_shard(s, n_shards)
+        before = M.copy()
+        ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=M)
+        assert ctx.matrix_shape() == (N, N)
+        now = (M != before)
+        assert not np.any(now & written), "two shards wrote the same cell"
+        written |= now
+    assert not np.any(M == -7.0)
+    assert np.array_equal(M, full)
+    # the staged (device matrix) variant of the same addressing: zeros outside the shard's cells
+    ctx.set_shard(0, n_shards)
+    dev = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+    own = np.zeros(N, bool); own[ctx.shard_layout()[1]] = True
+    iu = np.triu(np.ones((N, N), bool), 1)
+    mine = (iu & own[:, None]) | (iu & own[:, None]).T
+    assert np.array_equal(dev[mine], full[mine]) and not np.any(dev[~mine])
+    ctx.set_global_matrix(False)
+    ctx.set_shard(0, 1)
+    ctx.close()

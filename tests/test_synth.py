@@ -44,3 +44,18 @@ def test_reference_arrays_roundtrip_and_direct_agrees():
     assert np.array_equal(d["counts"][iu], r["counts"])
     assert np.array_equal(d["aji"], r["matrix"])
     assert (r["jac"]["N"] == 0).sum() == 0          # no zero-share pairs
+
+
+def test_subset_generation_reproduces_the_full_database_lists():
+    """generate_subset: the lists of a few genomes of a large synthetic database, without generating the database
+    (bench.py's per-rank parity check relies on it)."""
+    from parfastaai_b200 import synth
+    N, P = 300, 5
+    off, vals = synth.generate(N, P, seed=7)
+    ids = np.array([5, 299, 17, 0], np.int32)
+    for dense in (False, True):
+        offd, valsd = synth.generate(N, P, seed=7, dense=dense)
+        o2, v2 = synth.generate_subset(N, P, 7, ids, dense=dense)
+        for k, g in enumerate(ids):
+            for p in range(P):
+                assert np.array_equal(valsd[offd[g * P + p]:offd[g * P + p + 1]], v2[o2[k * P + p]:o2[k * P + p + 1]])
