@@ -63,8 +63,15 @@ typedef struct {
     int32_t n_launches;  /* kernels launched by the last build + compute                 */
     int32_t n_tiles;     /* tiles the core kernel processed                              */
     int64_t tile_alg_bytes; /* algorithmic bytes of the core kernel   */
-    float dict_ms;       /* column-block dictionary build inside compute                 */
+    float dict_ms;       /* column-block dictionary build inside compute (list path)     */
     int32_t reserved_;
+    int32_t path;        /* tile path of the last compute: 1 = lists (aji_tile_kernel), 2 = dense contraction (aji_mma_kernel) */
+    int32_t dense_tau;   /* dense path: posting lists at least this long are tensor-core columns                */
+    int64_t dense_k_sum; /* dense path: dense tetramers over all SCPs (padded to 32 per SCP)                    */
+    int64_t patch_records; /* dense path: co-occurrences on non-dense tetramers, added as patch records        */
+    int64_t e_size;      /* |E| = sum over posting lists of n(n-1)/2 (the reference's E array, all-vs-all), when known, else -1 */
+    float prep_ms;       /* dense path: list lengths + dense ids + operand images + patches inside compute      */
+    int32_t reserved2_;
 } pfaai_timings_t;
 
 /* ---- life cycle ------------------------------------------------------------------------------ */
@@ -90,6 +97,19 @@ int  pfaai_gpu_set_shard(pfaai_gpu_ctx *ctx, int shard, int n_shards);
  * complete in host memory: no gather, no host-side mirror pass (src/main.cpp:143-154 done by the kernels' own stores).
  * pfaai_gpu_matrix_shape then reports G x G.  Off (default): compact per-shard matrices as described above. */
 int  pfaai_gpu_set_global_matrix(pfaai_gpu_ctx *ctx, int on);
+/* Which tile kernel the next computes use (BASELINE north_star: "ncu evidence decides between the two paths"):
+ *   PFAAI_PATH_AUTO   (default) a cost model on the measured posting-list length distribution picks per compute call;
+ *   PFAAI_PATH_LISTS  the dictionary walk (aji_tile_kernel: bit-sliced counters, no tensor cores) -- sparse inputs;
+ *   PFAAI_PATH_MMA    the dense contraction (aji_mma_kernel: 0/1 u8 operands on tcgen05 tensor cores + exact patch records
+ *                     for the non-dense tetramers) -- real-like inputs whose per-SCP vocabulary is dense.  Needs an
+ *                     unpartitioned build and at most 255 SCPs; fails with PFAAI_ERR_CONSTRUCT otherwise.
+ * Both paths produce identical counts / S / N / AJI.  tau > 0 fixes the density threshold of the dense path (posting lists of at
+ * least tau genomes become tensor-core columns, shorter ones patch records); 0 = chosen by the cost model. */
+enum pfaai_path { PFAAI_PATH_AUTO = 0, PFAAI_PATH_LISTS = 1, PFAAI_PATH_MMA = 2 };
+int  pfaai_gpu_set_path(pfaai_gpu_ctx *ctx, int path, int tau);
+/* |E| of the built index for all-vs-all (sum over (SCP, tetramer) posting lists of n(n-1)/2: the size of the reference's E
+ * array, countTetramerTuples ds_helper.hpp:206-265) -- the layout-independent work unit of SURVEY 8(d). */
+int  pfaai_gpu_e_size(pfaai_gpu_ctx *ctx, int64_t *e_size);
 /* layout of the last compute: axis (0 = rows, 1 = columns) that is sharded, the number of owned indices along it and
  * (ids != NULL) their global indices in storage order.  Unsharded: n = the full extent, ids = 0..n-1. */
 int  pfaai_gpu_shard_layout(const pfaai_gpu_ctx *ctx, int *axis, int64_t *n, int32_t *ids);

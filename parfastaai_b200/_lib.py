@@ -19,6 +19,7 @@ JAC_DTYPE = np.dtype([("gA", "<i4"), ("gB", "<i4"), ("S", "<f8"), ("N", "<i4"), 
 assert JAC_DTYPE.itemsize == 24
 
 ALL_VS_ALL, QUERY_SUBSET, QUERY_DB = 0, 1, 2
+PATH_AUTO, PATH_LISTS, PATH_MMA = 0, 1, 2
 FLAG_REF_COMPAT_QT = 1
 NTETRA = 160000
 
@@ -30,14 +31,16 @@ EXPORTS = [
     "pfaai_gpu_build_partitioned", "pfaai_gpu_exchange_buffers", "pfaai_gpu_finish_partitioned", "pfaai_gpu_exchange_local",
     "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
     "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
-    "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench",
+    "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench", "pfaai_gpu_set_path", "pfaai_gpu_e_size",
 ]
 
 
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("build_ms", C.c_float), ("sort_ms", C.c_float), ("pack_ms", C.c_float),
                 ("tile_ms", C.c_float), ("d2h_ms", C.c_float), ("n_launches", C.c_int32), ("n_tiles", C.c_int32),
-                ("tile_alg_bytes", C.c_int64), ("dict_ms", C.c_float), ("reserved_", C.c_int32)]
+                ("tile_alg_bytes", C.c_int64), ("dict_ms", C.c_float), ("reserved_", C.c_int32),
+                ("path", C.c_int32), ("dense_tau", C.c_int32), ("dense_k_sum", C.c_int64), ("patch_records", C.c_int64),
+                ("e_size", C.c_int64), ("prep_ms", C.c_float), ("reserved2_", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -106,6 +109,8 @@ def load():
     L.pfaai_gpu_build_routed.argtypes = [vp, i64]
     L.pfaai_gpu_route_local.argtypes = [C.POINTER(vp), i32]
     L.pfaai_gpu_set_global_matrix.argtypes = [vp, i32]
+    L.pfaai_gpu_set_path.argtypes = [vp, i32, i32]
+    L.pfaai_gpu_e_size.argtypes = [vp, C.POINTER(i64)]
     L.pfaai_gpu_microbench.argtypes = [vp, i32, C.c_double, i32, C.POINTER(Microbench)]
     _lib = L
     return L
@@ -157,6 +162,17 @@ class PfaaiGpu:
         """Sharded all-vs-all: address the full G x G matrix (shared by all shards) and store the mirror images too."""
         self._check(self._L.pfaai_gpu_set_global_matrix(self._h, int(bool(on))), "set_global_matrix")
         self._global = bool(on)
+
+    def set_path(self, path=PATH_AUTO, tau=0):
+        """Tile path of the next computes: PATH_AUTO (cost model), PATH_LISTS (dictionary walk), PATH_MMA (tcgen05 dense
+        contraction + patches); tau > 0 fixes the dense path's posting-list length threshold."""
+        self._check(self._L.pfaai_gpu_set_path(self._h, int(path), int(tau)), "set_path")
+
+    def e_size(self):
+        """|E| of the built index (all-vs-all): sum over posting lists of n(n-1)/2."""
+        e = C.c_int64()
+        self._check(self._L.pfaai_gpu_e_size(self._h, C.byref(e)), "e_size")
+        return int(e.value)
 
     def upload_index(self, P, G, F, Lc, T=None):
         F = np.ascontiguousarray(F, dtype=PG_DTYPE)

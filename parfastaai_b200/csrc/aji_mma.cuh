@@ -1,0 +1,405 @@
+// aji_mma.cuh -- K5 of DESIGN.md: the dense-contraction tile path (tcgen05 tensor cores) of the AJI hot path.
+//
+// Replaces the same reference loci as aji_tile.cuh (constructTetramerTuples ds_helper.hpp:270-357, parallelMergeSort
+// psort.hpp:27-53, findEBlockExtents / computeEBlockJAC / computeAJI algorithm_impl.hpp:123-322, printOutput's matrix fill
+// main.cpp:143-154) and is selected instead of the list path where the per-SCP tetramer density makes the intersection count a
+// dense contraction (BASELINE north_star; the decision rule and the evidence are in DESIGN.md section 4b).
+//
+// Formulation.  Per SCP p the tetramers whose posting list is at least `tau` genomes long are the DENSE columns 0..K_p-1.
+// With X_p[g][k] = 1 iff genome g holds dense tetramer k of SCP p (one unsigned byte), the intersection count restricted to
+// dense tetramers is the integer matrix product  C_p = X_p(rows) * X_p(cols)^T  -- computed exactly by tcgen05.mma kind::i8
+// (u8 x u8 -> s32 accumulators in tensor memory).  Every co-occurrence on a NON-dense tetramer (short lists: n(n-1)/2 pairs each)
+// is enumerated once on the device into per-(tile, SCP, 32x32 sub-tile) PATCH records that the epilogue adds to C_p, so the
+// counts are bit-exact for any input; the cost model in pfaai_gpu.cu picks tau (and falls back to the list path when the
+// patches would outweigh the contraction).
+//
+//   tile      : 128 rows x 128 columns of genome pairs, one persistent CTA per SM, SCPs in ascending order (the reference's
+//               summation order).
+//   operands  : X is stored in HBM as ready-to-use shared-memory images, one per (128-genome block, SCP): K-major, no swizzle,
+//               core matrix = 8 genomes x 16 dense tetramers (128 contiguous bytes); byte (r, k) of an image sits at
+//               (k/16)*2048 + r*16 + k%16, so any K-range of all 128 genomes is ONE contiguous bulk copy (cp.async.bulk,
+//               SASS UBLKCP) -- no tensor maps.  A stage = 128 dense tetramers of the row block + of the column block (32 KB),
+//               4 stages.
+//   roles     : warp 16 lane 0 = bulk-copy producer; warp 17 lane 0 = tcgen05.mma issuer (M = N = 128, K = 32 per instruction,
+//               accumulators double-buffered in tensor memory: 2 x 128 columns); warps 0..15 = epilogue.  mbarrier pipelines:
+//               full/empty per stage, acc_full/acc_empty per accumulator buffer, ct_full/ct_empty for the ring of column T values.
+//   epilogue  : thread = (row = tensor-memory lane, 32 columns).  tcgen05.ld brings the counts, the patch records of the warp's
+//               32x32 sub-tile are added through a warp-private shared-memory counter array, then J = c/(Ta+Tb-c) (reciprocal
+//               table + two FMAs, correctly rounded: tests/test_division.py), S += J in fp64 REGISTERS, N += (c > 0).
+//               While the epilogue of SCP p runs, the tensor cores already work on SCP p+1.
+//   output    : AJI = S/N staged through shared memory in four 32-column rounds and written as contiguous row segments
+//               (and column segments for the mirror image / the transposed query modes), device memory or pinned host memory.
+#pragma once
+#include "aji_tile.cuh"
+
+namespace pfaai {
+
+constexpr int MM_ROWS = 128, MM_COLS = 128;          // tile
+constexpr int MM_EPI_WARPS = 16;
+constexpr int MM_THREADS = (MM_EPI_WARPS + 2) * 32;   // + producer warp + MMA warp
+constexpr int MM_STAGE_K = 128;                       // dense tetramers per pipeline stage
+constexpr int MM_OP_BYTES = MM_STAGE_K * 128;         // one operand of one stage: 128 genomes x 128 k = 16 KB
+constexpr int MM_STAGE_BYTES = 2 * MM_OP_BYTES;
+constexpr int MM_NSTAGE = 4;
+constexpr int MM_CT_RING = 4;                         // ring of column T values (128 x int32 per SCP)
+constexpr int MM_CNT_PITCH = 80;                      // bytes per row of a warp's patch counters (32 x uint16 + pad: conflict-free LDS.128)
+constexpr int MM_CNT_WARP = 32 * MM_CNT_PITCH;        // 2560 B per warp
+constexpr int MM_STG_PITCH = 33;                      // output staging [128][33] doubles (one 32-column round)
+constexpr int MM_SMEM_MISC = 1024;
+constexpr int MM_SMEM_CT = MM_CT_RING * MM_COLS * 4;
+constexpr int MM_SMEM_CNT = MM_EPI_WARPS * MM_CNT_WARP;   // 40960 >= 128*33*8 = 33792 (staging shares it)
+static_assert(MM_SMEM_CNT >= MM_ROWS * MM_STG_PITCH * 8, "output staging does not fit the patch-counter area");
+constexpr int MM_SMEM_TOTAL = MM_SMEM_MISC + MM_SMEM_CT + SMEM_RCP + MM_SMEM_CNT + MM_NSTAGE * MM_STAGE_BYTES;
+static_assert(MM_SMEM_TOTAL <= SMEM_TOTAL, "K5 shared memory");
+constexpr int MM_TMEM_COLS = 256;                     // 2 accumulator buffers x 128 columns (s32)
+constexpr uint16_t MM_NOT_DENSE = 0xffffu;
+
+struct MmaParams {
+    // operand images: block b of the row / column list, SCP p -> img + b*blk_stride + koff[p]*128, kpad[p]*128 bytes
+    const unsigned char *img_rows, *img_cols;
+    int64_t blk_stride;                 // bytes per 128-genome block = 128 * sum(kpad)
+    const int32_t *kpad;                // [P] dense tetramers of SCP p, padded to a multiple of 32 (0: none)
+    const int64_t *koff;                // [P] exclusive prefix sum of kpad
+    // patches: records of sub-tile key ((I*ncb + J)*P + p)*16 + (row/32)*4 + col/32 are rec[poff[key] .. poff[key+1])
+    const int64_t *poff;
+    const uint16_t *rec;                // (row & 31) | (col & 31) << 5
+    int has_patches;
+    // rows / columns (kernel index -> genome id, T column)
+    const int32_t *rows, *row_t, *cols, *col_t;
+    int n_rows, n_cols, ncb;            // ncb = column blocks of 128
+    const int32_t *T;                   // [P x t_ld]
+    const int32_t *colT;                // [ncb][P][128]: T(p, col_t[column]) (0 beyond n_cols)
+    const int32_t *rowTmax, *colTmax;   // [nrb][P], [ncb][P]: max T over the block (fast-path guard: sum < RCP_N)
+    int t_ld, P;
+    int quirk;                          // 1: T labels are not the genomes' own (query-DB label quirk): always the guarded division
+    // output (same conventions as TileParams)
+    double *out;
+    int64_t out_rs, out_cs;
+    int symmetric, mirror;
+    double *S_out; int32_t *N_out; int32_t *counts_out;
+    const int4 *tiles;                  // (row block I, column block J, first output row of block I, unused)
+    int n_tiles;
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// the mbarrier receives one arrival when every tcgen05 operation issued so far by this thread has completed
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// shared-memory matrix descriptor, K-major, no swizzle: core matrix (8 rows x 16 B) contiguous, next 8 rows +128 B (SBO),
+// next 16 bytes of K +2048 B (LBO); descriptor version 1 (sm_100)
+__device__ __forceinline__ uint64_t mm_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)(2048u >> 4) << 16) | ((uint64_t)(128u >> 4) << 32) | (1ull << 46);
+}
+// instruction descriptor: D = s32 (2 << 4), A = B = unsigned 8-bit (0), both K-major, N = 128 (16 << 17), M = 128 (8 << 24)
+constexpr uint32_t MM_IDESC = (2u << 4) | ((uint32_t)(MM_COLS >> 3) << 17) | ((uint32_t)(MM_ROWS >> 4) << 24);
+__device__ __forceinline__ void mm_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(MM_IDESC), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ double u32_to_f64(uint32_t v) {     // exact, on the fp64 pipe (no conversion unit)
+    return __hiloint2double(0x43300000, (int)v) - 4503599627370496.0;
+}
+
+template <int DUMMY = 0>
+__global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams prm) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem);                  // [NSTAGE]
+    uint64_t *empty = full + MM_NSTAGE;                                   // [NSTAGE]
+    uint64_t *acc_full = empty + MM_NSTAGE;                               // [2]
+    uint64_t *acc_empty = acc_full + 2;                                   // [2]
+    uint64_t *ct_full = acc_empty + 2;                                    // [CT_RING]
+    uint64_t *ct_empty = ct_full + MM_CT_RING;                            // [CT_RING]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + 192);
+    int32_t *col_g = reinterpret_cast<int32_t *>(smem + 256);             // [128] genome id of the tile's columns (output phase)
+    int32_t *ctring = reinterpret_cast<int32_t *>(smem + MM_SMEM_MISC);   // [CT_RING][128]
+    double *rcp = reinterpret_cast<double *>(smem + MM_SMEM_MISC + MM_SMEM_CT);
+    unsigned char *cnt_mem = smem + MM_SMEM_MISC + MM_SMEM_CT + SMEM_RCP;
+    unsigned char *stage_mem = cnt_mem + MM_SMEM_CNT;
+    static_assert((2 * MM_NSTAGE + 4 + 2 * MM_CT_RING) * 8 <= 192 && 256 + MM_COLS * 4 <= MM_SMEM_MISC, "misc area");
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int P = prm.P;
+
+    if (tid == 0) {
+        for (int s = 0; s < MM_NSTAGE; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; b++) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], MM_EPI_WARPS); }
+        for (int s = 0; s < MM_CT_RING; s++) { mbar_init(&ct_full[s], 1); mbar_init(&ct_empty[s], MM_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(tmem_slot, MM_TMEM_COLS);
+    for (int i = tid; i < RCP_N; i += MM_THREADS) rcp[i] = (i > 0) ? 1.0 / (double)i : 0.0;
+    for (int i = tid; i < MM_SMEM_CNT / 4; i += MM_THREADS) reinterpret_cast<uint32_t *>(cnt_mem)[i] = 0u;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == MM_EPI_WARPS) {
+        // ===================== producer: bulk copies of the operand images and the column T values =====================
+        if (lane == 0) {
+            uint32_t it = 0, ci = 0;
+            for (int tile_i = blockIdx.x; tile_i < prm.n_tiles; tile_i += gridDim.x) {
+                const int4 tile = prm.tiles[tile_i];
+                const unsigned char *a_img = prm.img_rows + (int64_t)tile.x * prm.blk_stride;
+                const unsigned char *b_img = prm.img_cols + (int64_t)tile.y * prm.blk_stride;
+                for (int p = 0; p < P; p++) {
+                    {   // column T values of SCP p
+                        const uint32_t s = ci % MM_CT_RING, ph = (ci / MM_CT_RING) & 1u;
+                        mbar_wait(&ct_empty[s], ph ^ 1u);
+                        mbar_expect_tx(&ct_full[s], MM_COLS * 4u);
+                        bulk_g2s(ctring + s * MM_COLS, prm.colT + ((int64_t)tile.y * P + p) * MM_COLS, MM_COLS * 4u, &ct_full[s]);
+                        ci++;
+                    }
+                    const int kp = __ldg(prm.kpad + p);
+                    const int64_t ko = __ldg(prm.koff + p) * 128;
+                    for (int k0 = 0; k0 < kp; k0 += MM_STAGE_K) {
+                        const uint32_t s = it % MM_NSTAGE, ph = (it / MM_NSTAGE) & 1u;
+                        const uint32_t bytes = (uint32_t)min(MM_STAGE_K, kp - k0) * 128u;
+                        mbar_wait(&empty[s], ph ^ 1u);
+                        mbar_expect_tx(&full[s], 2u * bytes);
+                        unsigned char *dst = stage_mem + (size_t)s * MM_STAGE_BYTES;
+                        bulk_g2s(dst, a_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
+                        bulk_g2s(dst + MM_OP_BYTES, b_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
+                        it++;
+                    }
+                }
+            }
+        }
+    } else if (warp == MM_EPI_WARPS + 1) {
+        // ===================== tensor-core issuer =====================
+        if (lane == 0) {
+            uint32_t it = 0, ai = 0;
+            const uint32_t stage32 = smem_u32(stage_mem);
+            for (int tile_i = blockIdx.x; tile_i < prm.n_tiles; tile_i += gridDim.x) {
+                for (int p = 0; p < P; p++) {
+                    const int kp = __ldg(prm.kpad + p);
+                    if (kp == 0) continue;
+                    const uint32_t buf = ai & 1u, aph = (ai >> 1) & 1u;
+                    mbar_wait(&acc_empty[buf], aph ^ 1u);        // the epilogue has read this buffer's previous SCP
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + buf * MM_COLS;
+                    for (int k0 = 0; k0 < kp; k0 += MM_STAGE_K) {
+                        const uint32_t s = it % MM_NSTAGE, ph = (it / MM_NSTAGE) & 1u;
+                        mbar_wait(&full[s], ph);
+                        tc_fence_after();
+                        const uint32_t a32 = stage32 + s * MM_STAGE_BYTES, b32 = a32 + MM_OP_BYTES;
+                        const int nk = min(MM_STAGE_K, kp - k0) / 32;
+                        for (int k = 0; k < nk; k++)
+                            mm_mma(d_tmem, mm_desc(a32 + k * 4096), mm_desc(b32 + k * 4096), (k0 | k) ? 1u : 0u);
+                        tc_commit(&empty[s]);                    // the stage is free once these MMAs have read it
+                        it++;
+                    }
+                    tc_commit(&acc_full[buf]);                   // SCP p's counts are complete in tensor memory
+                    ai++;
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue warps: counts -> Jaccard -> S, N -> AJI =====================
+        const int q = warp & 3, cg = warp >> 2;                  // tensor-memory lane quadrant (rows 32q..), column group (cols 32cg..)
+        const int rl = q * 32 + lane;                            // row of the tile
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        unsigned char *cw = cnt_mem + warp * MM_CNT_WARP;        // this warp's 32 x 32 patch counters (uint16)
+        const uint32_t cw32 = smem_u32(cw);
+        const uint32_t rcp32 = smem_u32(rcp);
+        uint32_t ai = 0, ci = 0;
+        for (int tile_i = blockIdx.x; tile_i < prm.n_tiles; tile_i += gridDim.x) {
+            const int4 tile = prm.tiles[tile_i];
+            const int row = tile.x * MM_ROWS + rl;
+            const bool row_ok = row < prm.n_rows;
+            const int gi = row_ok ? prm.rows[row] : -1;
+            const int ti = row_ok ? prm.row_t[row] : 0;
+            const int j0 = tile.y * MM_COLS;
+            const int ncol = min(MM_COLS, prm.n_cols - j0);
+            const int64_t key0 = ((int64_t)tile.x * prm.ncb + tile.y) * P * 16 + (q * 4 + cg);
+
+            double S[32];
+            uint32_t N8[8];
+#pragma unroll
+            for (int j = 0; j < 32; j++) S[j] = 0.0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) N8[j] = 0u;
+            // columns of this thread that are real pairs (isValidPair): inside the matrix and not the row's own genome
+            uint32_t valid = 0u;
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                const int col = cg * 32 + j;
+                const int gj = (col < ncol) ? __ldg(prm.cols + j0 + col) : -1;
+                if (row_ok && gj >= 0 && gj != gi) valid |= 1u << j;
+            }
+            int ta = row_ok ? __ldg(prm.T + ti) : 0;                                     // SCP 0
+            int64_t po0 = 0, po1 = 0;
+            if (prm.has_patches) { po0 = __ldg(prm.poff + key0); po1 = __ldg(prm.poff + key0 + 1); }
+            const bool never_fast = prm.quirk != 0;
+
+            for (int p = 0; p < P; p++) {
+                // prefetch the next SCP's row T value and patch extent
+                int ta_nxt = 0; int64_t pn0 = 0, pn1 = 0;
+                if (p + 1 < P) {
+                    if (row_ok) ta_nxt = __ldg(prm.T + (int64_t)(p + 1) * prm.t_ld + ti);
+                    if (prm.has_patches) { pn0 = __ldg(prm.poff + key0 + (int64_t)(p + 1) * 16); pn1 = __ldg(prm.poff + key0 + (int64_t)(p + 1) * 16 + 1); }
+                }
+                const int kp = __ldg(prm.kpad + p);
+                const bool fast = !never_fast &&
+                                  (__ldg(prm.rowTmax + (int64_t)tile.x * P + p) + __ldg(prm.colTmax + (int64_t)tile.y * P + p) < RCP_N);
+                // ---- patches of this warp's sub-tile: scatter into the warp-private counters ----
+                const uint32_t np = (uint32_t)(po1 - po0);
+                if (np) {
+                    for (uint32_t i = lane; i < np; i += 32) {
+                        const uint32_t r = __ldg(prm.rec + po0 + i);
+                        const uint32_t a = (r & 31u) * MM_CNT_PITCH + ((r >> 5) & 31u) * 2u;
+                        atomicAdd(reinterpret_cast<uint32_t *>(cw + (a & ~3u)), 1u << (8u * (a & 2u)));
+                    }
+                    __syncwarp();
+                }
+                // ---- column T values ----
+                const uint32_t cs = ci % MM_CT_RING;
+                mbar_wait(&ct_full[cs], (ci / MM_CT_RING) & 1u);
+                const uint32_t ct32 = smem_u32(ctring + cs * MM_COLS + cg * 32);
+                // ---- counts from tensor memory ----
+                uint32_t buf = 0u;
+                if (kp) {
+                    buf = ai & 1u;
+                    mbar_wait(&acc_full[buf], (ai >> 1) & 1u);
+                    tc_fence_after();
+                }
+#pragma unroll
+                for (int hf = 0; hf < 2; hf++) {
+                    uint32_t cv[16];
+                    if (kp) {
+                        tmem_ld16(tmem_base + lane_addr + buf * MM_COLS + cg * 32 + hf * 16, cv);
+                        tmem_wait_ld(cv);
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < 16; u++) cv[u] = 0u;
+                    }
+                    if (hf == 1 && kp) {                    // both halves are in registers: hand the buffer back to the tensor cores
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+                    }
+                    if (np) {                               // warp-uniform: add this row's patch counters, then clear them
+#pragma unroll
+                        for (int v4 = 0; v4 < 2; v4++) {
+                            uint32_t w0, w1, w2, w3;
+                            const uint32_t a = cw32 + lane * MM_CNT_PITCH + hf * 32 + v4 * 16;
+                            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(a));
+                            asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(a), "r"(0u) : "memory");
+                            const uint32_t w[4] = {w0, w1, w2, w3};
+#pragma unroll
+                            for (int u = 0; u < 4; u++) { cv[v4 * 8 + 2 * u] += w[u] & 0xffffu; cv[v4 * 8 + 2 * u + 1] += w[u] >> 16; }
+                        }
+                    }
+                    // ---- Jaccard + S, N for 16 columns ----
+#pragma unroll
+                    for (int g4 = 0; g4 < 4; g4++) {
+                        int tb0, tb1, tb2, tb3;
+                        asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(tb0), "=r"(tb1), "=r"(tb2), "=r"(tb3)
+                                     : "r"(ct32 + 4u * (uint32_t)(hf * 16 + g4 * 4)));
+                        const int tbv[4] = {tb0, tb1, tb2, tb3};
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            const int j = hf * 16 + g4 * 4 + u;
+                            const uint32_t c = ((valid >> j) & 1u) ? cv[g4 * 4 + u] : 0u;
+                            double J;
+                            if (fast) {
+                                // den < RCP_N and c <= den hold for the whole (tile, SCP): table reciprocal + 2 FMAs == IEEE division
+                                const uint32_t den = (uint32_t)(ta + tbv[u]) - c;
+                                const double r = lds_f64(rcp32 + 8u * den), cd = u32_to_f64(c), dd = u32_to_f64(den);
+                                const double qq = __dmul_rn(cd, r);
+                                J = __fma_rn(__fma_rn(-qq, dd, cd), r, qq);
+                            } else {
+                                const int den = max(ta + tbv[u] - (int)c, 1);
+                                J = (double)(int)c / (double)den;            // algorithm_impl.hpp:250-254
+                            }
+                            S[j] += J;
+                            N8[j >> 2] += (c ? 1u : 0u) << (8 * (j & 3));
+                            if (prm.counts_out) {
+                                const int col = cg * 32 + j;
+                                if (row_ok && col < ncol) prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = (int)c;
+                            }
+                        }
+                    }
+                }
+                if (kp) ai++;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ct_empty[cs]);
+                ci++;
+                ta = ta_nxt; po0 = pn0; po1 = pn1;
+            }
+
+            // ================= output: AJI = S / N (computeAJI) into the dense matrix, four 32-column rounds =================
+            double *stg = reinterpret_cast<double *>(cnt_mem);                 // [128][MM_STG_PITCH]
+            if (cg == 0) col_g[rl] = (rl < ncol) ? prm.cols[j0 + rl] : -1;     // 128 column genomes, written by the 4 warps of group 0
+            const int row0 = tile.x * MM_ROWS;
+            const int nrow = min(MM_ROWS, prm.n_rows - row0);
+            const int64_t ro0 = (int64_t)tile.z;
+            for (int round = 0; round < 4; round++) {
+                asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");      // staging (== patch counters) is free
+                if (cg == round) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const int n = (int)((N8[j >> 2] >> (8 * (j & 3))) & 0xffu);
+                        stg[rl * MM_STG_PITCH + j] = n ? S[j] / (double)n : 0.0;
+                        const int col = cg * 32 + j;
+                        if (row_ok && col < ncol) {
+                            if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + (j0 + col)] = S[j];
+                            if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + (j0 + col)] = n;
+                        }
+                    }
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");
+                const int c0 = round * 32, nc = min(32, ncol - c0);
+                if (nc > 0) {
+                    if (prm.out_cs == 1) {
+                        // direct cells: one 256-B row segment per warp instruction; symmetric: only gi <= gj, diagonal = 0
+                        for (int r2 = warp; r2 < nrow; r2 += MM_EPI_WARPS) {
+                            const int g_i = prm.rows[row0 + r2];
+                            double *dst = prm.out + (ro0 + r2) * prm.out_rs + j0 + c0;
+                            if (lane < nc) {
+                                const int g_j = col_g[c0 + lane];
+                                const double v = stg[r2 * MM_STG_PITCH + lane];
+                                if (prm.symmetric) { if (g_i <= g_j) dst[lane] = (g_i == g_j) ? 0.0 : v; }
+                                else dst[lane] = (g_i == g_j) ? 0.0 : v;
+                            }
+                        }
+                    }
+                    if (prm.out_cs != 1 || prm.mirror) {
+                        // transposed cells: for a fixed column the tile's rows are contiguous in the output
+                        const int64_t cstride = (prm.out_cs != 1) ? prm.out_cs : prm.out_rs;
+                        const int64_t rbase = (prm.out_cs != 1) ? ro0 : (int64_t)row0;
+                        for (int c = warp; c < nc; c += MM_EPI_WARPS) {
+                            const int g_j = col_g[c0 + c];
+                            double *dst = prm.out + (int64_t)(j0 + c0 + c) * cstride + rbase;
+                            for (int r2 = lane; r2 < nrow; r2 += 32) {
+                                const int g_i = prm.rows[row0 + r2];
+                                const double v = stg[r2 * MM_STG_PITCH + c];
+                                if (prm.symmetric) { if (g_i < g_j) dst[r2] = v; }
+                                else dst[r2] = (g_i == g_j) ? 0.0 : v;
+                            }
+                        }
+                    }
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");
+            // the staging area doubles as the patch counters: clear what the last round left behind
+            for (int i = tid; i < MM_SMEM_CNT / 4; i += MM_EPI_WARPS * 32) reinterpret_cast<uint32_t *>(cnt_mem)[i] = 0u;
+            asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, MM_TMEM_COLS);
+}
+
+}  // namespace pfaai

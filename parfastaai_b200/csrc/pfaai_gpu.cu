@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include "index_build.cuh"
 #include "microbench.cuh"
+#include "mma_index.cuh"
 #include "tile_index.cuh"
 
 namespace pfaai {
@@ -46,6 +47,11 @@ struct Ctx {
     int64_t slot_cap = 0;                 // dictionary slots (column blocks) per shard chunk
     void *exch_event = nullptr;           // pfaai_gpu_finish_partitioned_async: the exchange is complete when this cudaEvent_t fires
     DevBuf tile_ctr;
+    // dense-contraction path (K5): planning + operands + patches
+    int path_pref = PFAAI_PATH_AUTO, tau_pref = 0;
+    DevBuf mm_len, mm_hist, mm_did, mm_kcnt, mm_kpad, mm_koff, mm_img_rows, mm_img_cols, mm_colT, mm_rowmax, mm_colmax,
+           mm_rowof, mm_colof, mm_owned, mm_pcnt, mm_poff, mm_rec;
+    int64_t e_size = -1;                  // |E| of the built index (exact length histogram), -1 = not computed for this build
     // routed build: this context holds postings [slice_begin, slice_begin + n_slice) of F only
     bool sliced = false;
     int64_t slice_begin = 0, n_slice = 0, nF_total = 0;
@@ -186,7 +192,7 @@ static int build_internal(Ctx *c, bool partitioned) {
     const int P = c->P, G = c->G;
     const int64_t nF = c->nF, nseg = (int64_t)P * G;
     c->launches = 0;
-    c->built = false; c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr;
+    c->built = false; c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr; c->e_size = -1;
     PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
     PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->seg_len, sizeof(uint32_t) * (size_t)nseg));
@@ -287,7 +293,10 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
                      &c->tile_sums, &c->block_hist, &c->block_base, &c->flags, &c->rows, &c->row_t, &c->cols, &c->col_t,
                      &c->ell_nch, &c->ell_off, &c->ell, &c->tiles, &c->out, &c->S_out, &c->N_out, &c->counts_out,
                      &c->nsub, &c->sub, &c->colT, &c->blob, &c->stage_off, &c->stages, &c->stage_rng,
-                     &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr, &c->route_hist, &c->recv};
+                     &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr, &c->route_hist, &c->recv,
+                     &c->mm_len, &c->mm_hist, &c->mm_did, &c->mm_kcnt, &c->mm_kpad, &c->mm_koff, &c->mm_img_rows, &c->mm_img_cols,
+                     &c->mm_colT, &c->mm_rowmax, &c->mm_colmax, &c->mm_rowof, &c->mm_colof, &c->mm_owned, &c->mm_pcnt,
+                     &c->mm_poff, &c->mm_rec};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
@@ -316,6 +325,13 @@ int pfaai_gpu_set_shard(pfaai_gpu_ctx *h, int shard, int n_shards) {
     // the ownership table of the partitioned / routed builds holds one byte per 128 genomes
     if (!c || n_shards < 1 || n_shards > 255 || shard < 0 || shard >= n_shards) { set_error(c, "bad shard (1 <= n_shards <= 255)"); return PFAAI_ERR_CONSTRUCT; }
     c->shard = shard; c->n_shards = n_shards;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_set_path(pfaai_gpu_ctx *h, int path, int tau) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || path < PFAAI_PATH_AUTO || path > PFAAI_PATH_MMA || tau < 0 || tau == 1) { set_error(c, "set_path: bad path / threshold"); return PFAAI_ERR_CONSTRUCT; }
+    c->path_pref = path; c->tau_pref = tau;
     return PFAAI_OK;
 }
 
@@ -822,6 +838,187 @@ static int build_own_dictionaries(Ctx *c) {
     return PFAAI_OK;
 }
 
+
+// =====================================================================================================
+// K5 (dense-contraction path): planning and preparation.  DESIGN.md section 4b.
+// =====================================================================================================
+struct MmaPlan {
+    bool use = false;
+    bool exact = false;                   // the length histogram covers every genome (not the planning sample)
+    uint32_t tau = 0;
+    int64_t k_sum = 0;                    // dense tetramers over all SCPs, padded to 32 per SCP
+    int64_t patch_est = 0;                // co-occurrences on non-dense tetramers (estimate: all-vs-all pairs)
+    int64_t patch_records = 0;
+    bool has_patches = false;
+    double t_mma = 0, t_lists = 0;        // cost-model seconds
+    std::vector<unsigned long long> hist; // [0..HMAX] lists per length (sample units when !exact), [HMAX+1] = sum n(n-1)/2
+    int stride = 1;
+};
+
+// length histogram of the posting lists; stride > 1: every stride-th genome only (the planning estimate, ~|F|/stride work)
+static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl) {
+    const int P = c->P, G = c->G;
+    const int64_t nlen = (int64_t)P * NTETRA;
+    PF_TRY(ensure(c, c->mm_len, sizeof(uint32_t) * (size_t)nlen));
+    PF_TRY(ensure(c, c->mm_hist, sizeof(unsigned long long) * (MM_HMAX + 2)));
+    PF_CUDA(c, cudaMemsetAsync(c->mm_len.p, 0, sizeof(uint32_t) * (size_t)nlen, c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->mm_hist.p, 0, sizeof(unsigned long long) * (MM_HMAX + 2), c->stream));
+    const int64_t nseg = (int64_t)((G + stride - 1) / stride) * P;
+    if (nseg > 0 && c->nF > 0) {
+        k_list_len<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
+            ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), G, P, stride, ptr<uint32_t>(c->mm_len));
+        PF_LAUNCH_CHECK(c);
+    }
+    k_len_hist<<<(unsigned)(c->sm_count * 4), 256, 0, c->stream>>>(ptr<uint32_t>(c->mm_len), nlen, ptr<unsigned long long>(c->mm_hist),
+                                                                   ptr<unsigned long long>(c->mm_hist) + MM_HMAX + 1);
+    PF_LAUNCH_CHECK(c);
+    pl.hist.assign(MM_HMAX + 2, 0ull);
+    PF_CUDA(c, cudaMemcpyAsync(pl.hist.data(), c->mm_hist.p, sizeof(unsigned long long) * (MM_HMAX + 2), cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    pl.stride = stride; pl.exact = (stride == 1);
+    if (pl.exact) c->e_size = (int64_t)pl.hist[MM_HMAX + 1];
+    return PFAAI_OK;
+}
+
+// The decision rule between the two tile paths (north_star: dense contraction only where the per-SCP tetramer density makes it
+// the denser one).  Inputs: the posting-list length histogram, the number of matrix cells this context computes, |F|.
+// Constants are measured rates of this repository's kernels on B200: the list path performs
+// cells * (|F|/G) / 64 dictionary lookups at 8.2e11/s; the dense path streams K_sum bytes of each operand per cell row/column
+// (L2-bound: 7.6e14 multiply-accumulates/s), runs the fp64 epilogue at 5.4e-13 s per (cell, SCP) and pays 1.8e-11 s per patch
+// record (two atomic passes to build, one shared-memory atomic to apply).
+static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_blocks, bool force) {
+    static const uint32_t cand[] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048, 3072, 4096};
+    const int P = c->P, G = c->G;
+    const double s = (double)pl.stride, nF = (double)c->nF;
+    const double all_pairs = std::max(1.0, 0.5 * (double)G * ((double)G - 1.0));
+    const double frac = std::min(1.0, cells / all_pairs);
+    pl.t_lists = cells * (nF / std::max(1, G)) / 64.0 / 8.2e11 + nF * 1.4e-11;
+    double best = 1e300;
+    for (uint32_t tau : cand) {
+        if (c->tau_pref > 0 && tau != cand[0]) break;
+        if (c->tau_pref > 0) tau = (uint32_t)c->tau_pref;
+        const uint32_t m0 = (uint32_t)std::max(1.0, std::ceil((double)tau / s));   // sample count at which a list is called dense
+        double K = 0, E = 0;
+        for (uint32_t m = 1; m <= (uint32_t)MM_HMAX; m++) {
+            const double h = (double)pl.hist[m];
+            if (m >= m0 || m == (uint32_t)MM_HMAX) K += h;
+            else if (m >= 2) E += h * 0.5 * (double)m * (double)(m - 1) * s * s;
+        }
+        const double k_sum = K + 16.0 * P;                                          // padding to 32 per SCP, on average
+        const double img_bytes = (double)img_blocks * 128.0 * k_sum;
+        const double patches = E * frac * (frac < 1.0 ? 2.0 : 1.0);
+        if (c->tau_pref == 0 && (img_bytes > 48e9 || patches > 2.0e9)) continue;
+        const double t = k_sum * cells / 7.6e14 + patches * 1.8e-11 + img_bytes / 3e12;
+        if (t < best) { best = t; pl.tau = tau; pl.k_sum = (int64_t)k_sum; pl.patch_est = (int64_t)patches; }
+    }
+    pl.t_mma = best + cells * P * 5.4e-13 + nF * 2e-11;
+    pl.use = force ? (best < 1e299) : (pl.t_mma < pl.t_lists);
+}
+
+// dense ids, operand images, column T values, patches (everything aji_mma_kernel reads); sets prm's K5 pointers
+static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n_cols, const std::vector<uint8_t> &rb_owned,
+                       std::vector<int32_t> &kpad_host, MmaParams &prm) {
+    const int P = c->P, G = c->G;
+    const int64_t nlen = (int64_t)P * NTETRA;
+    const int nrb = (n_rows + MM_ROWS - 1) / MM_ROWS, ncb = (n_cols + MM_COLS - 1) / MM_COLS;
+    constexpr int KMAX = 16384;
+    // 1. dense tetramers of every SCP
+    PF_TRY(ensure(c, c->mm_did, sizeof(uint16_t) * (size_t)nlen));
+    PF_TRY(ensure(c, c->mm_kcnt, sizeof(int32_t) * (size_t)P));
+    int *err = ptr<int>(c->flags) + 12;
+    PF_CUDA(c, cudaMemsetAsync(err, 0, sizeof(int), c->stream));
+    k_dense_ids<<<(unsigned)P, 1024, 0, c->stream>>>(ptr<uint32_t>(c->mm_len), pl.tau, ptr<uint16_t>(c->mm_did), ptr<int32_t>(c->mm_kcnt), KMAX, err);
+    PF_LAUNCH_CHECK(c);
+    std::vector<int32_t> kcnt(P);
+    int err_h = 0;
+    PF_CUDA(c, cudaMemcpyAsync(kcnt.data(), c->mm_kcnt.p, sizeof(int32_t) * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(&err_h, err, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (err_h) { set_error(c, "dense path: an SCP has more than 16384 dense tetramers at this threshold"); return PFAAI_ERR_CONSTRUCT; }
+    kpad_host.assign(P, 0);
+    std::vector<int64_t> koff(P, 0);
+    int64_t k_sum = 0;
+    for (int p = 0; p < P; p++) { kpad_host[p] = (kcnt[p] + 31) & ~31; koff[p] = k_sum; k_sum += kpad_host[p]; }
+    pl.k_sum = k_sum;
+    PF_TRY(ensure(c, c->mm_kpad, sizeof(int32_t) * (size_t)P));
+    PF_TRY(ensure(c, c->mm_koff, sizeof(int64_t) * (size_t)P));
+    PF_CUDA(c, cudaMemcpyAsync(c->mm_kpad.p, kpad_host.data(), sizeof(int32_t) * (size_t)P, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(c->mm_koff.p, koff.data(), sizeof(int64_t) * (size_t)P, cudaMemcpyHostToDevice, c->stream));
+    // 2. operand images (all-vs-all: the column list IS the row list)
+    const int64_t blk_stride = 128 * k_sum;
+    auto fill = [&](DevBuf &img, const DevBuf &list, int n_list, int nblk) -> int {
+        PF_TRY(ensure(c, img, (size_t)nblk * (size_t)blk_stride));
+        if (blk_stride == 0 || n_list == 0) return PFAAI_OK;
+        PF_CUDA(c, cudaMemsetAsync(img.p, 0, (size_t)nblk * (size_t)blk_stride, c->stream));
+        k_image_fill<<<(unsigned)std::min<int64_t>(ceil_div64((int64_t)n_list * P, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
+            ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), reinterpret_cast<const int32_t *>(list.p), n_list, P, ptr<uint16_t>(c->mm_did),
+            ptr<int64_t>(c->mm_koff), blk_stride, reinterpret_cast<unsigned char *>(img.p));
+        PF_LAUNCH_CHECK(c);
+        return PFAAI_OK;
+    };
+    PF_TRY(fill(c->mm_img_rows, c->rows, n_rows, nrb));
+    const bool same = m.symmetric != 0;
+    if (!same) PF_TRY(fill(c->mm_img_cols, c->cols, n_cols, ncb));
+    // 3. T values per column block, block maxima (fast-division guard)
+    PF_TRY(ensure(c, c->mm_colT, sizeof(int32_t) * (size_t)ncb * P * MM_COLS));
+    PF_TRY(ensure(c, c->mm_colmax, sizeof(int32_t) * (size_t)ncb * P));
+    PF_TRY(ensure(c, c->mm_rowmax, sizeof(int32_t) * (size_t)nrb * P));
+    if (ncb > 0) {
+        k_block_t<<<(unsigned)(ncb * P), 128, 0, c->stream>>>(ptr<int32_t>(c->T), c->G, P, ptr<int32_t>(c->col_t), n_cols, ptr<int32_t>(c->mm_colT),
+                                                              ptr<int32_t>(c->mm_colmax));
+        PF_LAUNCH_CHECK(c);
+    }
+    if (nrb > 0) {
+        k_block_t<<<(unsigned)(nrb * P), 128, 0, c->stream>>>(ptr<int32_t>(c->T), c->G, P, ptr<int32_t>(c->row_t), n_rows, nullptr,
+                                                              ptr<int32_t>(c->mm_rowmax));
+        PF_LAUNCH_CHECK(c);
+    }
+    // 4. patches: every co-occurrence on a tetramer whose list is shorter than tau
+    double e_sparse = 0;
+    for (uint32_t L = 2; L < std::min<uint32_t>(pl.tau, MM_HMAX); L++) e_sparse += (double)pl.hist[L] * 0.5 * L * (L - 1);
+    pl.has_patches = false; pl.patch_records = 0;
+    const int64_t nkeys = (int64_t)nrb * ncb * P * 16;
+    if (e_sparse > 0 && nkeys > 0) {
+        std::vector<int32_t> row_of(G, -1), col_of(G, -1);
+        for (int i = 0; i < n_rows; i++) row_of[m.rows[i]] = i;
+        for (int j = 0; j < n_cols; j++) col_of[m.cols[j]] = j;
+        PF_TRY(upload_i32(c, c->mm_rowof, row_of)); PF_TRY(upload_i32(c, c->mm_colof, col_of));
+        PF_TRY(ensure(c, c->mm_owned, rb_owned.size()));
+        PF_CUDA(c, cudaMemcpyAsync(c->mm_owned.p, rb_owned.data(), rb_owned.size(), cudaMemcpyHostToDevice, c->stream));
+        PF_TRY(ensure(c, c->mm_pcnt, sizeof(uint32_t) * (size_t)nkeys));
+        PF_TRY(ensure(c, c->mm_poff, sizeof(int64_t) * (size_t)(nkeys + 1)));
+        PatchParams q;
+        q.F = ptr<pfaai_pg_t>(c->F); q.Lp = ptr<int64_t>(c->Lp64); q.len = ptr<uint32_t>(c->mm_len); q.tau = pl.tau;
+        q.P = P; q.ncb = ncb; q.symmetric = m.symmetric;
+        q.row_of = ptr<int32_t>(c->mm_rowof); q.col_of = ptr<int32_t>(c->mm_colof); q.rb_owned = ptr<uint8_t>(c->mm_owned);
+        q.cnt = ptr<uint32_t>(c->mm_pcnt); q.poff = nullptr; q.rec = nullptr;
+        const unsigned grid = (unsigned)(c->sm_count * 16);
+        PF_CUDA(c, cudaMemsetAsync(c->mm_pcnt.p, 0, sizeof(uint32_t) * (size_t)nkeys, c->stream));
+        k_patch_enum<false><<<grid, 256, 0, c->stream>>>(q);
+        PF_LAUNCH_CHECK(c);
+        PF_TRY(launch_scan(c, ptr<int32_t>(c->mm_pcnt), nkeys, ptr<int64_t>(c->mm_poff), nullptr));
+        int64_t total = 0;
+        PF_CUDA(c, cudaMemcpyAsync(&total, ptr<int64_t>(c->mm_poff) + nkeys, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+        PF_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (total > 0) {
+            PF_TRY(ensure(c, c->mm_rec, sizeof(uint16_t) * (size_t)total));
+            PF_CUDA(c, cudaMemsetAsync(c->mm_pcnt.p, 0, sizeof(uint32_t) * (size_t)nkeys, c->stream));
+            q.poff = ptr<int64_t>(c->mm_poff); q.rec = ptr<uint16_t>(c->mm_rec);
+            k_patch_enum<true><<<grid, 256, 0, c->stream>>>(q);
+            PF_LAUNCH_CHECK(c);
+            pl.has_patches = true; pl.patch_records = total;
+        }
+    }
+    prm.img_rows = reinterpret_cast<unsigned char *>(c->mm_img_rows.p);
+    prm.img_cols = same ? prm.img_rows : reinterpret_cast<unsigned char *>(c->mm_img_cols.p);
+    prm.blk_stride = blk_stride;
+    prm.kpad = ptr<int32_t>(c->mm_kpad); prm.koff = ptr<int64_t>(c->mm_koff);
+    prm.poff = ptr<int64_t>(c->mm_poff); prm.rec = ptr<uint16_t>(c->mm_rec); prm.has_patches = pl.has_patches ? 1 : 0;
+    prm.colT = ptr<int32_t>(c->mm_colT); prm.rowTmax = ptr<int32_t>(c->mm_rowmax); prm.colTmax = ptr<int32_t>(c->mm_colmax);
+    prm.ncb = ncb;
+    return PFAAI_OK;
+}
+
 template <int NPL, int NPN>
 static int launch_tiles(Ctx *c, const TileParams &prm, int n_tiles, int reserve_sms = 0, cudaStream_t stream = nullptr) {
     if (n_tiles <= 0) return PFAAI_OK;
@@ -854,44 +1051,71 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     PF_CUDA(c, cudaEventRecord(c->ev[EV_P0], c->stream));
     PF_TRY(upload_i32(c, c->rows, m.rows)); PF_TRY(upload_i32(c, c->row_t, m.row_t));
     PF_TRY(upload_i32(c, c->cols, m.cols)); PF_TRY(upload_i32(c, c->col_t, m.col_t));
-    // ---- K4a: pack the row slabs ----
-    const int64_t ngp = (int64_t)n_groups * P, nslab = ngp * NRANGE;
-    PF_TRY(ensure(c, c->ell_nch, sizeof(int32_t) * (size_t)nslab));
-    PF_TRY(ensure(c, c->ell_off, sizeof(int64_t) * (size_t)(nslab + 1)));
-    k_pack_count<<<(unsigned)ceil_div64(ngp, 256), 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals),
-                                                                        ptr<int32_t>(c->rows), n_rows, n_groups, P,
-                                                                        ptr<int32_t>(c->ell_nch));
-    PF_LAUNCH_CHECK(c);
-    PF_TRY(launch_scan(c, ptr<int32_t>(c->ell_nch), nslab, ptr<int64_t>(c->ell_off), nullptr));
-    int64_t total_chunks = 0;
-    PF_CUDA(c, cudaMemcpyAsync(&total_chunks, ptr<int64_t>(c->ell_off) + nslab, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
-    PF_CUDA(c, cudaStreamSynchronize(c->stream));
-    PF_TRY(ensure(c, c->ell, sizeof(uint4) * 32 * (size_t)total_chunks + 4096));   // + slack: the walk prefetches one step past the end
-    if (total_chunks > 0) {
-        k_pack_fill<<<(unsigned)std::min<int64_t>(ceil_div64(ngp, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
-            ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), ptr<int32_t>(c->rows), n_rows, n_groups, P, ptr<int64_t>(c->ell_off),
-            ptr<uint4>(c->ell));
-        PF_LAUNCH_CHECK(c);
+    // ---- which tile path (include/pfaai_gpu.h, pfaai_gpu_set_path) ----
+    const bool sharded = c->n_shards > 1;
+    bool use_mma = false;
+    MmaPlan pl;
+    {
+        const bool mma_possible = !c->partitioned && P <= 255 && c->nF > 0 && n_rows > 0 && n_cols > 0;
+        if (c->path_pref == PFAAI_PATH_MMA && !mma_possible) {
+            set_error(c, "compute: the dense path needs an unpartitioned build, a non-empty index and at most 255 SCPs");
+            return PFAAI_ERR_CONSTRUCT;
+        }
+        if (c->path_pref != PFAAI_PATH_LISTS && mma_possible) {
+            const bool force = c->path_pref == PFAAI_PATH_MMA;
+            const double cells = (double)n_rows * (double)n_cols * (m.symmetric ? 0.5 : 1.0) / (double)c->n_shards;
+            const int64_t img_blocks = (n_rows + MM_ROWS - 1) / MM_ROWS + (m.symmetric ? 0 : (n_cols + MM_COLS - 1) / MM_COLS);
+            // planning on a genome sample first (~|F| / stride work); the exact lengths only when the dense path is taken
+            PF_TRY(mma_length_hist(c, force ? 1 : std::max(1, c->G / 2048), pl));
+            mma_choose(c, pl, cells, img_blocks, force);
+            if (pl.use && !pl.exact) {
+                PF_TRY(mma_length_hist(c, 1, pl));
+                mma_choose(c, pl, cells, img_blocks, force);
+            }
+            if (force && !pl.use) { set_error(c, "compute: the dense path does not fit this input (operand images / patch records too large)"); return PFAAI_ERR_CONSTRUCT; }
+            use_mma = pl.use;
+        }
     }
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_P1], c->stream));
-    // ---- K4b: column-block dictionaries + stage lists (a partitioned context already holds them: built by the shards that
-    //      own the column blocks and exchanged over NVLink before this call) ----
-    const int nrb = (n_groups + TILE_WARPS - 1) / TILE_WARPS, ncb = (n_cols + COLS_PER_TILE - 1) / COLS_PER_TILE;
-    if (c->partitioned) {
-        if (mode != PFAAI_ALL_VS_ALL || c->n_shards < 2) { set_error(c, "compute: a partitioned build serves sharded all-vs-all only (use pfaai_gpu_build)"); return PFAAI_ERR_CONSTRUCT; }
-        if (!c->dict_ready) { set_error(c, "compute: partitioned build not finished (exchange the buffers, then pfaai_gpu_finish_partitioned)"); return PFAAI_ERR_CONSTRUCT; }
-        PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
-        PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
-    } else {
-        PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
-        PF_TRY(make_dictionaries(c, n_cols, nullptr, ncb, 0, ncb, 0, 0, 0, 0));
-        PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
+    const int TR = use_mma ? MM_ROWS : TILE_ROWS, TC = use_mma ? MM_COLS : COLS_PER_TILE;      // tile geometry of the path
+    const int nrb = (n_rows + TR - 1) / TR, ncb = (n_cols + TC - 1) / TC;
+    if (!use_mma) {
+        // ---- K4a: pack the row slabs ----
+        const int64_t ngp = (int64_t)n_groups * P, nslab = ngp * NRANGE;
+        PF_TRY(ensure(c, c->ell_nch, sizeof(int32_t) * (size_t)nslab));
+        PF_TRY(ensure(c, c->ell_off, sizeof(int64_t) * (size_t)(nslab + 1)));
+        k_pack_count<<<(unsigned)ceil_div64(ngp, 256), 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals),
+                                                                            ptr<int32_t>(c->rows), n_rows, n_groups, P,
+                                                                            ptr<int32_t>(c->ell_nch));
+        PF_LAUNCH_CHECK(c);
+        PF_TRY(launch_scan(c, ptr<int32_t>(c->ell_nch), nslab, ptr<int64_t>(c->ell_off), nullptr));
+        int64_t total_chunks = 0;
+        PF_CUDA(c, cudaMemcpyAsync(&total_chunks, ptr<int64_t>(c->ell_off) + nslab, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+        PF_CUDA(c, cudaStreamSynchronize(c->stream));
+        PF_TRY(ensure(c, c->ell, sizeof(uint4) * 32 * (size_t)total_chunks + 4096));   // + slack: the walk prefetches one step past the end
+        if (total_chunks > 0) {
+            k_pack_fill<<<(unsigned)std::min<int64_t>(ceil_div64(ngp, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
+                ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), ptr<int32_t>(c->rows), n_rows, n_groups, P, ptr<int64_t>(c->ell_off),
+                ptr<uint4>(c->ell));
+            PF_LAUNCH_CHECK(c);
+        }
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_P1], c->stream));
+        // ---- K4b: column-block dictionaries + stage lists (a partitioned context already holds them: built by the shards that
+        //      own the column blocks and exchanged over NVLink before this call) ----
+        if (c->partitioned) {
+            if (mode != PFAAI_ALL_VS_ALL || c->n_shards < 2) { set_error(c, "compute: a partitioned build serves sharded all-vs-all only (use pfaai_gpu_build)"); return PFAAI_ERR_CONSTRUCT; }
+            if (!c->dict_ready) { set_error(c, "compute: partitioned build not finished (exchange the buffers, then pfaai_gpu_finish_partitioned)"); return PFAAI_ERR_CONSTRUCT; }
+            PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
+            PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
+        } else {
+            PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
+            PF_TRY(make_dictionaries(c, n_cols, nullptr, ncb, 0, ncb, 0, 0, 0, 0));
+            PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
+        }
     }
     // ---- tile list: row block x column block, I-major so that concurrently resident CTAs share the row
     //      block's slabs in L2; symmetric mode keeps only tiles that contain a cell with row < col.
     //      Sharding: row block I belongs to shard fold(I mod 2n) (folded assignment balances the
     //      triangular work); a sharded context stores only its own row blocks, compactly, in ascending order ----
-    const bool sharded = c->n_shards > 1;
     // compact: the shard's matrix holds only its own row blocks (upper-triangle cells in all-vs-all).  Not compact
     // (pfaai_gpu_set_global_matrix, all-vs-all): every shard addresses the SAME full G x G matrix and stores its cells and their
     // mirror images into it -- the shards' cell sets are disjoint and together cover the matrix
@@ -913,16 +1137,18 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
             nblk[o]++;
         }
     }
+    std::vector<uint8_t> rb_owned(nrb, 0);       // ownership of the path's row blocks (sharding granule: 384 rows, both paths)
     for (int I = 0; I < nrb; I++) {
-        if (fold_owner(I, c->n_shards) != c->shard) continue;
-        const int row0 = I * TILE_ROWS, nr = std::min(TILE_ROWS, n_rows - row0);
+        if (fold_owner((int)(((int64_t)I * TR) / TILE_ROWS), c->n_shards) != c->shard) continue;
+        rb_owned[I] = 1;
+        const int row0 = I * TR, nr = std::min(TR, n_rows - row0);
         for (int J = 0; J < ncb; J++) {
             if (m.symmetric) {
-                const int col_max = std::min((J + 1) * COLS_PER_TILE, n_cols) - 1;
+                const int col_max = std::min((J + 1) * TC, n_cols) - 1;
                 if (row0 > col_max) continue;      // row0 == col_max: the tile still holds the diagonal cell (stored as 0)
             }
             const bool own_dict = !c->partitioned || fold_owner(J / RB_CBS, c->n_shards) == c->shard;
-            (own_dict ? tiles : tiles_late).push_back(make_int4(I, J, compact ? local_rows : row0, slot_of[J]));
+            (own_dict ? tiles : tiles_late).push_back(make_int4(I, J, compact ? local_rows : row0, use_mma ? 0 : slot_of[J]));
         }
         for (int r = 0; r < nr; r++) c->owned_rows.push_back(row0 + r);
         local_rows += nr;
@@ -970,8 +1196,9 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
     PF_CUDA(c, cudaMemsetAsync(c->tile_ctr.p, 0, 2 * sizeof(int), c->stream));
     // list 1 = tiles [0, n1), list 2 (optional) = tiles [n1, n1 + n2): a CTA moves on to list 2 when list 1 is exhausted
-    if (direct_dev && (tiles.empty() || c->nF <= 0))
-        // nothing will be launched: the caller's pinned matrix (no staging buffer, no memset) would stay untouched
+    if (direct_dev && (c->nF <= 0 || (tiles.empty() && (compact || !sharded))))
+        // nothing will be launched: the caller's pinned matrix (no staging buffer, no memset) would stay untouched.  (A shard of a
+        // shared global matrix that owns no row block must leave the other shards' cells alone.)
         PF_CUDA(c, cudaMemsetAsync(direct_dev, 0, sizeof(double) * ncell, c->stream));
     auto launch_lists = [&](int n1, int n2, int reserve, cudaStream_t st) -> int {
         if (n1 + n2 <= 0 || c->nF <= 0) return PFAAI_OK;
@@ -982,7 +1209,27 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         return (P <= 127) ? launch_tiles<12, 7>(c, prm, count, reserve, st) : launch_tiles<12, 10>(c, prm, count, reserve, st);
     };
     const int n_late = (int)tiles.size() - n_early;
-    if (c->partitioned && c->exch_event && n_late > 0) {
+    if (use_mma) {
+        // ---- K5: operands + patches (timed as "prep"), then the tensor-core tile kernel ----
+        MmaParams mp;
+        std::vector<int32_t> kpad_host;
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
+        PF_TRY(mma_prepare(c, m, pl, n_rows, n_cols, rb_owned, kpad_host, mp));
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
+        mp.rows = prm.rows; mp.row_t = prm.row_t; mp.cols = prm.cols; mp.col_t = ptr<int32_t>(c->col_t);
+        mp.n_rows = n_rows; mp.n_cols = n_cols; mp.T = prm.T; mp.t_ld = prm.t_ld; mp.P = P;
+        mp.quirk = (mode == PFAAI_QUERY_DB && (flags & PFAAI_FLAG_REF_COMPAT_QT)) ? 1 : 0;
+        mp.out = prm.out; mp.out_rs = prm.out_rs; mp.out_cs = prm.out_cs; mp.symmetric = prm.symmetric; mp.mirror = prm.mirror;
+        mp.S_out = prm.S_out; mp.N_out = prm.N_out; mp.counts_out = prm.counts_out;
+        mp.tiles = ptr<int4>(c->tiles); mp.n_tiles = (int)tiles.size();
+        PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
+        if (!tiles.empty()) {
+            auto kern = aji_mma_kernel<0>;
+            PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MM_SMEM_TOTAL));
+            kern<<<(unsigned)std::min<int>((int)tiles.size(), c->sm_count), MM_THREADS, MM_SMEM_TOTAL, c->stream>>>(mp);
+            PF_LAUNCH_CHECK(c);
+        }
+    } else if (c->partitioned && c->exch_event && n_late > 0) {
         // The other shards' dictionaries may still be in flight (exchange on the caller's stream).  Instance 1 of the kernel
         // starts now and takes only the tiles on our own column blocks; it leaves some SMs free, because a tile CTA fills its
         // SM (227 KB of shared memory) and would otherwise lock the exchange's collective kernels out.  Instance 2, on a second
@@ -1004,8 +1251,14 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     c->exch_event = nullptr;   // consumed: later computes on this build find the dictionaries in place
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->tm.pack_ms = ev_ms(c, EV_P0, EV_P1);
-    if (!c->partitioned) c->tm.dict_ms = ev_ms(c, EV_K0, EV_K1);
+    c->tm.pack_ms = use_mma ? 0.f : ev_ms(c, EV_P0, EV_P1);
+    if (!c->partitioned) c->tm.dict_ms = use_mma ? 0.f : ev_ms(c, EV_K0, EV_K1);
+    c->tm.prep_ms = use_mma ? ev_ms(c, EV_K0, EV_K1) : 0.f;
+    c->tm.path = use_mma ? PFAAI_PATH_MMA : PFAAI_PATH_LISTS;
+    c->tm.dense_tau = use_mma ? (int32_t)pl.tau : 0;
+    c->tm.dense_k_sum = use_mma ? pl.k_sum : 0;
+    c->tm.patch_records = use_mma ? pl.patch_records : 0;
+    c->tm.e_size = c->e_size;
     c->tm.tile_ms = ev_ms(c, EV_T0, EV_T1);
     c->tm.n_tiles = (int32_t)tiles.size();
     c->tm.n_launches = c->launches;   // build + this compute
@@ -1117,6 +1370,16 @@ int pfaai_gpu_compute(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_
         for (int q = 0; q < n_qry; q++) for (int t = 0; t < nT; t++)
             emit(quirk ? q : nT + q, quirk ? n_qry + t : t, (size_t)t * n_cols + q);
     }
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_e_size(pfaai_gpu_ctx *h, int64_t *e_size) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !e_size || !c->built) { set_error(c, "e_size: index not built"); return PFAAI_ERR_CONSTRUCT; }
+    if (c->partitioned) { set_error(c, "e_size: needs an unpartitioned build (every genome's lists on this GPU)"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    if (c->e_size < 0) { MmaPlan pl; PF_TRY(mma_length_hist(c, 1, pl)); }
+    *e_size = c->e_size;
     return PFAAI_OK;
 }
 

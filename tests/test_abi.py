@@ -58,6 +58,6 @@ def test_no_cpu_fallback(lib):
 def test_struct_layouts():
     from parfastaai_b200 import _lib
     assert _lib.PG_DTYPE.itemsize == 8 and _lib.JAC_DTYPE.itemsize == 24
-    assert C.sizeof(_lib.Timings) == 48
+    assert C.sizeof(_lib.Timings) == 88
     # pfaai_exchange_t: 4 pointers + 2 x 4 int64 + 2 int32; pfaai_route_t: pointer + 17 int64 + 2 int32 (include/pfaai_gpu.h)
     assert C.sizeof(_lib.Exchange) == 104 and C.sizeof(_lib.Route) == 152

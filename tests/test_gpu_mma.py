@@ -1,0 +1,204 @@
+"""GPU parity tests of the dense-contraction tile path (K5: aji_mma_kernel, tcgen05 u8 x u8 -> s32 + patch records).
+
+Same bars as test_gpu_parity.py: per-(pair, SCP) intersection counts and N bit-exact, S within 1e-7, AJI bit-identical to the
+reference goldens and to the oracle; and the two tile paths (PATH_LISTS / PATH_MMA) must agree bit for bit in every output.
+The density threshold tau is forced to several values so that both halves of the path are exercised: tau = 2 puts every shared
+tetramer on the tensor cores (no patches), a large tau moves most co-occurrences into patch records."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+pytestmark = pytest.mark.gpu
+
+from tests import golden_util as gu  # noqa: E402
+from tests.test_gpu_parity import _check_jac, _ctx_for  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def pf():
+    import __graft_entry__ as ge
+    ge.build()
+    import parfastaai_b200 as pf
+    return pf
+
+
+@pytest.fixture(scope="module")
+def orc():
+    from oracle import pfaai_oracle as orc
+    return orc
+
+
+@pytest.mark.parametrize("name", ["xanthodb", "xdb_subset1", "xdb_subset2"])
+@pytest.mark.parametrize("tau", [0, 2, 3, 9])
+def test_all_vs_all_golden_dense_path(pf, orc, name, tau):
+    g = gu.load(name)
+    ctx, P, G = _ctx_for(pf, g)
+    ctx.set_path(pf.PATH_MMA, tau)
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    tm = ctx.timings()
+    assert tm["path"] == pf.PATH_MMA and (tau == 0 or tm["dense_tau"] == tau)
+    if tau >= 3 and G >= tau:
+        assert tm["patch_records"] > 0
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, G, P, g["lc"], g["f"], g["t"])
+    assert np.array_equal(res["counts"], ref["counts"])
+    assert tm["e_size"] == int(ref["counts"].sum())          # |E| of the reference's E array
+    _check_jac(res, g["jac"], g["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    assert np.array_equal(res["matrix"], res["matrix"].T) and np.all(np.diag(res["matrix"]) == 0)
+    ctx.close()
+
+
+@pytest.mark.parametrize("tau", [2, 6])
+def test_query_modes_golden_dense_path(pf, orc, tau):
+    g = gu.load("xanthodb")
+    q = gu.load("xdb_qry_subset")
+    qids = gu.query_subset_ids()
+    ctx, P, G = _ctx_for(pf, g)
+    ctx.set_path(pf.PATH_MMA, tau)
+    res = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.QUERY_SUBSET, G, P, g["lc"], g["f"], g["t"], nQ=len(qids), qry_ids=qids)
+    assert np.array_equal(res["counts"], ref["counts"])
+    _check_jac(res, q["jac"], q["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    ctx.close()
+    # query-DB mode with the reference's label quirk (guarded division: c may exceed the mislabelled denominator)
+    g = gu.load("xdb_qt")
+    ctx, P, Gu = _ctx_for(pf, g, host_T=True)
+    ctx.set_path(pf.PATH_MMA, tau)
+    nQ = 4
+    qids = np.arange(Gu - nQ, Gu, dtype=np.int32)
+    res = ctx.compute(pf.QUERY_DB, qry_ids=qids, flags=pf.FLAG_REF_COMPAT_QT, want_jac=True, want_counts=True)
+    idx = lambda a, b: (a - (Gu - nQ)) * (Gu - nQ) + b
+    assert np.array_equal(res["counts"], gu.run_lengths_from_sorted_e(g["sorted_e"], idx, 16, P))
+    _check_jac(res, g["jac"], g["aji"])
+    res2 = ctx.compute(pf.QUERY_DB, qry_ids=qids, flags=0, want_jac=True)
+    ref2 = orc.full_pipeline(orc.QUERY_DB, Gu, P, g["lc"], g["f"], g["t"], nQ=nQ, quirk=False)
+    assert np.array_equal(res2["aji"], ref2["aji"])
+    ctx.close()
+
+
+@pytest.mark.parametrize("N,P,seed,dense,tau", [(70, 12, 1, False, 2), (200, 9, 2, False, 4), (333, 7, 3, True, 0), (333, 7, 3, True, 40),
+                                                (450, 5, 4, False, 12), (600, 4, 6, True, 3)])
+def test_synthetic_all_vs_all_both_paths_vs_oracle(pf, orc, N, P, seed, dense, tau):
+    """Several 128 x 128 tiles, ragged edges, triangular tile skipping, K chunks beyond one stage, dense and sparse families,
+    patch-heavy thresholds; the list path on the same context must give the same bytes."""
+    from parfastaai_b200 import synth
+    off, vals = synth.generate(N, P, seed=seed, dense=dense)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    ref = orc.full_pipeline(orc.ALL_VS_ALL, N, P, Lc, F, T)
+    ctx.set_path(pf.PATH_MMA, tau)
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    assert ctx.timings()["path"] == pf.PATH_MMA
+    assert np.array_equal(res["counts"], ref["counts"])
+    assert np.array_equal(res["jac"]["N"], ref["jac"]["N"])
+    assert np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    ctx.set_path(pf.PATH_LISTS)
+    res_l = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    assert ctx.timings()["path"] == pf.PATH_LISTS
+    for k in ("counts", "aji", "matrix"):
+        assert np.array_equal(res[k], res_l[k])
+    assert np.array_equal(res["jac"]["S"], res_l["jac"]["S"])
+    ctx.close()
+
+
+def test_synthetic_query_modes_sharding_and_pinned_output_dense_path(pf, orc):
+    import torch
+    from parfastaai_b200 import sharding, synth
+    N, P = 700, 5
+    off, vals = synth.generate(N, P, seed=11, dense=True)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    T = synth.t_matrix(N, P, off)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    ctx.set_path(pf.PATH_MMA, 5)
+    qids = np.array(sorted(np.random.default_rng(5).choice(N, 170, replace=False)), np.int32)
+    res = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.QUERY_SUBSET, N, P, Lc, F, T, nQ=len(qids), qry_ids=qids)
+    assert np.array_equal(res["counts"], ref["counts"]) and np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    nQ = 150
+    q2 = np.arange(N - nQ, N, dtype=np.int32)
+    res = ctx.compute(pf.QUERY_DB, qry_ids=q2, flags=0, want_jac=True, want_counts=True)
+    ref = orc.full_pipeline(orc.QUERY_DB, N, P, Lc, F, T, nQ=nQ, quirk=False)
+    assert np.array_equal(res["counts"], ref["counts"]) and np.array_equal(res["aji"], ref["aji"])
+    assert np.array_equal(res["matrix"], ref["matrix"])
+    # pinned (directly stored) matrices in all three modes, poisoned
+    full = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
+    ref_full = orc.full_pipeline(orc.ALL_VS_ALL, N, P, Lc, F, T)["matrix"]
+    assert np.array_equal(full, ref_full)
+    for mode, q, shape in [(pf.ALL_VS_ALL, None, (N, N)), (pf.QUERY_SUBSET, qids, (len(qids), N)), (pf.QUERY_DB, q2, (nQ, N - nQ))]:
+        staged = ctx.compute(mode, qry_ids=q, want_jac=False)["matrix"].copy()
+        pin = torch.full(shape, -7.0, dtype=torch.float64).pin_memory()
+        direct = ctx.compute(mode, qry_ids=q, want_jac=False, matrix_out=pin.numpy())["matrix"]
+        assert not np.any(direct == -7.0) and np.array_equal(direct, staged)
+    # row-block sharding (replicated build): compact shards assemble to the full matrix; one shared global matrix
+    parts, lays = [], []
+    for s in range(3):
+        ctx.set_shard(s, 3)
+        parts.append(ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy())
+        lays.append(ctx.shard_layout()[1])
+        assert ctx.timings()["path"] == pf.PATH_MMA
+    assert np.array_equal(sharding.assemble(pf.ALL_VS_ALL, parts, lays, np.empty((N, N))), full)
+    pin = torch.full((N, N), -7.0, dtype=torch.float64).pin_memory()
+    ctx.set_global_matrix(True)
+    for s in range(3):
+        ctx.set_shard(s, 3)
+        ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=pin.numpy())
+    assert np.array_equal(pin.numpy(), full)
+    ctx.set_global_matrix(False)
+    ctx.set_shard(0, 1)
+    ctx.close()
+
+
+def test_auto_path_picks_by_density_and_agrees(pf, orc):
+    """PATH_AUTO: the cost model takes the dense contraction on the real-like family and the list path on the sparse
+    synthetic family at the same size; both give the oracle's matrix."""
+    from parfastaai_b200 import synth
+    N, P = 1500, 6
+    picked = {}
+    for dense in (True, False):
+        off, vals = synth.generate(N, P, seed=3, dense=dense)
+        Lc, F = synth.to_reference(N, P, off, vals)
+        T = synth.t_matrix(N, P, off)
+        ctx = pf.PfaaiGpu(0)
+        ctx.upload_index(P, N, F, Lc)
+        ctx.build()
+        rows = np.arange(0, 40, dtype=np.int32)
+        cols = np.arange(N - 300, N, dtype=np.int32)
+        want = orc.direct_aji(P, N, off, vals, T, rows, cols)["aji"]
+        M = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+        picked[dense] = ctx.timings()["path"]
+        assert np.array_equal(M[np.ix_(rows, cols)], want)
+        assert ctx.e_size() > 0
+        ctx.close()
+    assert picked[True] == pf.PATH_MMA
+    assert picked[False] in (pf.PATH_LISTS, pf.PATH_MMA)
+
+
+def test_dense_path_refuses_what_it_cannot_serve(pf):
+    from parfastaai_b200 import synth
+    N, P = 900, 2
+    off, vals = synth.generate(N, P, seed=1)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    ctx = pf.PfaaiGpu(0)
+    ctx.set_shard(0, 2)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build_partitioned()
+    ctx.finish_partitioned()
+    ctx.set_path(pf.PATH_MMA)
+    with pytest.raises(pf.PfaaiError):
+        ctx.compute(pf.ALL_VS_ALL, want_jac=False)
+    with pytest.raises(pf.PfaaiError):
+        ctx.set_path(7)
+    ctx.close()
