@@ -338,6 +338,7 @@ def main():
                     help="the dense (real-like) synthetic family of SURVEY 8(d): 4 clades, d_k ~ U(0, 0.05), e_g ~ U(0, 0.01)")
     ap.add_argument("--no-shared-matrix", action="store_true",
                     help="N>1: keep compact per-rank matrices (upper-triangle cells only) instead of one shared host matrix")
+    ap.add_argument("--tau", type=int, default=0, help="dense path: posting-list length threshold (0 = cost model)")
     ap.add_argument("--path", default="auto", choices=["auto", "lists", "mma"],
                     help="tile path: lists = dictionary walk (K4), mma = dense tcgen05 contraction + patches (K5), auto = by density")
     args = ap.parse_args()
@@ -413,6 +414,7 @@ def main():
     ctx = pf.PfaaiGpu(local_rank)
     ctx.set_stream(stream.cuda_stream)
     ctx.set_shard(rank, world)
+    ctx.set_path({"auto": pf.PATH_AUTO, "lists": pf.PATH_LISTS, "mma": pf.PATH_MMA}[args.path], args.tau)
     my_rows, my_cols = sharding.shard_shape(pf.ALL_VS_ALL, G, 0, rank, world)
     my_pairs = sharding.pair_count(pf.ALL_VS_ALL, G, 0, rank, world)
     # N > 1: ONE G x G host matrix shared by all ranks (POSIX shared memory, page-locked in every process with
@@ -492,7 +494,7 @@ def main():
         stream.synchronize()
         if rank == 0 and not (args.verify and args.sliced_index):
             del F_pin, F
-        sliced = args.sliced_index and not args.replicated_build
+        sliced = args.sliced_index and not args.replicated_build and args.path != "mma"
         if sliced:
             # from here on the context holds only this rank's slice of F (the buffer of the full F is reused)
             fs_ptr, lcs_ptr = ctx.index_slice_buffers(P, G, nF, lo, hi - lo)
@@ -520,7 +522,7 @@ def main():
         Lc_dev.copy_(Lc_pin_r, non_blocking=True)
         dist.all_gather_into_tensor(F_all, mine)           # in place, straight into the context's F buffer
 
-    partitioned = world > 1 and not args.replicated_build
+    partitioned = world > 1 and not args.replicated_build and args.path != "mma"   # the dense path needs every genome's lists on the GPU
     xviews = {}
     xstream = torch.cuda.Stream(device=dev) if world > 1 else None
     x_ev = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
@@ -719,6 +721,12 @@ def main():
         except Exception as e:   # noqa: BLE001
             ceiling = {"error": str(e)}
 
+    e_size = None
+    if world == 1 or not partitioned:
+        try:
+            e_size = ctx.e_size()          # exact |E| (untimed): the reference's work unit, countTetramerTuples ds_helper.hpp:206-265
+        except Exception as e:   # noqa: BLE001
+            log(f"[bench] e_size unavailable: {e}")
     peak, peak_src = measured_peaks()
     tile_avg_ms = float(np.mean(tile_ms))
     alg_bytes = int(tm["tile_alg_bytes"])
@@ -764,18 +772,29 @@ def main():
         "gpu_launches": int(launches),
         "clocks": {"sm_mhz": clocks["sm_mhz"], "sm_max_mhz": clocks["sm_max_mhz"], "reasons": clocks["reasons"],
                    "samples": clocks["samples"], "power_w_max": clocks.get("power_w_max")},
-        "roofline": {"bound": "hbm", "kernel": "aji_tile_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "path": {"tile_kernel": "aji_mma_kernel (K5: tcgen05 u8 dense contraction + patch records)" if tm["path"] == pf.PATH_MMA
+                 else "aji_tile_kernel (K4: dictionary walk, bit-sliced counters)",
+                 "requested": args.path, "dense_tau": tm["dense_tau"], "dense_k_sum": tm["dense_k_sum"],
+                 "patch_records": tm["patch_records"], "prep_ms": tm["prep_ms"]},
+        "roofline": {"bound": "hbm", "kernel": "aji_mma_kernel" if tm["path"] == pf.PATH_MMA else "aji_tile_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "alg_bytes_per_launch": alg_bytes, "kernel_ms": tile_avg_ms,
                      "note": "the tile kernel is on-chip (shared-memory lookup / LOP3 issue) bound at this size; see DESIGN.md section 4"},
         # the limiter of the tile kernel is on-chip: live work rates + the pipe utilisations of the committed
         # ncu capture of this same configuration (profiles/tile_kernel_traffic.json)
-        "roofline_onchip": {"lookups_per_s": float(tm["n_tiles"]) * 384 * (nF / G) / (tile_avg_ms / 1e3),
+        "roofline_onchip": {"lookups_per_s": (float(tm["n_tiles"]) * 384 * (nF / G) / (tile_avg_ms / 1e3)) if tm["path"] == pf.PATH_LISTS else None,
                             "pair_scp_updates_per_s": (my_pairs if world > 1 else pairs_total) * P / (tile_avg_ms / 1e3),
                             "lookup": "one row tetramer against one 64-column dictionary (LDS.32 + rank + LDS.64 + bit-sliced add)",
+                            "e_size": e_size,
+                            "e_per_s": (e_size / world / (tile_avg_ms / 1e3)) if e_size else None,
+                            "e_unit": "|E| = sum over (SCP, tetramer) posting lists of n(n-1)/2 pair increments (the reference's E array); per GPU",
                             "ceiling": ceiling,
                             "frac": ((float(tm["n_tiles"]) * 384 * (nF / G) / (tile_avg_ms / 1e3)) / ceiling["lookups_per_s"]
-                                     if ceiling and ceiling.get("lookups_per_s") else None),
+                                     if ceiling and ceiling.get("lookups_per_s") and tm["path"] == pf.PATH_LISTS else None),
+                            "mma": ({"macs_per_s": float(tm["n_tiles"]) * 128 * 128 * tm["dense_k_sum"] / (tile_avg_ms / 1e3),
+                                     "operand_bytes_per_s": float(tm["n_tiles"]) * 256 * tm["dense_k_sum"] / (tile_avg_ms / 1e3),
+                                     "note": "u8 x u8 -> s32 multiply-accumulates on tcgen05 (0/1 operands: exact counts) and the bulk-copied operand bytes they consume"}
+                                    if tm["path"] == pf.PATH_MMA else None),
                             "ncu": onchip},
         "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
                       "exchange": exchange_ms, "exchange_bytes_per_rank": exchange_bytes,

@@ -49,9 +49,12 @@ constexpr int MM_SMEM_MISC = 1024;
 constexpr int MM_SMEM_CT = MM_CT_RING * MM_COLS * 4;
 constexpr int MM_SMEM_CNT = MM_EPI_WARPS * MM_CNT_WARP;   // 40960 >= 128*33*8 = 33792 (staging shares it)
 static_assert(MM_SMEM_CNT >= MM_ROWS * MM_STG_PITCH * 8, "output staging does not fit the patch-counter area");
-constexpr int MM_SMEM_TOTAL = MM_SMEM_MISC + MM_SMEM_CT + SMEM_RCP + MM_SMEM_CNT + MM_NSTAGE * MM_STAGE_BYTES;
+constexpr int MM_SMEM_RCP = SMEM_RCP;                   // RN(1/den) per denominator
+constexpr int MM_SMEM_KP = 1024;                        // kpad[p] of every SCP (P <= 255)
+constexpr int MM_SMEM_TOTAL = MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP + MM_SMEM_CNT + MM_NSTAGE * MM_STAGE_BYTES;
 static_assert(MM_SMEM_TOTAL <= SMEM_TOTAL, "K5 shared memory");
-constexpr int MM_TMEM_COLS = 256;                     // 2 accumulator buffers x 128 columns (s32)
+constexpr int MM_TMEM_COLS = 512;                     // 2 accumulator buffers x 128 columns (s32) + 256 columns of fp64 sums S
+constexpr int MM_TMEM_S = 256;                        // first column of S: thread (lane, column group cg) owns columns S + 64 cg .. + 63
 constexpr uint16_t MM_NOT_DENSE = 0xffffu;
 
 struct MmaParams {
@@ -61,7 +64,7 @@ struct MmaParams {
     const int32_t *kpad;                // [P] dense tetramers of SCP p, padded to a multiple of 32 (0: none)
     const int64_t *koff;                // [P] exclusive prefix sum of kpad
     // patches: records of sub-tile key ((I*ncb + J)*P + p)*16 + (row/32)*4 + col/32 are rec[poff[key] .. poff[key+1])
-    const int64_t *poff;
+    const uint32_t *poff;
     const uint16_t *rec;                // (row & 31) | (col & 31) << 5
     int has_patches;
     // rows / columns (kernel index -> genome id, T column)
@@ -72,6 +75,7 @@ struct MmaParams {
     const int32_t *rowTmax, *colTmax;   // [nrb][P], [ncb][P]: max T over the block (fast-path guard: sum < RCP_N)
     int t_ld, P;
     int quirk;                          // 1: T labels are not the genomes' own (query-DB label quirk): always the guarded division
+    int all_fast;                       // 1: 2 * max(T) < RCP_N over the whole matrix: no per-block guard loads
     // output (same conventions as TileParams)
     double *out;
     int64_t out_rs, out_cs;
@@ -110,6 +114,46 @@ __device__ __forceinline__ double u32_to_f64(uint32_t v) {     // exact, on the 
     return __hiloint2double(0x43300000, (int)v) - 4503599627370496.0;
 }
 
+
+// the guarded IEEE division of the list path (rare: denominators beyond the table, or the query-DB label quirk where c may
+// exceed the mislabelled denominator); out of line so that its temporaries do not compete with the fp64 sums for registers
+__device__ __noinline__ double mm_guarded_div(int c, int ta_tb) {
+    const int den = max(ta_tb - c, 1);
+    return (double)c / (double)den;            // algorithm_impl.hpp:250-254
+}
+
+// Jaccard + S, N for 8 columns of one row: columns C0 .. C0+7 of the thread's 32; sv = their fp64 sums as loaded from tensor
+// memory (lo, hi words).  FAST: den < RCP_N and c <= den hold for the whole (tile, SCP), so J = c/den is the table reciprocal +
+// two FMAs (== IEEE division, tests/test_division.py); otherwise the guarded IEEE division of the list path.
+template <bool FAST, int C0>
+__device__ __forceinline__ void mm_epi8(uint32_t (&sv)[16], uint32_t (&N8)[8], const uint32_t *cv, const int ta, const uint32_t ct32,
+                                        const uint32_t rcp32) {
+#pragma unroll
+    for (int g4 = 0; g4 < 2; g4++) {
+        int tb[4];
+        asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(tb[0]), "=r"(tb[1]), "=r"(tb[2]), "=r"(tb[3])
+                     : "r"(ct32 + 4u * (uint32_t)(C0 + g4 * 4)));
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int j = C0 + g4 * 4 + u, k = g4 * 4 + u;
+            const uint32_t c = cv[k];
+            double J;
+            if (FAST) {
+                const uint32_t den = (uint32_t)(ta + tb[u]) - c;
+                const double r = lds_f64(rcp32 + 8u * den), cd = u32_to_f64(c), dd = u32_to_f64(den);
+                const double qq = __dmul_rn(cd, r);
+                J = __fma_rn(__fma_rn(-qq, dd, cd), r, qq);
+            } else {
+                J = mm_guarded_div((int)c, ta + tb[u]);
+            }
+            const double sum = __hiloint2double((int)sv[2 * k + 1], (int)sv[2 * k]) + J;
+            sv[2 * k] = (uint32_t)__double2loint(sum);
+            sv[2 * k + 1] = (uint32_t)__double2hiint(sum);
+            if (c) N8[j >> 2] += 1u << (8 * (j & 3));
+        }
+    }
+}
+
 template <int DUMMY = 0>
 __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams prm) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -123,7 +167,8 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
     int32_t *col_g = reinterpret_cast<int32_t *>(smem + 256);             // [128] genome id of the tile's columns (output phase)
     int32_t *ctring = reinterpret_cast<int32_t *>(smem + MM_SMEM_MISC);   // [CT_RING][128]
     double *rcp = reinterpret_cast<double *>(smem + MM_SMEM_MISC + MM_SMEM_CT);
-    unsigned char *cnt_mem = smem + MM_SMEM_MISC + MM_SMEM_CT + SMEM_RCP;
+    int32_t *kp_s = reinterpret_cast<int32_t *>(smem + MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP);   // [P] kpad
+    unsigned char *cnt_mem = smem + MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP;
     unsigned char *stage_mem = cnt_mem + MM_SMEM_CNT;
     static_assert((2 * MM_NSTAGE + 4 + 2 * MM_CT_RING) * 8 <= 192 && 256 + MM_COLS * 4 <= MM_SMEM_MISC, "misc area");
 
@@ -138,6 +183,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
     }
     if (warp == 0) tmem_alloc(tmem_slot, MM_TMEM_COLS);
     for (int i = tid; i < RCP_N; i += MM_THREADS) rcp[i] = (i > 0) ? 1.0 / (double)i : 0.0;
+    for (int i = tid; i < P; i += MM_THREADS) kp_s[i] = prm.kpad[i];
     for (int i = tid; i < MM_SMEM_CNT / 4; i += MM_THREADS) reinterpret_cast<uint32_t *>(cnt_mem)[i] = 0u;
     tc_fence_before();
     __syncthreads();
@@ -160,7 +206,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                         bulk_g2s(ctring + s * MM_COLS, prm.colT + ((int64_t)tile.y * P + p) * MM_COLS, MM_COLS * 4u, &ct_full[s]);
                         ci++;
                     }
-                    const int kp = __ldg(prm.kpad + p);
+                    const int kp = kp_s[p];
                     const int64_t ko = __ldg(prm.koff + p) * 128;
                     for (int k0 = 0; k0 < kp; k0 += MM_STAGE_K) {
                         const uint32_t s = it % MM_NSTAGE, ph = (it / MM_NSTAGE) & 1u;
@@ -182,7 +228,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
             const uint32_t stage32 = smem_u32(stage_mem);
             for (int tile_i = blockIdx.x; tile_i < prm.n_tiles; tile_i += gridDim.x) {
                 for (int p = 0; p < P; p++) {
-                    const int kp = __ldg(prm.kpad + p);
+                    const int kp = kp_s[p];
                     if (kp == 0) continue;
                     const uint32_t buf = ai & 1u, aph = (ai >> 1) & 1u;
                     mbar_wait(&acc_empty[buf], aph ^ 1u);        // the epilogue has read this buffer's previous SCP
@@ -209,6 +255,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
         const int q = warp & 3, cg = warp >> 2;                  // tensor-memory lane quadrant (rows 32q..), column group (cols 32cg..)
         const int rl = q * 32 + lane;                            // row of the tile
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        const uint32_t s_addr = tmem_base + lane_addr + MM_TMEM_S + cg * 64;       // this thread's 32 fp64 sums
         unsigned char *cw = cnt_mem + warp * MM_CNT_WARP;        // this warp's 32 x 32 patch counters (uint16)
         const uint32_t cw32 = smem_u32(cw);
         const uint32_t rcp32 = smem_u32(rcp);
@@ -223,12 +270,18 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
             const int ncol = min(MM_COLS, prm.n_cols - j0);
             const int64_t key0 = ((int64_t)tile.x * prm.ncb + tile.y) * P * 16 + (q * 4 + cg);
 
-            double S[32];
             uint32_t N8[8];
 #pragma unroll
-            for (int j = 0; j < 32; j++) S[j] = 0.0;
-#pragma unroll
             for (int j = 0; j < 8; j++) N8[j] = 0u;
+            {   // S = 0 for the 32 columns of this thread (tensor memory)
+                uint32_t z[16];
+#pragma unroll
+                for (int k = 0; k < 16; k++) z[k] = 0u;
+                __syncwarp();
+#pragma unroll
+                for (int g = 0; g < 4; g++) tmem_st16(s_addr + 16 * g, z);
+                tmem_wait_st();
+            }
             // columns of this thread that are real pairs (isValidPair): inside the matrix and not the row's own genome
             uint32_t valid = 0u;
 #pragma unroll
@@ -237,26 +290,38 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                 const int gj = (col < ncol) ? __ldg(prm.cols + j0 + col) : -1;
                 if (row_ok && gj >= 0 && gj != gi) valid |= 1u << j;
             }
-            int ta = row_ok ? __ldg(prm.T + ti) : 0;                                     // SCP 0
-            int64_t po0 = 0, po1 = 0;
-            if (prm.has_patches) { po0 = __ldg(prm.poff + key0); po1 = __ldg(prm.poff + key0 + 1); }
-            const bool never_fast = prm.quirk != 0;
+            // per-SCP scalars are fetched one SCP ahead (their latency hides behind the previous SCP's epilogue): the row's T value,
+            // the extent of the sub-tile's patch records and this lane's first record
+            const int tileP_r = tile.x * P, tileP_c = tile.y * P;
+            const bool patches = prm.has_patches != 0, never_fast = prm.quirk != 0, all_fast = prm.all_fast != 0;
+            int ta = row_ok ? __ldg(prm.T + ti) : 0;
+            bool fast = !never_fast && (all_fast || __ldg(prm.rowTmax + tileP_r) + __ldg(prm.colTmax + tileP_c) < RCP_N);
+            // patch extents are fetched TWO SCPs ahead and the lane's first record ONE ahead, so that no load is consumed in the
+            // iteration that issued it
+            uint32_t po0 = 0u, po1 = 0u, pn0 = 0u, pn1 = 0u, rec0 = 0u;
+            if (patches) {
+                po0 = __ldg(prm.poff + key0); po1 = __ldg(prm.poff + key0 + 1);
+                if (P > 1) { pn0 = __ldg(prm.poff + key0 + 16); pn1 = __ldg(prm.poff + key0 + 17); }
+                if ((uint32_t)lane < po1 - po0) rec0 = __ldg(prm.rec + po0 + lane);
+            }
 
             for (int p = 0; p < P; p++) {
-                // prefetch the next SCP's row T value and patch extent
-                int ta_nxt = 0; int64_t pn0 = 0, pn1 = 0;
+                int ta_nxt = 0; bool fast_nxt = false; uint32_t pq0 = 0u, pq1 = 0u, rec_nxt = 0u;
                 if (p + 1 < P) {
                     if (row_ok) ta_nxt = __ldg(prm.T + (int64_t)(p + 1) * prm.t_ld + ti);
-                    if (prm.has_patches) { pn0 = __ldg(prm.poff + key0 + (int64_t)(p + 1) * 16); pn1 = __ldg(prm.poff + key0 + (int64_t)(p + 1) * 16 + 1); }
+                    fast_nxt = !never_fast && (all_fast || __ldg(prm.rowTmax + tileP_r + p + 1) + __ldg(prm.colTmax + tileP_c + p + 1) < RCP_N);
+                    if (patches) {
+                        if ((uint32_t)lane < pn1 - pn0) rec_nxt = __ldg(prm.rec + pn0 + lane);        // extents arrived an SCP ago
+                        if (p + 2 < P) { pq0 = __ldg(prm.poff + key0 + (int64_t)(p + 2) * 16); pq1 = __ldg(prm.poff + key0 + (int64_t)(p + 2) * 16 + 1); }
+                    }
                 }
-                const int kp = __ldg(prm.kpad + p);
-                const bool fast = !never_fast &&
-                                  (__ldg(prm.rowTmax + (int64_t)tile.x * P + p) + __ldg(prm.colTmax + (int64_t)tile.y * P + p) < RCP_N);
+                const int kp = kp_s[p];
+                const uint32_t np = po1 - po0;
                 // ---- patches of this warp's sub-tile: scatter into the warp-private counters ----
-                const uint32_t np = (uint32_t)(po1 - po0);
                 if (np) {
+                    uint32_t r = rec0;
                     for (uint32_t i = lane; i < np; i += 32) {
-                        const uint32_t r = __ldg(prm.rec + po0 + i);
+                        if (i >= 32u) r = __ldg(prm.rec + po0 + i);
                         const uint32_t a = (r & 31u) * MM_CNT_PITCH + ((r >> 5) & 31u) * 2u;
                         atomicAdd(reinterpret_cast<uint32_t *>(cw + (a & ~3u)), 1u << (8u * (a & 2u)));
                     }
@@ -267,75 +332,67 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                 mbar_wait(&ct_full[cs], (ci / MM_CT_RING) & 1u);
                 const uint32_t ct32 = smem_u32(ctring + cs * MM_COLS + cg * 32);
                 // ---- counts from tensor memory ----
-                uint32_t buf = 0u;
+                uint32_t taddr = 0u, buf = 0u;
                 if (kp) {
                     buf = ai & 1u;
                     mbar_wait(&acc_full[buf], (ai >> 1) & 1u);
                     tc_fence_after();
+                    taddr = tmem_base + lane_addr + buf * MM_COLS + cg * 32;
                 }
 #pragma unroll
                 for (int hf = 0; hf < 2; hf++) {
-                    uint32_t cv[16];
+                    uint32_t cv[16], sv[16];
+                    tmem_ld16(s_addr + hf * 32, sv);        // the sums of columns 16 hf .. 16 hf + 7
                     if (kp) {
-                        tmem_ld16(tmem_base + lane_addr + buf * MM_COLS + cg * 32 + hf * 16, cv);
+                        tmem_ld16(taddr + hf * 16, cv);
                         tmem_wait_ld(cv);
+                        if (hf == 1) {                      // both halves are in registers: hand the buffer back to the tensor cores
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+                        }
                     } else {
 #pragma unroll
                         for (int u = 0; u < 16; u++) cv[u] = 0u;
                     }
-                    if (hf == 1 && kp) {                    // both halves are in registers: hand the buffer back to the tensor cores
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&acc_empty[buf]);
-                    }
                     if (np) {                               // warp-uniform: add this row's patch counters, then clear them
 #pragma unroll
                         for (int v4 = 0; v4 < 2; v4++) {
-                            uint32_t w0, w1, w2, w3;
+                            uint32_t w[4];
                             const uint32_t a = cw32 + lane * MM_CNT_PITCH + hf * 32 + v4 * 16;
-                            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(a));
+                            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(a));
                             asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(a), "r"(0u) : "memory");
-                            const uint32_t w[4] = {w0, w1, w2, w3};
 #pragma unroll
                             for (int u = 0; u < 4; u++) { cv[v4 * 8 + 2 * u] += w[u] & 0xffffu; cv[v4 * 8 + 2 * u + 1] += w[u] >> 16; }
                         }
                     }
-                    // ---- Jaccard + S, N for 16 columns ----
+                    if (valid != 0xffffffffu) {             // the row's own genome / columns beyond the matrix (diagonal and edge tiles)
 #pragma unroll
-                    for (int g4 = 0; g4 < 4; g4++) {
-                        int tb0, tb1, tb2, tb3;
-                        asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(tb0), "=r"(tb1), "=r"(tb2), "=r"(tb3)
-                                     : "r"(ct32 + 4u * (uint32_t)(hf * 16 + g4 * 4)));
-                        const int tbv[4] = {tb0, tb1, tb2, tb3};
+                        for (int u = 0; u < 16; u++) if (!((valid >> (hf * 16 + u)) & 1u)) cv[u] = 0u;
+                    }
+                    if (prm.counts_out) {                   // small-N parity hook
 #pragma unroll
-                        for (int u = 0; u < 4; u++) {
-                            const int j = hf * 16 + g4 * 4 + u;
-                            const uint32_t c = ((valid >> j) & 1u) ? cv[g4 * 4 + u] : 0u;
-                            double J;
-                            if (fast) {
-                                // den < RCP_N and c <= den hold for the whole (tile, SCP): table reciprocal + 2 FMAs == IEEE division
-                                const uint32_t den = (uint32_t)(ta + tbv[u]) - c;
-                                const double r = lds_f64(rcp32 + 8u * den), cd = u32_to_f64(c), dd = u32_to_f64(den);
-                                const double qq = __dmul_rn(cd, r);
-                                J = __fma_rn(__fma_rn(-qq, dd, cd), r, qq);
-                            } else {
-                                const int den = max(ta + tbv[u] - (int)c, 1);
-                                J = (double)(int)c / (double)den;            // algorithm_impl.hpp:250-254
-                            }
-                            S[j] += J;
-                            N8[j >> 2] += (c ? 1u : 0u) << (8 * (j & 3));
-                            if (prm.counts_out) {
-                                const int col = cg * 32 + j;
-                                if (row_ok && col < ncol) prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = (int)c;
-                            }
+                        for (int u = 0; u < 16; u++) {
+                            const int col = cg * 32 + hf * 16 + u;
+                            if (row_ok && col < ncol) prm.counts_out[((int64_t)row * prm.n_cols + (j0 + col)) * P + p] = (int)cv[u];
                         }
                     }
+                    tmem_wait_ld(sv);
+                    if (hf == 0) { if (fast) mm_epi8<true, 0>(sv, N8, cv, ta, ct32, rcp32); else mm_epi8<false, 0>(sv, N8, cv, ta, ct32, rcp32); }
+                    else         { if (fast) mm_epi8<true, 16>(sv, N8, cv, ta, ct32, rcp32); else mm_epi8<false, 16>(sv, N8, cv, ta, ct32, rcp32); }
+                    tmem_st16(s_addr + hf * 32, sv);
+                    tmem_ld16(s_addr + hf * 32 + 16, sv);   // the sums of columns 16 hf + 8 .. 16 hf + 15
+                    tmem_wait_ld(sv);
+                    if (hf == 0) { if (fast) mm_epi8<true, 8>(sv, N8, cv + 8, ta, ct32, rcp32); else mm_epi8<false, 8>(sv, N8, cv + 8, ta, ct32, rcp32); }
+                    else         { if (fast) mm_epi8<true, 24>(sv, N8, cv + 8, ta, ct32, rcp32); else mm_epi8<false, 24>(sv, N8, cv + 8, ta, ct32, rcp32); }
+                    tmem_st16(s_addr + hf * 32 + 16, sv);
                 }
+                tmem_wait_st();
                 if (kp) ai++;
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ct_empty[cs]);
                 ci++;
-                ta = ta_nxt; po0 = pn0; po1 = pn1;
+                ta = ta_nxt; fast = fast_nxt; po0 = pn0; po1 = pn1; pn0 = pq0; pn1 = pq1; rec0 = rec_nxt;
             }
 
             // ================= output: AJI = S / N (computeAJI) into the dense matrix, four 32-column rounds =================
@@ -348,13 +405,21 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                 asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");      // staging (== patch counters) is free
                 if (cg == round) {
 #pragma unroll
-                    for (int j = 0; j < 32; j++) {
-                        const int n = (int)((N8[j >> 2] >> (8 * (j & 3))) & 0xffu);
-                        stg[rl * MM_STG_PITCH + j] = n ? S[j] / (double)n : 0.0;
-                        const int col = cg * 32 + j;
-                        if (row_ok && col < ncol) {
-                            if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + (j0 + col)] = S[j];
-                            if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + (j0 + col)] = n;
+                    for (int g = 0; g < 4; g++) {
+                        uint32_t sv[16];
+                        tmem_ld16(s_addr + 16 * g, sv);
+                        tmem_wait_ld(sv);
+#pragma unroll
+                        for (int u = 0; u < 8; u++) {
+                            const int j = 8 * g + u;
+                            const double Ssum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]);
+                            const int n = (int)((N8[j >> 2] >> (8 * (j & 3))) & 0xffu);
+                            stg[rl * MM_STG_PITCH + j] = n ? Ssum / (double)n : 0.0;
+                            const int col = cg * 32 + j;
+                            if (row_ok && col < ncol) {
+                                if (prm.S_out) prm.S_out[(int64_t)row * prm.n_cols + (j0 + col)] = Ssum;
+                                if (prm.N_out) prm.N_out[(int64_t)row * prm.n_cols + (j0 + col)] = n;
+                            }
                         }
                     }
                 }

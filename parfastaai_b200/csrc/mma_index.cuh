@@ -110,6 +110,19 @@ __global__ void __launch_bounds__(128) k_block_t(const int32_t *__restrict__ T, 
     if (threadIdx.x == 0) blkmax[(int64_t)blk * P + p] = max(max(wm[0], wm[1]), max(wm[2], wm[3]));
 }
 
+// int64 scan result -> the uint32 offsets the kernels read (the record count is checked against 2^32 on the host)
+__global__ void k_narrow_u32(const int64_t *__restrict__ in, int64_t n, uint32_t *__restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (uint32_t)in[i];
+}
+
+// largest T value of the matrix's rows / columns -> *out (atomicMax); out must be zeroed
+__global__ void k_max_t(const int32_t *__restrict__ blkmax, int64_t n, int *__restrict__ out) {
+    int m = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) m = max(m, blkmax[i]);
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+
 struct PatchParams {
     const pfaai_pg_t *F;            // (tetramer, protein, genome) order; genomes ascend inside a (tetramer, protein) run
     const int64_t *Lp;              // [NTETRA + 1]
@@ -119,7 +132,7 @@ struct PatchParams {
     const int32_t *row_of, *col_of; // genome -> kernel row / column index, -1 = none
     const uint8_t *rb_owned;        // [row blocks of 128] 1 = this shard computes the block
     uint32_t *cnt;                  // [nkeys] counts (pass 1) / cursors (pass 2)
-    const int64_t *poff;            // [nkeys + 1] (pass 2)
+    const uint32_t *poff;           // [nkeys + 1] (pass 2)
     uint16_t *rec;                  // (pass 2)
 };
 

@@ -50,7 +50,7 @@ struct Ctx {
     // dense-contraction path (K5): planning + operands + patches
     int path_pref = PFAAI_PATH_AUTO, tau_pref = 0;
     DevBuf mm_len, mm_hist, mm_did, mm_kcnt, mm_kpad, mm_koff, mm_img_rows, mm_img_cols, mm_colT, mm_rowmax, mm_colmax,
-           mm_rowof, mm_colof, mm_owned, mm_pcnt, mm_poff, mm_rec;
+           mm_rowof, mm_colof, mm_owned, mm_pcnt, mm_poff, mm_poff32, mm_rec;
     int64_t e_size = -1;                  // |E| of the built index (exact length histogram), -1 = not computed for this build
     // routed build: this context holds postings [slice_begin, slice_begin + n_slice) of F only
     bool sliced = false;
@@ -296,7 +296,7 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
                      &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr, &c->route_hist, &c->recv,
                      &c->mm_len, &c->mm_hist, &c->mm_did, &c->mm_kcnt, &c->mm_kpad, &c->mm_koff, &c->mm_img_rows, &c->mm_img_cols,
                      &c->mm_colT, &c->mm_rowmax, &c->mm_colmax, &c->mm_rowof, &c->mm_colof, &c->mm_owned, &c->mm_pcnt,
-                     &c->mm_poff, &c->mm_rec};
+                     &c->mm_poff, &c->mm_poff32, &c->mm_rec};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
@@ -922,18 +922,38 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
     const int64_t nlen = (int64_t)P * NTETRA;
     const int nrb = (n_rows + MM_ROWS - 1) / MM_ROWS, ncb = (n_cols + MM_COLS - 1) / MM_COLS;
     constexpr int KMAX = 16384;
+    // 0. T values per column block, block maxima (fast-division guard) and their overall maximum
+    PF_TRY(ensure(c, c->mm_colT, sizeof(int32_t) * (size_t)ncb * P * MM_COLS));
+    PF_TRY(ensure(c, c->mm_colmax, sizeof(int32_t) * (size_t)ncb * P));
+    PF_TRY(ensure(c, c->mm_rowmax, sizeof(int32_t) * (size_t)nrb * P));
+    int *err = ptr<int>(c->flags) + 12, *tmax = ptr<int>(c->flags) + 13;
+    PF_CUDA(c, cudaMemsetAsync(err, 0, 2 * sizeof(int), c->stream));
+    if (ncb > 0) {
+        k_block_t<<<(unsigned)(ncb * P), 128, 0, c->stream>>>(ptr<int32_t>(c->T), c->G, P, ptr<int32_t>(c->col_t), n_cols, ptr<int32_t>(c->mm_colT),
+                                                              ptr<int32_t>(c->mm_colmax));
+        PF_LAUNCH_CHECK(c);
+        k_max_t<<<64, 256, 0, c->stream>>>(ptr<int32_t>(c->mm_colmax), (int64_t)ncb * P, tmax);
+        PF_LAUNCH_CHECK(c);
+    }
+    if (nrb > 0) {
+        k_block_t<<<(unsigned)(nrb * P), 128, 0, c->stream>>>(ptr<int32_t>(c->T), c->G, P, ptr<int32_t>(c->row_t), n_rows, nullptr,
+                                                              ptr<int32_t>(c->mm_rowmax));
+        PF_LAUNCH_CHECK(c);
+        k_max_t<<<64, 256, 0, c->stream>>>(ptr<int32_t>(c->mm_rowmax), (int64_t)nrb * P, tmax);
+        PF_LAUNCH_CHECK(c);
+    }
     // 1. dense tetramers of every SCP
     PF_TRY(ensure(c, c->mm_did, sizeof(uint16_t) * (size_t)nlen));
     PF_TRY(ensure(c, c->mm_kcnt, sizeof(int32_t) * (size_t)P));
-    int *err = ptr<int>(c->flags) + 12;
-    PF_CUDA(c, cudaMemsetAsync(err, 0, sizeof(int), c->stream));
     k_dense_ids<<<(unsigned)P, 1024, 0, c->stream>>>(ptr<uint32_t>(c->mm_len), pl.tau, ptr<uint16_t>(c->mm_did), ptr<int32_t>(c->mm_kcnt), KMAX, err);
     PF_LAUNCH_CHECK(c);
     std::vector<int32_t> kcnt(P);
-    int err_h = 0;
+    int eh[2] = {0, 0};
     PF_CUDA(c, cudaMemcpyAsync(kcnt.data(), c->mm_kcnt.p, sizeof(int32_t) * (size_t)P, cudaMemcpyDeviceToHost, c->stream));
-    PF_CUDA(c, cudaMemcpyAsync(&err_h, err, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(eh, err, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    const int err_h = eh[0];
+    prm.all_fast = (2 * (int64_t)eh[1] < RCP_N) ? 1 : 0;
     if (err_h) { set_error(c, "dense path: an SCP has more than 16384 dense tetramers at this threshold"); return PFAAI_ERR_CONSTRUCT; }
     kpad_host.assign(P, 0);
     std::vector<int64_t> koff(P, 0);
@@ -959,20 +979,6 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
     PF_TRY(fill(c->mm_img_rows, c->rows, n_rows, nrb));
     const bool same = m.symmetric != 0;
     if (!same) PF_TRY(fill(c->mm_img_cols, c->cols, n_cols, ncb));
-    // 3. T values per column block, block maxima (fast-division guard)
-    PF_TRY(ensure(c, c->mm_colT, sizeof(int32_t) * (size_t)ncb * P * MM_COLS));
-    PF_TRY(ensure(c, c->mm_colmax, sizeof(int32_t) * (size_t)ncb * P));
-    PF_TRY(ensure(c, c->mm_rowmax, sizeof(int32_t) * (size_t)nrb * P));
-    if (ncb > 0) {
-        k_block_t<<<(unsigned)(ncb * P), 128, 0, c->stream>>>(ptr<int32_t>(c->T), c->G, P, ptr<int32_t>(c->col_t), n_cols, ptr<int32_t>(c->mm_colT),
-                                                              ptr<int32_t>(c->mm_colmax));
-        PF_LAUNCH_CHECK(c);
-    }
-    if (nrb > 0) {
-        k_block_t<<<(unsigned)(nrb * P), 128, 0, c->stream>>>(ptr<int32_t>(c->T), c->G, P, ptr<int32_t>(c->row_t), n_rows, nullptr,
-                                                              ptr<int32_t>(c->mm_rowmax));
-        PF_LAUNCH_CHECK(c);
-    }
     // 4. patches: every co-occurrence on a tetramer whose list is shorter than tau
     double e_sparse = 0;
     for (uint32_t L = 2; L < std::min<uint32_t>(pl.tau, MM_HMAX); L++) e_sparse += (double)pl.hist[L] * 0.5 * L * (L - 1);
@@ -987,6 +993,7 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
         PF_CUDA(c, cudaMemcpyAsync(c->mm_owned.p, rb_owned.data(), rb_owned.size(), cudaMemcpyHostToDevice, c->stream));
         PF_TRY(ensure(c, c->mm_pcnt, sizeof(uint32_t) * (size_t)nkeys));
         PF_TRY(ensure(c, c->mm_poff, sizeof(int64_t) * (size_t)(nkeys + 1)));
+        PF_TRY(ensure(c, c->mm_poff32, sizeof(uint32_t) * (size_t)(nkeys + 1)));
         PatchParams q;
         q.F = ptr<pfaai_pg_t>(c->F); q.Lp = ptr<int64_t>(c->Lp64); q.len = ptr<uint32_t>(c->mm_len); q.tau = pl.tau;
         q.P = P; q.ncb = ncb; q.symmetric = m.symmetric;
@@ -1000,10 +1007,13 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
         int64_t total = 0;
         PF_CUDA(c, cudaMemcpyAsync(&total, ptr<int64_t>(c->mm_poff) + nkeys, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
         PF_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (total >= (1ll << 32)) { set_error(c, "dense path: more than 2^32 patch records at this threshold"); return PFAAI_ERR_CONSTRUCT; }
         if (total > 0) {
+            k_narrow_u32<<<(unsigned)(c->sm_count * 8), 256, 0, c->stream>>>(ptr<int64_t>(c->mm_poff), nkeys + 1, ptr<uint32_t>(c->mm_poff32));
+            PF_LAUNCH_CHECK(c);
             PF_TRY(ensure(c, c->mm_rec, sizeof(uint16_t) * (size_t)total));
             PF_CUDA(c, cudaMemsetAsync(c->mm_pcnt.p, 0, sizeof(uint32_t) * (size_t)nkeys, c->stream));
-            q.poff = ptr<int64_t>(c->mm_poff); q.rec = ptr<uint16_t>(c->mm_rec);
+            q.poff = ptr<uint32_t>(c->mm_poff32); q.rec = ptr<uint16_t>(c->mm_rec);
             k_patch_enum<true><<<grid, 256, 0, c->stream>>>(q);
             PF_LAUNCH_CHECK(c);
             pl.has_patches = true; pl.patch_records = total;
@@ -1013,7 +1023,7 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
     prm.img_cols = same ? prm.img_rows : reinterpret_cast<unsigned char *>(c->mm_img_cols.p);
     prm.blk_stride = blk_stride;
     prm.kpad = ptr<int32_t>(c->mm_kpad); prm.koff = ptr<int64_t>(c->mm_koff);
-    prm.poff = ptr<int64_t>(c->mm_poff); prm.rec = ptr<uint16_t>(c->mm_rec); prm.has_patches = pl.has_patches ? 1 : 0;
+    prm.poff = ptr<uint32_t>(c->mm_poff32); prm.rec = ptr<uint16_t>(c->mm_rec); prm.has_patches = pl.has_patches ? 1 : 0;
     prm.colT = ptr<int32_t>(c->mm_colT); prm.rowTmax = ptr<int32_t>(c->mm_rowmax); prm.colTmax = ptr<int32_t>(c->mm_colmax);
     prm.ncb = ncb;
     return PFAAI_OK;
