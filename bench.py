@@ -425,7 +425,7 @@ def main():
     if world > 1 and not args.no_shared_matrix:
         shm_path = "/dev/shm/pfaai_bench_M_%s.bin" % os.environ.get("MASTER_PORT", "0")
         ok = torch.ones(1, dtype=torch.int32, device=dev)
-        need = 8 * G * G
+        need = (8 * G * G + 4095) & ~4095            # whole pages: the mapping is page-locked page by page
         try:
             if rank == 0:
                 st = os.statvfs("/dev/shm")
@@ -438,16 +438,31 @@ def main():
             ok[0] = 0
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if int(ok.item()) == 1:
-            M_sh = torch.from_file(shm_path, shared=True, size=G * G, dtype=torch.float64)
-            rc = int(torch.cuda.cudart().cudaHostRegister(M_sh.data_ptr(), need, 1 | 2))   # portable | mapped
-            ok[0] = 1 if rc == 0 else 0
+            M_sh = torch.from_file(shm_path, shared=True, size=need // 8, dtype=torch.float64)
+            if rank == 0:
+                # fault every page in once, before anybody page-locks the mapping (tools/probe_host_register.py: registering a
+                # never-touched 20 GB shared mapping from two processes at once failed on this box; a populated one does not)
+                M_sh.view(torch.uint8)[::4096] = 0
+            dist.barrier()
+            t_reg = time.perf_counter()
+            ok[0] = 1 if pf.host_register(M_sh.data_ptr(), need) else 0     # 1 GiB pieces; clears the CUDA error on failure
+            mine_ok = int(ok.item())
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
             if int(ok.item()) == 1:
                 shared_matrix = True
-                M = M_sh.numpy().reshape(G, G)     # addressed globally only by the e2e steps (set_global_matrix below)
+                M = M_sh.numpy()[:G * G].reshape(G, G)     # addressed globally only by the e2e steps (set_global_matrix below)
+                log(f"[rank {rank}] shared host matrix: {need/1e9:.1f} GB page-locked in {time.perf_counter()-t_reg:.1f} s")
             else:
-                shm_note = "cudaHostRegister of the shared matrix failed on some rank"
+                shm_note = "page-locking the shared matrix failed on some rank"
+                if mine_ok:
+                    pf.host_unregister(M_sh.data_ptr(), need)
                 del M_sh
+                dist.barrier()
+                if rank == 0:
+                    try:
+                        os.remove(shm_path)
+                    except OSError:
+                        pass
         if not shared_matrix:
             log(f"[rank {rank}] shared host matrix unavailable ({shm_note}); compact per-rank matrices (upper-triangle cells only)")
     if not shared_matrix:
@@ -827,7 +842,7 @@ def main():
     if world > 1:
         dist.barrier()
         if shared_matrix:
-            torch.cuda.cudart().cudaHostUnregister(M_sh.data_ptr())
+            pf.host_unregister(M_sh.data_ptr(), need)
             if rank == 0:
                 try:
                     os.remove(shm_path)

@@ -27,6 +27,7 @@
 #ifndef PFAAI_GPU_H
 #define PFAAI_GPU_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -97,6 +98,13 @@ int  pfaai_gpu_set_shard(pfaai_gpu_ctx *ctx, int shard, int n_shards);
  * complete in host memory: no gather, no host-side mirror pass (src/main.cpp:143-154 done by the kernels' own stores).
  * pfaai_gpu_matrix_shape then reports G x G.  Off (default): compact per-shard matrices as described above. */
 int  pfaai_gpu_set_global_matrix(pfaai_gpu_ctx *ctx, int on);
+/* Page-lock (and map for device access) a host range the caller allocated itself -- e.g. the POSIX shared-memory mapping of
+ * the global matrix above, once in every process that stores into it.  The range is registered in 1 GiB pieces (one
+ * cudaHostRegister call over tens of GB of a not-yet-faulted shared mapping was seen to fail when two processes issue it at
+ * once); on failure everything registered so far is released again, the CUDA error state is cleared and PFAAI_ERR_CONSTRUCT
+ * is returned, so the caller can fall back to compact per-shard matrices.  ptr and bytes must be multiples of the page size. */
+int  pfaai_gpu_host_register(void *ptr, size_t bytes);
+int  pfaai_gpu_host_unregister(void *ptr, size_t bytes);
 /* Which tile kernel the next computes use (BASELINE north_star: "ncu evidence decides between the two paths"):
  *   PFAAI_PATH_AUTO   (default) a cost model on the measured posting-list length distribution picks per compute call;
  *   PFAAI_PATH_LISTS  the dictionary walk (aji_tile_kernel: bit-sliced counters, no tensor cores) -- sparse inputs;

@@ -32,6 +32,7 @@ EXPORTS = [
     "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
     "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
     "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench", "pfaai_gpu_set_path", "pfaai_gpu_e_size",
+    "pfaai_gpu_host_register", "pfaai_gpu_host_unregister",
 ]
 
 
@@ -110,6 +111,8 @@ def load():
     L.pfaai_gpu_route_local.argtypes = [C.POINTER(vp), i32]
     L.pfaai_gpu_set_global_matrix.argtypes = [vp, i32]
     L.pfaai_gpu_set_path.argtypes = [vp, i32, i32]
+    L.pfaai_gpu_host_register.argtypes = [vp, C.c_size_t]
+    L.pfaai_gpu_host_unregister.argtypes = [vp, C.c_size_t]
     L.pfaai_gpu_e_size.argtypes = [vp, C.POINTER(i64)]
     L.pfaai_gpu_microbench.argtypes = [vp, i32, C.c_double, i32, C.POINTER(Microbench)]
     _lib = L
@@ -122,6 +125,15 @@ def _p(a):
 
 class PfaaiError(RuntimeError):
     pass
+
+
+def host_register(ptr: int, nbytes: int) -> bool:
+    """Page-lock + map a caller-allocated host range (pfaai_gpu_host_register); False = the driver refused (no error left behind)."""
+    return load().pfaai_gpu_host_register(C.c_void_p(ptr), nbytes) == 0
+
+
+def host_unregister(ptr: int, nbytes: int) -> bool:
+    return load().pfaai_gpu_host_unregister(C.c_void_p(ptr), nbytes) == 0
 
 
 class PfaaiGpu:

@@ -342,6 +342,28 @@ int pfaai_gpu_set_global_matrix(pfaai_gpu_ctx *h, int on) {
     return PFAAI_OK;
 }
 
+static constexpr size_t HOST_REG_PIECE = (size_t)1 << 30;
+
+int pfaai_gpu_host_unregister(void *ptr, size_t bytes) {
+    int rc = PFAAI_OK;
+    for (size_t o = 0; o < bytes; o += HOST_REG_PIECE)
+        if (cudaHostUnregister(static_cast<char *>(ptr) + o) != cudaSuccess) { cudaGetLastError(); rc = PFAAI_ERR_CONSTRUCT; }
+    return rc;
+}
+
+int pfaai_gpu_host_register(void *ptr, size_t bytes) {
+    if (!ptr || !bytes || (reinterpret_cast<uintptr_t>(ptr) & 4095u) || (bytes & 4095u)) return PFAAI_ERR_CONSTRUCT;
+    for (size_t o = 0; o < bytes; o += HOST_REG_PIECE) {
+        const size_t n = bytes - o < HOST_REG_PIECE ? bytes - o : HOST_REG_PIECE;
+        if (cudaHostRegister(static_cast<char *>(ptr) + o, n, cudaHostRegisterPortable | cudaHostRegisterMapped) != cudaSuccess) {
+            cudaGetLastError();                          // not sticky: leave no error behind for the caller's next CUDA call
+            pfaai_gpu_host_unregister(ptr, o);
+            return PFAAI_ERR_CONSTRUCT;
+        }
+    }
+    return PFAAI_OK;
+}
+
 int pfaai_gpu_upload_index(pfaai_gpu_ctx *h, int P, int G, const pfaai_pg_t *F, const int32_t *Lc, int64_t nF,
                            const int32_t *T) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
