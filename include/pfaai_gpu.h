@@ -43,8 +43,11 @@ typedef struct { int32_t protein, genome; } pfaai_pg_t;
 /* == JACTuple<int,double> fields (interface.hpp:61-75), natural C alignment (24 B) */
 typedef struct { int32_t gA, gB; double S; int32_t N; int32_t pad_; } pfaai_jac_t;
 
-/* == PFAAI_ERROR_CODE (interface.hpp:39-44) */
+/* == PFAAI_ERROR_CODE (interface.hpp:39-44).  A translation unit of the reference itself, which already has that enum with
+ * the same enumerator names, defines PFAAI_GPU_REFERENCE_ERROR_CODES before including this header (tests/binding). */
+#ifndef PFAAI_GPU_REFERENCE_ERROR_CODES
 enum pfaai_status { PFAAI_OK = 0, PFAAI_ERR_SQLITE_DB = 1, PFAAI_ERR_SQLITE_MEM_ALLOC = 2, PFAAI_ERR_CONSTRUCT = 3 };
+#endif
 
 /* the three drivers of src/main.cpp:177,234,302 */
 enum pfaai_mode { PFAAI_ALL_VS_ALL = 0, PFAAI_QUERY_SUBSET = 1, PFAAI_QUERY_DB = 2 };
