@@ -790,7 +790,7 @@ def main():
         "path": {"tile_kernel": "aji_mma_kernel (K5: tcgen05 u8 dense contraction + patch records)" if tm["path"] == pf.PATH_MMA
                  else "aji_tile_kernel (K4: dictionary walk, bit-sliced counters)",
                  "requested": args.path, "dense_tau": tm["dense_tau"], "dense_k_sum": tm["dense_k_sum"],
-                 "patch_records": tm["patch_records"], "prep_ms": tm["prep_ms"]},
+                 "sparse_items": tm["sparse_items"], "prep_ms": tm["prep_ms"]},
         "roofline": {"bound": "hbm", "kernel": "aji_mma_kernel" if tm["path"] == pf.PATH_MMA else "aji_tile_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "alg_bytes_per_launch": alg_bytes, "kernel_ms": tile_avg_ms,

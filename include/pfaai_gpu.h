@@ -72,7 +72,7 @@ typedef struct {
     int32_t path;        /* tile path of the last compute: 1 = lists (aji_tile_kernel), 2 = dense contraction (aji_mma_kernel) */
     int32_t dense_tau;   /* dense path: posting lists at least this long are tensor-core columns                */
     int64_t dense_k_sum; /* dense path: dense tetramers over all SCPs (padded to 32 per SCP)                    */
-    int64_t patch_records; /* dense path: co-occurrences on non-dense tetramers, added as patch records        */
+    int64_t sparse_items; /* dense path: postings on non-dense tetramers (walked in-kernel as sparse row items)  */
     int64_t e_size;      /* |E| = sum over posting lists of n(n-1)/2 (the reference's E array, all-vs-all), when known, else -1 */
     float prep_ms;       /* dense path: list lengths + dense ids + operand images + patches inside compute      */
     int32_t reserved2_;
@@ -134,6 +134,13 @@ int  pfaai_gpu_shard_layout(const pfaai_gpu_ctx *ctx, int *axis, int64_t *n, int
  * n_genomes is the TOTAL number of genome ids (query-DB mode: nT + nQ, targets first). */
 int  pfaai_gpu_upload_index(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes,
                             const pfaai_pg_t *F, const int32_t *Lc, int64_t nF, const int32_t *T);
+/* The same hand-over with the tetramer key of every posting instead of Lc ("tetramer[nF]"): the triples
+ * (tetramer, protein, genome) as the reference's range queries return them (scp_db.hpp:121-158), tetramer-major.  Lc is then
+ * built on the device (constructLc, ds_helper.hpp:82-109: one pass over the keys, run boundaries, no atomics) and is bit-identical
+ * to tetramerOccCounts; pfaai_gpu_get_arrays returns it.  Keys that are not ascending or outside [0, 160000) fail with
+ * PFAAI_ERR_CONSTRUCT. */
+int  pfaai_gpu_upload_triples(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes, const int32_t *tetramer,
+                              const pfaai_pg_t *F, int64_t nF, const int32_t *T_or_null);
 /* The same for a caller that fills the index itself on the device (e.g. a broadcast / all-gather over NVLink from
  * the rank that read the database): sizes the context's F [nF], Lc [160000] and T [P x G] buffers and returns their
  * device pointers; the caller writes them on the context's stream (or synchronises) before pfaai_gpu_build().

@@ -40,7 +40,7 @@ class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("build_ms", C.c_float), ("sort_ms", C.c_float), ("pack_ms", C.c_float),
                 ("tile_ms", C.c_float), ("d2h_ms", C.c_float), ("n_launches", C.c_int32), ("n_tiles", C.c_int32),
                 ("tile_alg_bytes", C.c_int64), ("dict_ms", C.c_float), ("reserved_", C.c_int32),
-                ("path", C.c_int32), ("dense_tau", C.c_int32), ("dense_k_sum", C.c_int64), ("patch_records", C.c_int64),
+                ("path", C.c_int32), ("dense_tau", C.c_int32), ("dense_k_sum", C.c_int64), ("sparse_items", C.c_int64),
                 ("e_size", C.c_int64), ("prep_ms", C.c_float), ("reserved2_", C.c_int32)]
 
     def as_dict(self):
@@ -84,6 +84,7 @@ def load():
     L.pfaai_gpu_set_stream.argtypes = [vp, vp]
     L.pfaai_gpu_set_shard.argtypes = [vp, i32, i32]
     L.pfaai_gpu_upload_index.argtypes = [vp, i32, i32, vp, vp, i64, vp]
+    L.pfaai_gpu_upload_triples.argtypes = [vp, i32, i32, vp, vp, i64, vp]
     L.pfaai_gpu_build.argtypes = [vp]
     L.pfaai_gpu_get_arrays.argtypes = [vp, vp, vp, vp, vp, vp]
     L.pfaai_gpu_compute_device.argtypes = [vp, i32, vp, i32, u32]
@@ -197,6 +198,17 @@ class PfaaiGpu:
                 raise ValueError("T must be P x G")
         self.P, self.G, self.nF = P, G, F.shape[0]
         self._check(self._L.pfaai_gpu_upload_index(self._h, P, G, _p(F), _p(Lc), F.shape[0], _p(T)), "upload_index")
+
+    def upload_triples(self, P, G, tetramer, F, T=None):
+        """(tetramer, protein, genome) triples in tetramer-major order; Lc is built on the device (pfaai_gpu_upload_triples)."""
+        F = np.ascontiguousarray(F, dtype=PG_DTYPE)
+        tetramer = np.ascontiguousarray(tetramer, dtype=np.int32)
+        if tetramer.shape[0] != F.shape[0]:
+            raise ValueError("one tetramer key per posting")
+        if T is not None:
+            T = np.ascontiguousarray(T, dtype=np.int32)
+        self.P, self.G, self.nF = P, G, F.shape[0]
+        self._check(self._L.pfaai_gpu_upload_triples(self._h, P, G, _p(tetramer), _p(F), F.shape[0], _p(T)), "upload_triples")
 
     def index_device_buffers(self, P, G, nF, host_T=False):
         """Size the device index buffers and return their pointers (F, Lc, T) for a caller-side fill (NCCL broadcast)."""

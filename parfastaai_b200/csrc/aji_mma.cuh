@@ -8,50 +8,57 @@
 // Formulation.  Per SCP p the tetramers whose posting list is at least `tau` genomes long are the DENSE columns 0..K_p-1.
 // With X_p[g][k] = 1 iff genome g holds dense tetramer k of SCP p (one unsigned byte), the intersection count restricted to
 // dense tetramers is the integer matrix product  C_p = X_p(rows) * X_p(cols)^T  -- computed exactly by tcgen05.mma kind::i8
-// (u8 x u8 -> s32 accumulators in tensor memory).  Every co-occurrence on a NON-dense tetramer (short lists: n(n-1)/2 pairs each)
-// is enumerated once on the device into per-(tile, SCP, 32x32 sub-tile) PATCH records that the epilogue adds to C_p, so the
-// counts are bit-exact for any input; the cost model in pfaai_gpu.cu picks tau (and falls back to the list path when the
-// patches would outweigh the contraction).
+// (u8 x u8 -> s32 accumulators in tensor memory).  Every co-occurrence on a NON-dense tetramer (short lists) is counted in the
+// same kernel by the SPARSE WALK (sparse_index.cuh): while the tensor cores work on SCP p, the epilogue warps stream the tile
+// rows' non-dense tetramers through the column block's sparse dictionary (presence bitmap + rank -> column entry, one bulk copy
+// per (tile, SCP)) and bump 16-bit shared-memory counters that the epilogue adds to C_p -- so the counts are bit-exact for any
+// input and any tau; the cost model in pfaai_gpu.cu picks tau (and falls back to the list path when that is cheaper).
 //
 //   tile      : 128 rows x 128 columns of genome pairs, one persistent CTA per SM, SCPs in ascending order (the reference's
 //               summation order).
 //   operands  : X is stored in HBM as ready-to-use shared-memory images, one per (128-genome block, SCP): K-major, no swizzle,
 //               core matrix = 8 genomes x 16 dense tetramers (128 contiguous bytes); byte (r, k) of an image sits at
 //               (k/16)*2048 + r*16 + k%16, so any K-range of all 128 genomes is ONE contiguous bulk copy (cp.async.bulk,
-//               SASS UBLKCP) -- no tensor maps.  A stage = 128 dense tetramers of the row block + of the column block (32 KB),
+//               SASS UBLKCP) -- no tensor maps.  A stage = 64 dense tetramers of the row block + of the column block (16 KB),
 //               4 stages.
-//   roles     : warp 16 lane 0 = bulk-copy producer; warp 17 lane 0 = tcgen05.mma issuer (M = N = 128, K = 32 per instruction,
-//               accumulators double-buffered in tensor memory: 2 x 128 columns); warps 0..15 = epilogue.  mbarrier pipelines:
-//               full/empty per stage, acc_full/acc_empty per accumulator buffer, ct_full/ct_empty for the ring of column T values.
-//   epilogue  : thread = (row = tensor-memory lane, 32 columns).  tcgen05.ld brings the counts, the patch records of the warp's
-//               32x32 sub-tile are added through a warp-private shared-memory counter array, then J = c/(Ta+Tb-c) (reciprocal
-//               table + two FMAs, correctly rounded: tests/test_division.py), S += J in fp64 REGISTERS, N += (c > 0).
-//               While the epilogue of SCP p runs, the tensor cores already work on SCP p+1.
+//   roles     : warp 16 lane 0 = bulk-copy producer of the operand stages and the column T values; warp 17 lane 0 = tcgen05.mma
+//               issuer (M = N = 128, K = 32 per instruction, accumulators double-buffered in tensor memory: 2 x 128 columns);
+//               warp 18 lane 0 = bulk-copy producer of the sparse dictionaries (one 96 KB stage); warps 0..15 = sparse walk +
+//               epilogue.  mbarrier pipelines: full/empty per stage, acc_full/acc_empty per accumulator buffer, ct_full/ct_empty
+//               for the ring of column T values, dict_full/dict_empty for the dictionary stage.
+//   walk      : the 4 warps of a tensor-memory lane quadrant (32 rows) share the quadrant's row items of the SCP, 128 items per
+//               warp step (coalesced LDG.128): item -> LDS.32 bitmap word -> (hit) LDS.U16 rank + POPC -> LDS.U16 entry ->
+//               RED.shared on the (row, column) counter.  The dictionary of SCP p+1 arrives while the epilogue of SCP p runs.
+//   epilogue  : thread = (row = tensor-memory lane, 32 columns).  tcgen05.ld brings the dense counts, the quadrant's sparse
+//               counters are added (and cleared), then J = c/(Ta+Tb-c) (reciprocal table + two FMAs, correctly rounded:
+//               tests/test_division.py), S += J in fp64 (tensor memory), N += (c > 0).
+//               While the walk and the epilogue of SCP p run, the tensor cores already work on SCP p+1.
 //   output    : AJI = S/N staged through shared memory in four 32-column rounds and written as contiguous row segments
 //               (and column segments for the mirror image / the transposed query modes), device memory or pinned host memory.
 #pragma once
 #include "aji_tile.cuh"
+#include "sparse_index.cuh"
 
 namespace pfaai {
 
 constexpr int MM_ROWS = 128, MM_COLS = 128;          // tile
 constexpr int MM_EPI_WARPS = 16;
-constexpr int MM_THREADS = (MM_EPI_WARPS + 2) * 32;   // + producer warp + MMA warp
-constexpr int MM_STAGE_K = 128;                       // dense tetramers per pipeline stage
-constexpr int MM_OP_BYTES = MM_STAGE_K * 128;         // one operand of one stage: 128 genomes x 128 k = 16 KB
+constexpr int MM_THREADS = (MM_EPI_WARPS + 3) * 32;   // + operand producer warp + MMA warp + dictionary producer warp
+constexpr int MM_STAGE_K = 64;                        // dense tetramers per pipeline stage
+constexpr int MM_OP_BYTES = MM_STAGE_K * 128;         // one operand of one stage: 128 genomes x 64 k = 8 KB
 constexpr int MM_STAGE_BYTES = 2 * MM_OP_BYTES;
 constexpr int MM_NSTAGE = 4;
 constexpr int MM_CT_RING = 4;                         // ring of column T values (128 x int32 per SCP)
-constexpr int MM_CNT_PITCH = 80;                      // bytes per row of a warp's patch counters (32 x uint16 + pad: conflict-free LDS.128)
-constexpr int MM_CNT_WARP = 32 * MM_CNT_PITCH;        // 2560 B per warp
+constexpr int MM_CNT_PITCH = 272;                     // bytes per row of the sparse counters (128 x uint16 + pad: conflict-free LDS.128)
+constexpr int MM_CNT_QUAD = 32 * MM_CNT_PITCH;        // 8704 B per lane quadrant (32 rows)
 constexpr int MM_STG_PITCH = 33;                      // output staging [128][33] doubles (one 32-column round)
 constexpr int MM_SMEM_MISC = 1024;
 constexpr int MM_SMEM_CT = MM_CT_RING * MM_COLS * 4;
-constexpr int MM_SMEM_CNT = MM_EPI_WARPS * MM_CNT_WARP;   // 40960 >= 128*33*8 = 33792 (staging shares it)
+constexpr int MM_SMEM_CNT = 4 * MM_CNT_QUAD;              // 34816 >= 128*33*8 = 33792 (staging shares it)
 static_assert(MM_SMEM_CNT >= MM_ROWS * MM_STG_PITCH * 8, "output staging does not fit the patch-counter area");
 constexpr int MM_SMEM_RCP = SMEM_RCP;                   // RN(1/den) per denominator
 constexpr int MM_SMEM_KP = 1024;                        // kpad[p] of every SCP (P <= 255)
-constexpr int MM_SMEM_TOTAL = MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP + MM_SMEM_CNT + MM_NSTAGE * MM_STAGE_BYTES;
+constexpr int MM_SMEM_TOTAL = MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP + MM_SMEM_CNT + MM_NSTAGE * MM_STAGE_BYTES + SP_STAGE_BYTES;
 static_assert(MM_SMEM_TOTAL <= SMEM_TOTAL, "K5 shared memory");
 constexpr int MM_TMEM_COLS = 512;                     // 2 accumulator buffers x 128 columns (s32) + 256 columns of fp64 sums S
 constexpr int MM_TMEM_S = 256;                        // first column of S: thread (lane, column group cg) owns columns S + 64 cg .. + 63
@@ -63,10 +70,14 @@ struct MmaParams {
     int64_t blk_stride;                 // bytes per 128-genome block = 128 * sum(kpad)
     const int32_t *kpad;                // [P] dense tetramers of SCP p, padded to a multiple of 32 (0: none)
     const int64_t *koff;                // [P] exclusive prefix sum of kpad
-    // patches: records of sub-tile key ((I*ncb + J)*P + p)*16 + (row/32)*4 + col/32 are rec[poff[key] .. poff[key+1])
-    const uint32_t *poff;
-    const uint16_t *rec;                // (row & 31) | (col & 31) << 5
-    int has_patches;
+    // sparse side (sparse_index.cuh): row items of (32-row group g, SCP p) = sp_items[sp_off[g*P+p]*128 ...), chunks of 128;
+    // dictionaries of (column block J, SCP p) = sp_sub[(J*P + p)*SP_MAXSUB + 0 .. sp_nsub[J*P+p]) inside sp_blob
+    const uint32_t *sp_items;
+    const int64_t *sp_off;
+    const int32_t *sp_nsub;
+    const SpSub *sp_sub;
+    const unsigned char *sp_blob;
+    int has_sparse;
     // rows / columns (kernel index -> genome id, T column)
     const int32_t *rows, *row_t, *cols, *col_t;
     int n_rows, n_cols, ncb;            // ncb = column blocks of 128
@@ -154,6 +165,33 @@ __device__ __forceinline__ void mm_epi8(uint32_t (&sv)[16], uint32_t (&N8)[8], c
     }
 }
 
+// one item of the sparse walk: x = sp_item(row, tetramer); dict32 / cq32 = shared-space addresses of the dictionary stage and of
+// the quadrant's counters.  A miss costs the bitmap load and the shift; a hit bumps the 16-bit counter(s) of the tetramer's column(s).
+__device__ __forceinline__ void sp_lookup(uint32_t dict32, uint32_t cq32, uint32_t x) {
+    uint32_t w;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(dict32 + (x >> 16)));
+    const uint32_t t = __funnelshift_l(0u, w, x);                   // w << (x & 31): presence bit of the tetramer in bit 31
+    if ((int32_t)t < 0) {
+        uint32_t rk, e;
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(rk) : "r"(dict32 + (uint32_t)SP_BM_BYTES + (x >> 17)));
+        const uint32_t ent32 = dict32 + (uint32_t)SP_ENT_OFF;
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(e) : "r"(ent32 + 2u * (rk + __popc(t))));
+        const uint32_t row32 = cq32 + ((x >> 8) & 31u) * (uint32_t)MM_CNT_PITCH;
+        if (e < 0x8000u) {
+            asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(row32 + (e & 0xffu)), "r"(1u << (e >> 8)) : "memory");
+        } else {                                                    // several columns of the block hold the tetramer: [n, e1 .. en]
+            const uint32_t l32 = ent32 + 2u * (e & 0x7fffu);
+            uint32_t n;
+            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(n) : "r"(l32));
+            for (uint32_t k = 1; k <= n; k++) {
+                uint32_t e2;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=r"(e2) : "r"(l32 + 2u * k));
+                asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(row32 + (e2 & 0xffu)), "r"(1u << (e2 >> 8)) : "memory");
+            }
+        }
+    }
+}
+
 template <int DUMMY = 0>
 __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams prm) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -163,6 +201,8 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
     uint64_t *acc_empty = acc_full + 2;                                   // [2]
     uint64_t *ct_full = acc_empty + 2;                                    // [CT_RING]
     uint64_t *ct_empty = ct_full + MM_CT_RING;                            // [CT_RING]
+    uint64_t *dict_full = ct_empty + MM_CT_RING;                          // the sparse dictionary stage
+    uint64_t *dict_empty = dict_full + 1;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + 192);
     int32_t *col_g = reinterpret_cast<int32_t *>(smem + 256);             // [128] genome id of the tile's columns (output phase)
     int32_t *ctring = reinterpret_cast<int32_t *>(smem + MM_SMEM_MISC);   // [CT_RING][128]
@@ -170,7 +210,8 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
     int32_t *kp_s = reinterpret_cast<int32_t *>(smem + MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP);   // [P] kpad
     unsigned char *cnt_mem = smem + MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP;
     unsigned char *stage_mem = cnt_mem + MM_SMEM_CNT;
-    static_assert((2 * MM_NSTAGE + 4 + 2 * MM_CT_RING) * 8 <= 192 && 256 + MM_COLS * 4 <= MM_SMEM_MISC, "misc area");
+    unsigned char *dict_mem = stage_mem + MM_NSTAGE * MM_STAGE_BYTES;
+    static_assert((2 * MM_NSTAGE + 4 + 2 * MM_CT_RING + 2) * 8 <= 192 && 256 + MM_COLS * 4 <= MM_SMEM_MISC, "misc area");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int P = prm.P;
@@ -179,6 +220,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
         for (int s = 0; s < MM_NSTAGE; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int b = 0; b < 2; b++) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], MM_EPI_WARPS); }
         for (int s = 0; s < MM_CT_RING; s++) { mbar_init(&ct_full[s], 1); mbar_init(&ct_empty[s], MM_EPI_WARPS); }
+        mbar_init(dict_full, 1); mbar_init(dict_empty, MM_EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) tmem_alloc(tmem_slot, MM_TMEM_COLS);
@@ -250,16 +292,38 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                 }
             }
         }
+    } else if (warp == MM_EPI_WARPS + 2) {
+        // ===================== producer of the sparse dictionaries: one bulk copy per (tile, SCP, part) =====================
+        if (lane == 0 && prm.has_sparse) {
+            uint32_t di = 0;
+            for (int tile_i = blockIdx.x; tile_i < prm.n_tiles; tile_i += gridDim.x) {
+                const int4 tile = prm.tiles[tile_i];
+                const int64_t jp = (int64_t)tile.y * P;
+                for (int p = 0; p < P; p++) {
+                    const int ns = __ldg(prm.sp_nsub + jp + p);
+                    for (int k = 0; k < ns; k++) {
+                        const uint4 d = __ldg(reinterpret_cast<const uint4 *>(prm.sp_sub + (jp + p) * SP_MAXSUB + k));   // {off.lo, off.hi, bytes, n}
+                        const int64_t off = (int64_t)(((uint64_t)d.y << 32) | d.x);
+                        mbar_wait(dict_empty, (di & 1u) ^ 1u);              // every walker warp is done with the previous dictionary
+                        mbar_expect_tx(dict_full, d.z);
+                        bulk_g2s(dict_mem, prm.sp_blob + off, d.z, dict_full);
+                        di++;
+                    }
+                }
+            }
+        }
     } else {
-        // ===================== epilogue warps: counts -> Jaccard -> S, N -> AJI =====================
+        // ===================== walker / epilogue warps: sparse counts, dense counts -> Jaccard -> S, N -> AJI =====================
         const int q = warp & 3, cg = warp >> 2;                  // tensor-memory lane quadrant (rows 32q..), column group (cols 32cg..)
         const int rl = q * 32 + lane;                            // row of the tile
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
         const uint32_t s_addr = tmem_base + lane_addr + MM_TMEM_S + cg * 64;       // this thread's 32 fp64 sums
-        unsigned char *cw = cnt_mem + warp * MM_CNT_WARP;        // this warp's 32 x 32 patch counters (uint16)
-        const uint32_t cw32 = smem_u32(cw);
+        const uint32_t cq32 = smem_u32(cnt_mem + q * MM_CNT_QUAD);      // the quadrant's 32 x 128 sparse counters (uint16)
+        const uint32_t cw32 = cq32 + lane * MM_CNT_PITCH + cg * 64;     // this thread's 32 counters
+        const uint32_t dict32 = smem_u32(dict_mem);
         const uint32_t rcp32 = smem_u32(rcp);
-        uint32_t ai = 0, ci = 0;
+        const bool sparse = prm.has_sparse != 0;
+        uint32_t ai = 0, ci = 0, di = 0;
         for (int tile_i = blockIdx.x; tile_i < prm.n_tiles; tile_i += gridDim.x) {
             const int4 tile = prm.tiles[tile_i];
             const int row = tile.x * MM_ROWS + rl;
@@ -268,7 +332,6 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
             const int ti = row_ok ? prm.row_t[row] : 0;
             const int j0 = tile.y * MM_COLS;
             const int ncol = min(MM_COLS, prm.n_cols - j0);
-            const int64_t key0 = ((int64_t)tile.x * prm.ncb + tile.y) * P * 16 + (q * 4 + cg);
 
             uint32_t N8[8];
 #pragma unroll
@@ -293,39 +356,43 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
             // per-SCP scalars are fetched one SCP ahead (their latency hides behind the previous SCP's epilogue): the row's T value,
             // the extent of the sub-tile's patch records and this lane's first record
             const int tileP_r = tile.x * P, tileP_c = tile.y * P;
-            const bool patches = prm.has_patches != 0, never_fast = prm.quirk != 0, all_fast = prm.all_fast != 0;
+            const bool never_fast = prm.quirk != 0, all_fast = prm.all_fast != 0;
             int ta = row_ok ? __ldg(prm.T + ti) : 0;
             bool fast = !never_fast && (all_fast || __ldg(prm.rowTmax + tileP_r) + __ldg(prm.colTmax + tileP_c) < RCP_N);
-            // patch extents are fetched TWO SCPs ahead and the lane's first record ONE ahead, so that no load is consumed in the
-            // iteration that issued it
-            uint32_t po0 = 0u, po1 = 0u, pn0 = 0u, pn1 = 0u, rec0 = 0u;
-            if (patches) {
-                po0 = __ldg(prm.poff + key0); po1 = __ldg(prm.poff + key0 + 1);
-                if (P > 1) { pn0 = __ldg(prm.poff + key0 + 16); pn1 = __ldg(prm.poff + key0 + 17); }
-                if ((uint32_t)lane < po1 - po0) rec0 = __ldg(prm.rec + po0 + lane);
-            }
+            // sparse side: the slab extents of the quadrant's row items and the number of dictionary parts, one SCP ahead
+            const int64_t gp0 = ((int64_t)tile.x * 4 + q) * P, jp0 = (int64_t)tile.y * P;
+            int64_t so0 = 0, so1 = 0;
+            int ns = 0;
+            if (sparse) { so0 = __ldg(prm.sp_off + gp0); so1 = __ldg(prm.sp_off + gp0 + 1); ns = __ldg(prm.sp_nsub + jp0); }
 
             for (int p = 0; p < P; p++) {
-                int ta_nxt = 0; bool fast_nxt = false; uint32_t pq0 = 0u, pq1 = 0u, rec_nxt = 0u;
+                int ta_nxt = 0; bool fast_nxt = false; int64_t so2 = 0; int ns_nxt = 0;
                 if (p + 1 < P) {
                     if (row_ok) ta_nxt = __ldg(prm.T + (int64_t)(p + 1) * prm.t_ld + ti);
                     fast_nxt = !never_fast && (all_fast || __ldg(prm.rowTmax + tileP_r + p + 1) + __ldg(prm.colTmax + tileP_c + p + 1) < RCP_N);
-                    if (patches) {
-                        if ((uint32_t)lane < pn1 - pn0) rec_nxt = __ldg(prm.rec + pn0 + lane);        // extents arrived an SCP ago
-                        if (p + 2 < P) { pq0 = __ldg(prm.poff + key0 + (int64_t)(p + 2) * 16); pq1 = __ldg(prm.poff + key0 + (int64_t)(p + 2) * 16 + 1); }
-                    }
+                    if (sparse) { so2 = __ldg(prm.sp_off + gp0 + p + 2); ns_nxt = __ldg(prm.sp_nsub + jp0 + p + 1); }
                 }
                 const int kp = kp_s[p];
-                const uint32_t np = po1 - po0;
-                // ---- patches of this warp's sub-tile: scatter into the warp-private counters ----
+                // ---- sparse walk: the quadrant's row items of this SCP through every part of the column block's dictionary ----
+                const bool np = ns > 0;                    // the same for the 4 warps of the quadrant (and for the whole CTA)
                 if (np) {
-                    uint32_t r = rec0;
-                    for (uint32_t i = lane; i < np; i += 32) {
-                        if (i >= 32u) r = __ldg(prm.rec + po0 + i);
-                        const uint32_t a = (r & 31u) * MM_CNT_PITCH + ((r >> 5) & 31u) * 2u;
-                        atomicAdd(reinterpret_cast<uint32_t *>(cw + (a & ~3u)), 1u << (8u * (a & 2u)));
+                    const uint4 *slab = reinterpret_cast<const uint4 *>(prm.sp_items) + so0 * 32 + lane;
+                    const int nch = (int)(so1 - so0);
+                    for (int k = 0; k < ns; k++) {
+                        uint4 it = make_uint4(0u, 0u, 0u, 0u);
+                        if (cg < nch) it = __ldg(slab + (int64_t)cg * 32);                       // in flight while we wait for the dictionary
+                        mbar_wait(dict_full, di & 1u);
+                        di++;
+                        for (int ch = cg; ch < nch; ch += 4) {
+                            const uint4 cur = it;
+                            if (ch + 4 < nch) it = __ldg(slab + (int64_t)(ch + 4) * 32);
+                            sp_lookup(dict32, cq32, cur.x); sp_lookup(dict32, cq32, cur.y);
+                            sp_lookup(dict32, cq32, cur.z); sp_lookup(dict32, cq32, cur.w);
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(dict_empty);
                     }
-                    __syncwarp();
+                    asm volatile("bar.sync %0, 128;" ::"r"(2 + q) : "memory");                   // the quadrant's counters are complete
                 }
                 // ---- column T values ----
                 const uint32_t cs = ci % MM_CT_RING;
@@ -359,7 +426,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
 #pragma unroll
                         for (int v4 = 0; v4 < 2; v4++) {
                             uint32_t w[4];
-                            const uint32_t a = cw32 + lane * MM_CNT_PITCH + hf * 32 + v4 * 16;
+                            const uint32_t a = cw32 + hf * 32 + v4 * 16;
                             asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(a));
                             asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(a), "r"(0u) : "memory");
 #pragma unroll
@@ -392,7 +459,8 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ct_empty[cs]);
                 ci++;
-                ta = ta_nxt; fast = fast_nxt; po0 = pn0; po1 = pn1; pn0 = pq0; pn1 = pq1; rec0 = rec_nxt;
+                if (np) asm volatile("bar.sync %0, 128;" ::"r"(2 + q) : "memory");              // counters read and cleared: the next walk may add
+                ta = ta_nxt; fast = fast_nxt; so0 = so1; so1 = so2; ns = ns_nxt;
             }
 
             // ================= output: AJI = S / N (computeAJI) into the dense matrix, four 32-column rounds =================

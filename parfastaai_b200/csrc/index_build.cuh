@@ -495,4 +495,29 @@ __global__ void __launch_bounds__(OS_THREADS, PF_OS_CTAS) k_onesweep(const uint6
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// K1a: Lc from an explicit tetramer key per posting (constructLc, ds_helper.hpp:82-109 <- scp_db.hpp:121-158): the postings
+// arrive tetramer-major, so the count of tetramer t is (last index of its run + 1) - (first index of its run) -- two
+// boundary stores per run, no atomics, one coalesced pass over 4 bytes per posting (HBM-bound).  run_beg / Lc must be zeroed.
+// err[0] = 1 when the keys are not ascending or out of range.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_lc_run_begins(const int32_t *__restrict__ tet, int64_t n, int32_t *__restrict__ run_beg_lo,
+                                                        int32_t *__restrict__ run_beg_hi, int *__restrict__ err) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t t = tet[i];
+        if (t < 0 || t >= NTETRA) { *err = 1; continue; }
+        const int32_t prev = (i > 0) ? tet[i - 1] : -1;
+        if (prev > t) *err = 1;
+        if (prev != t) { run_beg_lo[t] = (int32_t)(i & 0x7fffffff); run_beg_hi[t] = (int32_t)(i >> 31); }
+    }
+}
+__global__ void __launch_bounds__(256) k_lc_run_ends(const int32_t *__restrict__ tet, int64_t n, const int32_t *__restrict__ run_beg_lo,
+                                                      const int32_t *__restrict__ run_beg_hi, int32_t *__restrict__ Lc) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t t = tet[i];
+        if (t < 0 || t >= NTETRA) continue;
+        if (i + 1 == n || tet[i + 1] != t) Lc[t] = (int32_t)(i + 1 - (((int64_t)run_beg_hi[t] << 31) | (int64_t)run_beg_lo[t]));
+    }
+}
+
 }  // namespace pfaai

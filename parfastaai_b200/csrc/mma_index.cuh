@@ -4,8 +4,7 @@
 //   k_dense_ids    per SCP: dense tetramers (length >= tau) numbered 0..K_p-1
 //   k_image_fill   0/1 operand images in the tensor cores' shared-memory layout (K-major, no swizzle)
 //   k_block_t      per 128-genome block: column T values and the block maxima of T (fast-division guard)
-//   k_patch_enum   every co-occurrence on a NON-dense tetramer -> one patch record (the reference's E enumeration,
-//                  constructTetramerTuples ds_helper.hpp:270-357, restricted to the short lists)
+// (the sparse side -- row items and sparse dictionaries of the non-dense tetramers -- is built by sparse_index.cuh)
 #pragma once
 #include "aji_mma.cuh"
 
@@ -110,61 +109,12 @@ __global__ void __launch_bounds__(128) k_block_t(const int32_t *__restrict__ T, 
     if (threadIdx.x == 0) blkmax[(int64_t)blk * P + p] = max(max(wm[0], wm[1]), max(wm[2], wm[3]));
 }
 
-// int64 scan result -> the uint32 offsets the kernels read (the record count is checked against 2^32 on the host)
-__global__ void k_narrow_u32(const int64_t *__restrict__ in, int64_t n, uint32_t *__restrict__ out) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (uint32_t)in[i];
-}
-
 // largest T value of the matrix's rows / columns -> *out (atomicMax); out must be zeroed
 __global__ void k_max_t(const int32_t *__restrict__ blkmax, int64_t n, int *__restrict__ out) {
     int m = 0;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) m = max(m, blkmax[i]);
     for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
-}
-
-struct PatchParams {
-    const pfaai_pg_t *F;            // (tetramer, protein, genome) order; genomes ascend inside a (tetramer, protein) run
-    const int64_t *Lp;              // [NTETRA + 1]
-    const uint32_t *len;            // [P][NTETRA]
-    uint32_t tau;
-    int P, ncb, symmetric;
-    const int32_t *row_of, *col_of; // genome -> kernel row / column index, -1 = none
-    const uint8_t *rb_owned;        // [row blocks of 128] 1 = this shard computes the block
-    uint32_t *cnt;                  // [nkeys] counts (pass 1) / cursors (pass 2)
-    const uint32_t *poff;           // [nkeys + 1] (pass 2)
-    uint16_t *rec;                  // (pass 2)
-};
-
-template <bool FILL>
-__device__ __forceinline__ void patch_emit(const PatchParams &q, int ga, int gb, int p) {
-    const int ri = q.row_of[ga], cj = q.col_of[gb];
-    if (ri < 0 || cj < 0 || !q.rb_owned[ri >> 7]) return;
-    const int64_t key = (((int64_t)(ri >> 7) * q.ncb + (cj >> 7)) * q.P + p) * 16 + ((ri >> 5) & 3) * 4 + ((cj >> 5) & 3);
-    const uint32_t at = atomicAdd(q.cnt + key, 1u);
-    if (FILL) q.rec[q.poff[key] + at] = (uint16_t)((ri & 31) | ((cj & 31) << 5));
-}
-
-// one warp per tetramer block of F: lane i pairs posting i with the later postings of its (tetramer, protein) run
-template <bool FILL>
-__global__ void __launch_bounds__(256) k_patch_enum(const PatchParams q) {
-    const int lane = threadIdx.x & 31;
-    const int nwarp = (gridDim.x * blockDim.x) >> 5;
-    for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < NTETRA; t += nwarp) {
-        const int64_t b = q.Lp[t], e = q.Lp[t + 1];
-        for (int64_t i = b + lane; i < e; i += 32) {
-            const pfaai_pg_t a = q.F[i];
-            const uint32_t L = q.len[(int64_t)a.protein * NTETRA + t];
-            if (L < 2u || L >= q.tau) continue;
-            for (int64_t j = i + 1; j < e; j++) {
-                const pfaai_pg_t o = q.F[j];
-                if (o.protein != a.protein) break;
-                if (o.genome == a.genome) continue;
-                patch_emit<FILL>(q, a.genome, o.genome, a.protein);            // row = the smaller genome id (a < o)
-                if (!q.symmetric) patch_emit<FILL>(q, o.genome, a.genome, a.protein);
-            }
-        }
-    }
 }
 
 }  // namespace pfaai

@@ -50,7 +50,7 @@ struct Ctx {
     // dense-contraction path (K5): planning + operands + patches
     int path_pref = PFAAI_PATH_AUTO, tau_pref = 0;
     DevBuf mm_len, mm_hist, mm_did, mm_kcnt, mm_kpad, mm_koff, mm_img_rows, mm_img_cols, mm_colT, mm_rowmax, mm_colmax,
-           mm_rowof, mm_colof, mm_owned, mm_pcnt, mm_poff, mm_poff32, mm_rec;
+           mm_owned, sp_cnt, sp_nch, sp_tot, sp_off, sp_items, sp_nsub, sp_sub, sp_blob;
     int64_t e_size = -1;                  // |E| of the built index (exact length histogram), -1 = not computed for this build
     // routed build: this context holds postings [slice_begin, slice_begin + n_slice) of F only
     bool sliced = false;
@@ -278,8 +278,8 @@ int pfaai_gpu_create(pfaai_gpu_ctx **out, int device, unsigned /*flags*/) {
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { g_create_error = "cudaStreamCreate failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
     for (auto &ev : c->ev)
         if (cudaEventCreate(&ev) != cudaSuccess) { g_create_error = "cudaEventCreate failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
-    if (cudaMalloc(&c->flags.p, 64) != cudaSuccess) { g_create_error = "cudaMalloc failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
-    c->flags.cap = 64;
+    if (cudaMalloc(&c->flags.p, 128) != cudaSuccess) { g_create_error = "cudaMalloc failed"; delete c; return PFAAI_ERR_CONSTRUCT; }
+    c->flags.cap = 128;
     *out = reinterpret_cast<pfaai_gpu_ctx *>(c);
     return PFAAI_OK;
 }
@@ -295,8 +295,8 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
                      &c->nsub, &c->sub, &c->colT, &c->blob, &c->stage_off, &c->stages, &c->stage_rng,
                      &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr, &c->route_hist, &c->recv,
                      &c->mm_len, &c->mm_hist, &c->mm_did, &c->mm_kcnt, &c->mm_kpad, &c->mm_koff, &c->mm_img_rows, &c->mm_img_cols,
-                     &c->mm_colT, &c->mm_rowmax, &c->mm_colmax, &c->mm_rowof, &c->mm_colof, &c->mm_owned, &c->mm_pcnt,
-                     &c->mm_poff, &c->mm_poff32, &c->mm_rec};
+                     &c->mm_colT, &c->mm_rowmax, &c->mm_colmax, &c->mm_owned, &c->sp_cnt, &c->sp_nch, &c->sp_tot, &c->sp_off, &c->sp_items,
+                     &c->sp_nsub, &c->sp_sub, &c->sp_blob};
     for (DevBuf *b : all) release(*b);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
@@ -381,6 +381,49 @@ int pfaai_gpu_upload_index(pfaai_gpu_ctx *h, int P, int G, const pfaai_pg_t *F, 
     if (T) PF_CUDA(c, cudaMemcpyAsync(c->T.p, T, sizeof(int32_t) * (size_t)P * G, cudaMemcpyHostToDevice, c->stream));
     PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));   // the caller may reuse its buffers
+    c->tm.h2d_ms = ev_ms(c, EV_H2D0, EV_H2D1);
+    c->uploaded = true;
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_upload_triples(pfaai_gpu_ctx *h, int P, int G, const int32_t *tetramer, const pfaai_pg_t *F, int64_t nF, const int32_t *T) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (P <= 0 || G <= 0 || nF < 0 || (nF > 0 && (!F || !tetramer))) { set_error(c, "upload_triples: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
+    if ((int64_t)P * G >= (1ll << 31)) { set_error(c, "upload_triples: P*G too large"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false;
+    PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
+    PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
+    // the tetramer keys are staged in the (not yet used) sort buffer; two boundary arrays of NTETRA int32 live in Lp32 / Lp64
+    PF_TRY(ensure(c, c->itemsA, sizeof(uint64_t) * (size_t)std::max<int64_t>(nF, 1)));
+    PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
+    PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
+    int32_t *tet_dev = ptr<int32_t>(c->itemsA);
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D0], c->stream));
+    if (nF > 0) {
+        PF_CUDA(c, cudaMemcpyAsync(c->F.p, F, sizeof(pfaai_pg_t) * (size_t)nF, cudaMemcpyHostToDevice, c->stream));
+        PF_CUDA(c, cudaMemcpyAsync(tet_dev, tetramer, sizeof(int32_t) * (size_t)nF, cudaMemcpyHostToDevice, c->stream));
+    }
+    if (T) PF_CUDA(c, cudaMemcpyAsync(c->T.p, T, sizeof(int32_t) * (size_t)P * G, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D1], c->stream));
+    int *err = ptr<int>(c->flags) + 15;
+    PF_CUDA(c, cudaMemsetAsync(err, 0, sizeof(int), c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->Lc.p, 0, sizeof(int32_t) * NTETRA, c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->Lp32.p, 0, sizeof(int32_t) * NTETRA, c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->Lp64.p, 0, sizeof(int32_t) * NTETRA, c->stream));
+    if (nF > 0) {
+        const unsigned grid = (unsigned)std::min<int64_t>(ceil_div64(nF, 256), (int64_t)c->sm_count * 32);
+        k_lc_run_begins<<<grid, 256, 0, c->stream>>>(tet_dev, nF, ptr<int32_t>(c->Lp32), ptr<int32_t>(c->Lp64), err);
+        PF_LAUNCH_CHECK(c);
+        k_lc_run_ends<<<grid, 256, 0, c->stream>>>(tet_dev, nF, ptr<int32_t>(c->Lp32), ptr<int32_t>(c->Lp64), ptr<int32_t>(c->Lc));
+        PF_LAUNCH_CHECK(c);
+    }
+    int eh = 0;
+    PF_CUDA(c, cudaMemcpyAsync(&eh, err, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (eh) { set_error(c, "upload_triples: tetramer keys must be ascending and inside [0, 160000)"); return PFAAI_ERR_CONSTRUCT; }
     c->tm.h2d_ms = ev_ms(c, EV_H2D0, EV_H2D1);
     c->uploaded = true;
     return PFAAI_OK;
@@ -869,9 +912,9 @@ struct MmaPlan {
     bool exact = false;                   // the length histogram covers every genome (not the planning sample)
     uint32_t tau = 0;
     int64_t k_sum = 0;                    // dense tetramers over all SCPs, padded to 32 per SCP
-    int64_t patch_est = 0;                // co-occurrences on non-dense tetramers (estimate: all-vs-all pairs)
-    int64_t patch_records = 0;
-    bool has_patches = false;
+    int64_t sparse_est = 0;               // postings on non-dense tetramers (estimate)
+    int64_t sparse_items = 0;
+    bool has_sparse = false;
     double t_mma = 0, t_lists = 0;        // cost-model seconds
     std::vector<unsigned long long> hist; // [0..HMAX] lists per length (sample units when !exact), [HMAX+1] = sum n(n-1)/2
     int stride = 1;
@@ -905,39 +948,38 @@ static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl) {
 // The decision rule between the two tile paths (north_star: dense contraction only where the per-SCP tetramer density makes it
 // the denser one).  Inputs: the posting-list length histogram, the number of matrix cells this context computes, |F|.
 // Constants are measured rates of this repository's kernels on B200: the list path performs
-// cells * (|F|/G) / 64 dictionary lookups at 8.2e11/s; the dense path streams K_sum bytes of each operand per cell row/column
-// (L2-bound: 7.6e14 multiply-accumulates/s), runs the fp64 epilogue at 5.4e-13 s per (cell, SCP) and pays 1.8e-11 s per patch
-// record (two atomic passes to build, one shared-memory atomic to apply).
+// cells * (|F|/G) / 64 dictionary lookups at 8.2e11/s.  The hybrid path streams K_sum bytes of each operand per cell row/column
+// through the tensor cores (L2-bound: 7.6e14 multiply-accumulates/s) and, concurrently on the other warps, walks the rows'
+// non-dense postings through one sparse dictionary per 128 columns (cells/128 * non-dense postings per genome lookups at
+// PF_WALK_S seconds each) and runs the fp64 epilogue (5.4e-13 s per (cell, SCP)); tau moves tetramers between the two sides.
+#ifndef PF_WALK_S
+#define PF_WALK_S 7.0e-13
+#endif
 static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_blocks, bool force) {
     static const uint32_t cand[] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048, 3072, 4096};
     const int P = c->P, G = c->G;
     const double s = (double)pl.stride, nF = (double)c->nF;
-    const double all_pairs = std::max(1.0, 0.5 * (double)G * ((double)G - 1.0));
-    const double frac = std::min(1.0, cells / all_pairs);
     pl.t_lists = cells * (nF / std::max(1, G)) / 64.0 / 8.2e11 + nF * 1.4e-11;
     double best = 1e300;
     for (uint32_t tau : cand) {
         if (c->tau_pref > 0 && tau != cand[0]) break;
-        if (c->tau_pref > 0) tau = (uint32_t)c->tau_pref;
+        if (c->tau_pref > 0) tau = (uint32_t)std::min(c->tau_pref, MM_HMAX);   // lists of >= MM_HMAX genomes are always dense
         const uint32_t m0 = (uint32_t)std::max(1.0, std::ceil((double)tau / s));   // sample count at which a list is called dense
-        double K = 0, E = 0;
-        for (uint32_t m = 1; m <= (uint32_t)MM_HMAX; m++) {
-            const double h = (double)pl.hist[m];
-            if (m >= m0 || m == (uint32_t)MM_HMAX) K += h;
-            else if (m >= 2) E += h * 0.5 * (double)m * (double)(m - 1) * s * s;
-        }
+        double K = 0, dense_post = 0;
+        for (uint32_t m = m0; m <= (uint32_t)MM_HMAX; m++) { K += (double)pl.hist[m]; dense_post += (double)pl.hist[m] * m * s; }
+        const double sparse_post = std::max(0.0, nF - dense_post);                  // includes the lists the sample never saw
         const double k_sum = K + 16.0 * P;                                          // padding to 32 per SCP, on average
         const double img_bytes = (double)img_blocks * 128.0 * k_sum;
-        const double patches = E * frac * (frac < 1.0 ? 2.0 : 1.0);
-        if (c->tau_pref == 0 && (img_bytes > 48e9 || patches > 2.0e9)) continue;
-        const double t = k_sum * cells / 7.6e14 + patches * 1.8e-11 + img_bytes / 3e12;
-        if (t < best) { best = t; pl.tau = tau; pl.k_sum = (int64_t)k_sum; pl.patch_est = (int64_t)patches; }
+        if (c->tau_pref == 0 && img_bytes > 48e9) continue;
+        const double lookups = cells / 128.0 * sparse_post / std::max(1, G);
+        const double t = std::max(k_sum * cells / 7.6e14, cells * P * 5.4e-13 + lookups * PF_WALK_S) + img_bytes / 3e12 + sparse_post * 2e-11;
+        if (t < best) { best = t; pl.tau = tau; pl.k_sum = (int64_t)k_sum; pl.sparse_est = (int64_t)sparse_post; }
     }
-    pl.t_mma = best + cells * P * 5.4e-13 + nF * 2e-11;
+    pl.t_mma = best + nF * 2e-11;
     pl.use = force ? (best < 1e299) : (pl.t_mma < pl.t_lists);
 }
 
-// dense ids, operand images, column T values, patches (everything aji_mma_kernel reads); sets prm's K5 pointers
+// dense ids, operand images, column T values, sparse row items and dictionaries (everything aji_mma_kernel reads); sets prm's K5 pointers
 static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n_cols, const std::vector<uint8_t> &rb_owned,
                        std::vector<int32_t> &kpad_host, MmaParams &prm) {
     const int P = c->P, G = c->G;
@@ -1001,51 +1043,73 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
     PF_TRY(fill(c->mm_img_rows, c->rows, n_rows, nrb));
     const bool same = m.symmetric != 0;
     if (!same) PF_TRY(fill(c->mm_img_cols, c->cols, n_cols, ncb));
-    // 4. patches: every co-occurrence on a tetramer whose list is shorter than tau
+    // 4. sparse side: row items of the kernel rows and the column blocks' sparse dictionaries (sparse_index.cuh) -- every
+    //    co-occurrence on a tetramer whose list is shorter than tau is counted by the tile kernel's walk
     double e_sparse = 0;
-    for (uint32_t L = 2; L < std::min<uint32_t>(pl.tau, MM_HMAX); L++) e_sparse += (double)pl.hist[L] * 0.5 * L * (L - 1);
-    pl.has_patches = false; pl.patch_records = 0;
-    const int64_t nkeys = (int64_t)nrb * ncb * P * 16;
-    if (e_sparse > 0 && nkeys > 0) {
-        std::vector<int32_t> row_of(G, -1), col_of(G, -1);
-        for (int i = 0; i < n_rows; i++) row_of[m.rows[i]] = i;
-        for (int j = 0; j < n_cols; j++) col_of[m.cols[j]] = j;
-        PF_TRY(upload_i32(c, c->mm_rowof, row_of)); PF_TRY(upload_i32(c, c->mm_colof, col_of));
+    for (uint32_t L = 1; L < std::min<uint32_t>(pl.tau, MM_HMAX); L++) e_sparse += (double)pl.hist[L] * L;   // non-dense postings
+    pl.has_sparse = false; pl.sparse_items = 0;
+    if (e_sparse > 0 && nrb > 0 && ncb > 0) {
+        const int64_t n_gp = (int64_t)nrb * 4 * P;                   // (32-row group, SCP) slabs; groups beyond the last row stay empty
+        PF_TRY(ensure(c, c->sp_cnt, sizeof(int32_t) * (size_t)n_gp * SP_ROWS));
+        PF_TRY(ensure(c, c->sp_nch, sizeof(int32_t) * (size_t)n_gp));
+        PF_TRY(ensure(c, c->sp_tot, sizeof(int32_t) * (size_t)n_gp));
+        PF_TRY(ensure(c, c->sp_off, sizeof(int64_t) * (size_t)(n_gp + 1)));
+        PF_CUDA(c, cudaMemsetAsync(c->sp_cnt.p, 0, sizeof(int32_t) * (size_t)n_gp * SP_ROWS, c->stream));
         PF_TRY(ensure(c, c->mm_owned, rb_owned.size()));
         PF_CUDA(c, cudaMemcpyAsync(c->mm_owned.p, rb_owned.data(), rb_owned.size(), cudaMemcpyHostToDevice, c->stream));
-        PF_TRY(ensure(c, c->mm_pcnt, sizeof(uint32_t) * (size_t)nkeys));
-        PF_TRY(ensure(c, c->mm_poff, sizeof(int64_t) * (size_t)(nkeys + 1)));
-        PF_TRY(ensure(c, c->mm_poff32, sizeof(uint32_t) * (size_t)(nkeys + 1)));
-        PatchParams q;
-        q.F = ptr<pfaai_pg_t>(c->F); q.Lp = ptr<int64_t>(c->Lp64); q.len = ptr<uint32_t>(c->mm_len); q.tau = pl.tau;
-        q.P = P; q.ncb = ncb; q.symmetric = m.symmetric;
-        q.row_of = ptr<int32_t>(c->mm_rowof); q.col_of = ptr<int32_t>(c->mm_colof); q.rb_owned = ptr<uint8_t>(c->mm_owned);
-        q.cnt = ptr<uint32_t>(c->mm_pcnt); q.poff = nullptr; q.rec = nullptr;
-        const unsigned grid = (unsigned)(c->sm_count * 16);
-        PF_CUDA(c, cudaMemsetAsync(c->mm_pcnt.p, 0, sizeof(uint32_t) * (size_t)nkeys, c->stream));
-        k_patch_enum<false><<<grid, 256, 0, c->stream>>>(q);
+        const unsigned wgrid = (unsigned)std::min<int64_t>(ceil_div64((int64_t)n_rows * P, 8), (int64_t)c->sm_count * 16);
+        k_sp_count<<<wgrid, 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), ptr<int32_t>(c->rows), n_rows, P,
+                                                 ptr<uint16_t>(c->mm_did), ptr<uint8_t>(c->mm_owned), ptr<int32_t>(c->sp_cnt));
         PF_LAUNCH_CHECK(c);
-        PF_TRY(launch_scan(c, ptr<int32_t>(c->mm_pcnt), nkeys, ptr<int64_t>(c->mm_poff), nullptr));
-        int64_t total = 0;
-        PF_CUDA(c, cudaMemcpyAsync(&total, ptr<int64_t>(c->mm_poff) + nkeys, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+        k_sp_group<<<(unsigned)ceil_div64(n_gp, 256), 256, 0, c->stream>>>(ptr<int32_t>(c->sp_cnt), n_gp, ptr<int32_t>(c->sp_nch), ptr<int32_t>(c->sp_tot));
+        PF_LAUNCH_CHECK(c);
+        PF_TRY(launch_scan(c, ptr<int32_t>(c->sp_nch), n_gp, ptr<int64_t>(c->sp_off), nullptr));
+        int64_t n_chunks = 0;
+        PF_CUDA(c, cudaMemcpyAsync(&n_chunks, ptr<int64_t>(c->sp_off) + n_gp, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
         PF_CUDA(c, cudaStreamSynchronize(c->stream));
-        if (total >= (1ll << 32)) { set_error(c, "dense path: more than 2^32 patch records at this threshold"); return PFAAI_ERR_CONSTRUCT; }
-        if (total > 0) {
-            k_narrow_u32<<<(unsigned)(c->sm_count * 8), 256, 0, c->stream>>>(ptr<int64_t>(c->mm_poff), nkeys + 1, ptr<uint32_t>(c->mm_poff32));
+        PF_TRY(ensure(c, c->sp_items, sizeof(uint32_t) * SP_CHUNK * (size_t)std::max<int64_t>(n_chunks, 1)));
+        if (n_chunks > 0) {
+            k_sp_fill<<<wgrid, 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), ptr<int32_t>(c->rows), n_rows, P,
+                                                    ptr<uint16_t>(c->mm_did), ptr<uint8_t>(c->mm_owned), ptr<int32_t>(c->sp_cnt), ptr<int32_t>(c->sp_tot),
+                                                    ptr<int64_t>(c->sp_off), ptr<uint32_t>(c->sp_items));
             PF_LAUNCH_CHECK(c);
-            PF_TRY(ensure(c, c->mm_rec, sizeof(uint16_t) * (size_t)total));
-            PF_CUDA(c, cudaMemsetAsync(c->mm_pcnt.p, 0, sizeof(uint32_t) * (size_t)nkeys, c->stream));
-            q.poff = ptr<uint32_t>(c->mm_poff32); q.rec = ptr<uint16_t>(c->mm_rec);
-            k_patch_enum<true><<<grid, 256, 0, c->stream>>>(q);
-            PF_LAUNCH_CHECK(c);
-            pl.has_patches = true; pl.patch_records = total;
         }
+        // dictionaries: bump allocation; when the first estimate is too small the builder still counts the need and we re-run
+        const int64_t n_dict = (int64_t)ncb * P;
+        PF_TRY(ensure(c, c->sp_nsub, sizeof(int32_t) * (size_t)n_dict));
+        PF_TRY(ensure(c, c->sp_sub, sizeof(SpSub) * (size_t)n_dict * SP_MAXSUB));
+        int *sp_err = ptr<int>(c->flags) + 14;
+        unsigned long long *cursor = reinterpret_cast<unsigned long long *>(ptr<int>(c->flags) + 16);
+        size_t cap = (size_t)n_dict * (SP_ENT_OFF + 64) + (size_t)(2.5 * e_sparse * (m.symmetric ? 1.0 : (double)n_cols / std::max(1, G))) + (1u << 20);
+        auto kern = k_spdict_build;
+        PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SD_SMEM));
+        for (int attempt = 0; attempt < 2; attempt++) {
+            PF_TRY(ensure(c, c->sp_blob, cap));
+            PF_CUDA(c, cudaMemsetAsync(sp_err, 0, sizeof(int), c->stream));
+            PF_CUDA(c, cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), c->stream));
+            SpDictParams q;
+            q.seg_off = ptr<int64_t>(c->seg_off); q.vals = ptr<uint32_t>(c->vals); q.cols = ptr<int32_t>(c->cols); q.n_cols = n_cols; q.P = P;
+            q.did = ptr<uint16_t>(c->mm_did); q.blob = ptr<unsigned char>(c->sp_blob); q.blob_cap = (unsigned long long)c->sp_blob.cap;
+            q.cursor = cursor; q.nsub = ptr<int32_t>(c->sp_nsub); q.sub = ptr<SpSub>(c->sp_sub); q.err = sp_err;
+            kern<<<(unsigned)n_dict, SD_THREADS, SD_SMEM, c->stream>>>(q);
+            PF_LAUNCH_CHECK(c);
+            int eh2 = 0; unsigned long long need = 0;
+            PF_CUDA(c, cudaMemcpyAsync(&eh2, sp_err, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+            PF_CUDA(c, cudaMemcpyAsync(&need, cursor, sizeof(need), cudaMemcpyDeviceToHost, c->stream));
+            PF_CUDA(c, cudaStreamSynchronize(c->stream));
+            if (eh2 == 2) { set_error(c, "dense path: a column block's sparse dictionary does not fit a shared-memory stage at this threshold"); return PFAAI_ERR_CONSTRUCT; }
+            if (eh2 == 0) break;
+            if (attempt == 1) { set_error(c, "dense path: sparse dictionary buffer too small"); return PFAAI_ERR_CONSTRUCT; }
+            cap = (size_t)need + (size_t)need / 16 + (1u << 20);
+        }
+        pl.has_sparse = true; pl.sparse_items = (int64_t)e_sparse;
     }
+    prm.sp_items = ptr<uint32_t>(c->sp_items); prm.sp_off = ptr<int64_t>(c->sp_off); prm.sp_nsub = ptr<int32_t>(c->sp_nsub);
+    prm.sp_sub = ptr<SpSub>(c->sp_sub); prm.sp_blob = ptr<unsigned char>(c->sp_blob); prm.has_sparse = pl.has_sparse ? 1 : 0;
     prm.img_rows = reinterpret_cast<unsigned char *>(c->mm_img_rows.p);
     prm.img_cols = same ? prm.img_rows : reinterpret_cast<unsigned char *>(c->mm_img_cols.p);
     prm.blk_stride = blk_stride;
     prm.kpad = ptr<int32_t>(c->mm_kpad); prm.koff = ptr<int64_t>(c->mm_koff);
-    prm.poff = ptr<uint32_t>(c->mm_poff32); prm.rec = ptr<uint16_t>(c->mm_rec); prm.has_patches = pl.has_patches ? 1 : 0;
     prm.colT = ptr<int32_t>(c->mm_colT); prm.rowTmax = ptr<int32_t>(c->mm_rowmax); prm.colTmax = ptr<int32_t>(c->mm_colmax);
     prm.ncb = ncb;
     return PFAAI_OK;
@@ -1185,6 +1249,20 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         for (int r = 0; r < nr; r++) c->owned_rows.push_back(row0 + r);
         local_rows += nr;
     }
+    if (use_mma) {
+        // K5 streams column-side data (operand image + sparse dictionary of the column block) as well as row-side data per
+        // (tile, SCP): order the tiles in 12 x 12 super-tiles, so that the ~148 tiles in flight share 12 row blocks and 12
+        // column blocks and every stream is read from HBM once and from L2 eleven times
+        constexpr int ST = 12;
+        std::stable_sort(tiles.begin(), tiles.end(), [](const int4 &a, const int4 &b) {
+            const int ka = (a.x / ST), kb = (b.x / ST);
+            if (ka != kb) return ka < kb;
+            const int ja = (a.y / ST), jb = (b.y / ST);
+            if (ja != jb) return ja < jb;
+            if (a.x != b.x) return a.x < b.x;
+            return a.y < b.y;
+        });
+    }
     const int n_early = (int)tiles.size();
     tiles.insert(tiles.end(), tiles_late.begin(), tiles_late.end());
     PF_TRY(ensure(c, c->tiles, sizeof(int4) * tiles.size()));
@@ -1289,7 +1367,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     c->tm.path = use_mma ? PFAAI_PATH_MMA : PFAAI_PATH_LISTS;
     c->tm.dense_tau = use_mma ? (int32_t)pl.tau : 0;
     c->tm.dense_k_sum = use_mma ? pl.k_sum : 0;
-    c->tm.patch_records = use_mma ? pl.patch_records : 0;
+    c->tm.sparse_items = use_mma ? pl.sparse_items : 0;
     c->tm.e_size = c->e_size;
     c->tm.tile_ms = ev_ms(c, EV_T0, EV_T1);
     c->tm.n_tiles = (int32_t)tiles.size();

@@ -14,9 +14,11 @@
 #pragma once
 #include <chrono>
 #include <cstdio>
+#include <iomanip>
 #include <iostream>
 #include <memory>
 #include <string>
+#include <sys/resource.h>
 #include <thread>
 #include <unordered_map>
 #include <vector>
@@ -42,6 +44,29 @@ struct PhaseTimer {
         return ms;
     }
 };
+
+// One phase line in the reference's format (PRINT_RUNTIME_MEMUSED, utils.hpp:136-147,181-200): users parse these prefixes --
+//   "<prefix><ms> ms (<sec> sec/<min> min); <maxrss> KB (<MB> MB/<GB> GB)."  with the same iostream widths / precisions.
+inline void print_ref_phase(const char *prefix, double ms) {
+    std::ostream &ox = std::cout;
+    const std::ios::fmtflags f = ox.flags();
+    const std::streamsize pr = ox.precision();
+    ox << prefix;
+    ox.precision(3); ox << std::setw(10) << ms << " ms (";
+    ox.precision(4); ox << std::setw(10) << ms / 1000.0 << " sec/";
+    ox.precision(4); ox << std::setw(10) << ms / 60000.0 << " min)";
+    struct rusage usage;
+    ox << "; ";
+    if (getrusage(RUSAGE_SELF, &usage) == 0) {
+        const uint64_t kb = (uint64_t)usage.ru_maxrss;
+        ox.precision(2);
+        ox << std::setw(10) << kb << " KB (" << std::setw(10) << kb / 1024 << " MB/" << std::setw(10) << kb / (1024 * 1024) << " GB).";
+    } else {
+        ox << " Mem usage returned error ";
+    }
+    ox << std::endl;
+    ox.flags(f); ox.precision(pr);
+}
 
 // JAC/AJI lists (the reference's per-pair vectors) are only materialised up to this many pairs; beyond it
 // the dense matrix is the only product (1.25e9 pairs x 24 B would be 30 GB at BASELINE config 5).
@@ -110,7 +135,15 @@ class DataStructBase {
             std::cerr << "Error in Lc, F, T host load ; Error code : " << PFAAI_ERR_SQLITE_DB << std::endl;
             return m_errorCode = PFAAI_ERR_SQLITE_DB;
         }
-        std::printf("Lc, F, T host load  : %10.3f ms; |F| = %zu\n", tm.lap_ms(), m_ix.F.size());
+        // the reference's phase lines (interface.hpp:307-325).  One pass per table delivers Lc, F and T together, so the whole
+        // ingest is reported on the first line and the other two carry 0; "E constr." is what replaces it here: upload + device
+        // index build (no E array exists).  Our own detail lines follow, indented.
+        const double load_ms = tm.lap_ms();
+        std::fflush(stdout);
+        print_ref_phase("Lc & Lp contruction : ", load_ms);
+        print_ref_phase("F contruction       : ", 0.0);
+        print_ref_phase("T construction      : ", 0.0);
+        std::printf("  Lc, F, T host load  : %10.3f ms; |F| = %zu\n", load_ms, m_ix.F.size());
         // one host thread per GPU (the C-ABI is one-thread-per-context): upload + device build on every GPU in parallel
         const int n = (int)m_devices.size();
         m_ctxs.assign(n, nullptr);
@@ -183,8 +216,11 @@ class DataStructBase {
         }
         pfaai_timings_t t;
         pfaai_gpu_get_timings(m_ctx, &t);
-        std::printf("Device index build  : %10.3f ms; (%d GPU(s); GPU %d: H2D %.3f ms, build kernels %.3f ms, of which sort %.3f ms)\n",
-                    tm.lap_ms(), n, m_devices[0], t.h2d_ms, t.build_ms, t.sort_ms);
+        const double build_ms = tm.lap_ms();
+        std::fflush(stdout);
+        print_ref_phase("E constr.   (fin)   : ", build_ms);
+        std::printf("  Device index build  : %10.3f ms; (%d GPU(s); GPU %d: H2D %.3f ms, build kernels %.3f ms, of which sort %.3f ms)\n",
+                    build_ms, n, m_devices[0], t.h2d_ms, t.build_ms, t.sort_ms);
         return m_errorCode = PFAAI_OK;
     }
 };
@@ -378,8 +414,12 @@ class ParFAAIImpl {
             }
             pfaai_gpu_get_timings(ctx, &t);
         }
-        std::printf("JAC Construction    : %10.3f ms; (%d GPU(s); GPU 0: row slabs %.3f ms, dictionaries %.3f ms, tile kernel %.3f ms over %d tiles, D2H %.3f ms)\n",
-                    tm.lap_ms(), n, t.pack_ms, t.dict_ms, t.tile_ms, t.n_tiles, t.d2h_ms);
+        const double jac_ms = tm.lap_ms();
+        std::fflush(stdout);
+        print_ref_phase("JAC Construction    : ", jac_ms);                 // algorithm_impl.hpp:304
+        std::printf("  JAC on %d GPU(s)     : %10.3f ms; (GPU 0: %s, row slabs %.3f ms, dictionaries %.3f ms, dense-path prep %.3f ms, tile kernel %.3f ms over %d tiles, D2H %.3f ms)\n",
+                    n, jac_ms, t.path == PFAAI_PATH_MMA ? "tensor-core contraction + sparse walk" : "dictionary walk", t.pack_ms, t.dict_ms, t.prep_ms,
+                    t.tile_ms, t.n_tiles, t.d2h_ms);
         return PFAAI_OK;
     }
     // AJI = S / N is fused into the tile kernel (computeAJI, algorithm_impl.hpp:309-322); kept for call compatibility

@@ -1,9 +1,9 @@
-"""GPU parity tests of the dense-contraction tile path (K5: aji_mma_kernel, tcgen05 u8 x u8 -> s32 + patch records).
+"""GPU parity tests of the hybrid tile path (K5: aji_mma_kernel, tcgen05 u8 x u8 -> s32 + in-kernel sparse walk).
 
 Same bars as test_gpu_parity.py: per-(pair, SCP) intersection counts and N bit-exact, S within 1e-7, AJI bit-identical to the
 reference goldens and to the oracle; and the two tile paths (PATH_LISTS / PATH_MMA) must agree bit for bit in every output.
 The density threshold tau is forced to several values so that both halves of the path are exercised: tau = 2 puts every shared
-tetramer on the tensor cores (no patches), a large tau moves most co-occurrences into patch records."""
+tetramer on the tensor cores (no sparse side), a large tau moves most co-occurrences to the sparse walk."""
 import os
 import sys
 
@@ -43,7 +43,7 @@ def test_all_vs_all_golden_dense_path(pf, orc, name, tau):
     tm = ctx.timings()
     assert tm["path"] == pf.PATH_MMA and (tau == 0 or tm["dense_tau"] == tau)
     if tau >= 3 and G >= tau:
-        assert tm["patch_records"] > 0
+        assert tm["sparse_items"] > 0
     ref = orc.full_pipeline(orc.ALL_VS_ALL, G, P, g["lc"], g["f"], g["t"])
     assert np.array_equal(res["counts"], ref["counts"])
     assert tm["e_size"] == int(ref["counts"].sum())          # |E| of the reference's E array
@@ -83,10 +83,13 @@ def test_query_modes_golden_dense_path(pf, orc, tau):
 
 
 @pytest.mark.parametrize("N,P,seed,dense,tau", [(70, 12, 1, False, 2), (200, 9, 2, False, 4), (333, 7, 3, True, 0), (333, 7, 3, True, 40),
-                                                (450, 5, 4, False, 12), (600, 4, 6, True, 3)])
+                                                (450, 5, 4, False, 12), (600, 4, 6, True, 3),
+                                                # everything on the sparse walk (no dense tetramer at all): multi-column lists,
+                                                # dictionaries split by columns
+                                                (333, 7, 3, True, 100000), (450, 5, 4, False, 100000), (1100, 3, 8, False, 30)])
 def test_synthetic_all_vs_all_both_paths_vs_oracle(pf, orc, N, P, seed, dense, tau):
     """Several 128 x 128 tiles, ragged edges, triangular tile skipping, K chunks beyond one stage, dense and sparse families,
-    patch-heavy thresholds; the list path on the same context must give the same bytes."""
+    walk-heavy thresholds; the list path on the same context must give the same bytes."""
     from parfastaai_b200 import synth
     off, vals = synth.generate(N, P, seed=seed, dense=dense)
     Lc, F = synth.to_reference(N, P, off, vals)

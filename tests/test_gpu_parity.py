@@ -69,6 +69,28 @@ def test_index_build_golden(pf, orc, name):
 
 
 @pytest.mark.parametrize("name", ["xanthodb", "xdb_subset1", "xdb_subset2"])
+def test_lc_built_on_the_device_from_tetramer_keys(pf, name):
+    """constructLc (ds_helper.hpp:82-109) on the device: the (tetramer, protein, genome) triples go in, Lc == *_lc_array.bin
+    comes out, and everything downstream (Lp, T, lists, AJI) equals the Lc-fed path; unsorted / out-of-range keys fail loudly."""
+    g = gu.load(name)
+    P, G = g["t"].shape
+    tet = np.repeat(np.arange(pf.NTETRA, dtype=np.int32), g["lc"])
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_triples(P, G, tet, g["f"])
+    ctx.build()
+    a = ctx.get_arrays()
+    assert np.array_equal(a["Lc"], g["lc"]) and np.array_equal(a["Lp"], g["lp"]) and np.array_equal(a["T"], g["t"])
+    res = ctx.compute(pf.ALL_VS_ALL, want_jac=True)
+    assert np.array_equal(res["aji"], g["aji"])
+    with pytest.raises(pf.PfaaiError):
+        ctx.upload_triples(P, G, tet[::-1].copy(), g["f"])
+    bad = tet.copy(); bad[-1] = pf.NTETRA
+    with pytest.raises(pf.PfaaiError):
+        ctx.upload_triples(P, G, bad, g["f"])
+    ctx.close()
+
+
+@pytest.mark.parametrize("name", ["xanthodb", "xdb_subset1", "xdb_subset2"])
 def test_all_vs_all_golden(pf, orc, name):
     g = gu.load(name)
     ctx, P, G = _ctx_for(pf, g)
