@@ -32,7 +32,7 @@ EXPORTS = [
     "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
     "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
     "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench", "pfaai_gpu_set_path", "pfaai_gpu_e_size",
-    "pfaai_gpu_host_register", "pfaai_gpu_host_unregister",
+    "pfaai_gpu_host_register", "pfaai_gpu_host_unregister", "pfaai_gpu_upload_triples",
 ]
 
 

@@ -47,7 +47,19 @@ constexpr int MM_THREADS = (MM_EPI_WARPS + 3) * 32;   // + operand producer warp
 constexpr int MM_STAGE_K = 64;                        // dense tetramers per pipeline stage
 constexpr int MM_OP_BYTES = MM_STAGE_K * 128;         // one operand of one stage: 128 genomes x 64 k = 8 KB
 constexpr int MM_STAGE_BYTES = 2 * MM_OP_BYTES;
-constexpr int MM_NSTAGE = 4;
+// Shared-memory plan, two variants chosen per compute call (what is not fixed is split between the operand ring, the ring of
+// row items and the dictionary stage): sparse inputs walk many items through large dictionaries and contract few dense
+// tetramers; dense inputs stream large operands and walk almost nothing.
+template <int NSTAGE_, int ENT_MAX_, int RING_D_> struct MmCfg {
+    static constexpr int NSTAGE = NSTAGE_;                        // operand pipeline stages
+    static constexpr int ENT_MAX = ENT_MAX_;                      // dictionary stage capacity (sparse_index.cuh)
+    static constexpr int RING_D = RING_D_;                        // row-item chunks in flight per walker warp (cp.async ring)
+    static constexpr int DICT_BYTES = sp_stage_bytes(ENT_MAX_);
+    static constexpr int RING_BYTES = 16 * RING_D_ * 512;
+    static constexpr int STAGES_BYTES = NSTAGE_ * 2 * 64 * 128;
+};
+using MmCfgSparse = MmCfg<3, SP_ENT_MAX, 4>;
+using MmCfgDense = MmCfg<7, SP_ENT_MAX_SMALL, 2>;
 constexpr int MM_CT_RING = 4;                         // ring of column T values (128 x int32 per SCP)
 constexpr int MM_CNT_PITCH = 272;                     // bytes per row of the sparse counters (128 x uint16 + pad: conflict-free LDS.128)
 constexpr int MM_CNT_QUAD = 32 * MM_CNT_PITCH;        // 8704 B per lane quadrant (32 rows)
@@ -58,8 +70,9 @@ constexpr int MM_SMEM_CNT = 4 * MM_CNT_QUAD;              // 34816 >= 128*33*8 =
 static_assert(MM_SMEM_CNT >= MM_ROWS * MM_STG_PITCH * 8, "output staging does not fit the patch-counter area");
 constexpr int MM_SMEM_RCP = SMEM_RCP;                   // RN(1/den) per denominator
 constexpr int MM_SMEM_KP = 1024;                        // kpad[p] of every SCP (P <= 255)
-constexpr int MM_SMEM_TOTAL = MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP + MM_SMEM_CNT + MM_NSTAGE * MM_STAGE_BYTES + SP_STAGE_BYTES;
-static_assert(MM_SMEM_TOTAL <= SMEM_TOTAL, "K5 shared memory");
+constexpr int MM_SMEM_FIXED = MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP + MM_SMEM_CNT;
+template <class Cfg> constexpr int mm_smem_total() { return MM_SMEM_FIXED + Cfg::STAGES_BYTES + Cfg::RING_BYTES + Cfg::DICT_BYTES; }
+static_assert(mm_smem_total<MmCfgSparse>() <= SMEM_TOTAL && mm_smem_total<MmCfgDense>() <= SMEM_TOTAL, "K5 shared memory");
 constexpr int MM_TMEM_COLS = 512;                     // 2 accumulator buffers x 128 columns (s32) + 256 columns of fp64 sums S
 constexpr int MM_TMEM_S = 256;                        // first column of S: thread (lane, column group cg) owns columns S + 64 cg .. + 63
 constexpr uint16_t MM_NOT_DENSE = 0xffffu;
@@ -192,8 +205,28 @@ __device__ __forceinline__ void sp_lookup(uint32_t dict32, uint32_t cq32, uint32
     }
 }
 
-template <int DUMMY = 0>
+// row items travel global -> shared memory by cp.async (LDGSTS), 16 bytes per lane and chunk, into a ring private to the warp:
+// RING_D chunks are in flight per warp without holding registers, and the first chunks of SCP p+1 are requested before the
+// epilogue of SCP p starts.  Every step commits exactly one group (possibly empty), so "at most RING_D - 1 groups pending"
+// means the oldest chunk has landed.
+__device__ __forceinline__ void cp_async16(uint32_t dst32, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst32), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// requests this warp's first RING_D chunks (cg, cg + 4, ...) of a slab of nch chunks
+template <int RING_D>
+__device__ __forceinline__ void sp_prefetch(uint32_t ring32, const uint4 *slab, int nch, int cg) {
+#pragma unroll
+    for (int d = 0; d < RING_D; d++) {
+        if (cg + 4 * d < nch) cp_async16(ring32 + d * 512, slab + (int64_t)(cg + 4 * d) * 32);
+        cp_async_commit();
+    }
+}
+
+template <class Cfg>
 __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams prm) {
+    constexpr int MM_NSTAGE = Cfg::NSTAGE, RING_D = Cfg::RING_D;
     extern __shared__ __align__(128) unsigned char smem[];
     uint64_t *full = reinterpret_cast<uint64_t *>(smem);                  // [NSTAGE]
     uint64_t *empty = full + MM_NSTAGE;                                   // [NSTAGE]
@@ -203,15 +236,16 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
     uint64_t *ct_empty = ct_full + MM_CT_RING;                            // [CT_RING]
     uint64_t *dict_full = ct_empty + MM_CT_RING;                          // the sparse dictionary stage
     uint64_t *dict_empty = dict_full + 1;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + 192);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + 240);
     int32_t *col_g = reinterpret_cast<int32_t *>(smem + 256);             // [128] genome id of the tile's columns (output phase)
     int32_t *ctring = reinterpret_cast<int32_t *>(smem + MM_SMEM_MISC);   // [CT_RING][128]
     double *rcp = reinterpret_cast<double *>(smem + MM_SMEM_MISC + MM_SMEM_CT);
     int32_t *kp_s = reinterpret_cast<int32_t *>(smem + MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP);   // [P] kpad
     unsigned char *cnt_mem = smem + MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP;
     unsigned char *stage_mem = cnt_mem + MM_SMEM_CNT;
-    unsigned char *dict_mem = stage_mem + MM_NSTAGE * MM_STAGE_BYTES;
-    static_assert((2 * MM_NSTAGE + 4 + 2 * MM_CT_RING + 2) * 8 <= 192 && 256 + MM_COLS * 4 <= MM_SMEM_MISC, "misc area");
+    unsigned char *ring_mem = stage_mem + Cfg::STAGES_BYTES;               // [16 warps][RING_D][32 lanes x 16 B]
+    unsigned char *dict_mem = ring_mem + Cfg::RING_BYTES;
+    static_assert((2 * MM_NSTAGE + 4 + 2 * MM_CT_RING + 2) * 8 <= 240 && 256 + MM_COLS * 4 <= MM_SMEM_MISC, "misc area");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int P = prm.P;
@@ -321,6 +355,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
         const uint32_t cq32 = smem_u32(cnt_mem + q * MM_CNT_QUAD);      // the quadrant's 32 x 128 sparse counters (uint16)
         const uint32_t cw32 = cq32 + lane * MM_CNT_PITCH + cg * 64;     // this thread's 32 counters
         const uint32_t dict32 = smem_u32(dict_mem);
+        const uint32_t ring32 = smem_u32(ring_mem + warp * (RING_D * 512) + lane * 16);   // this lane's 16 bytes of ring slot 0
         const uint32_t rcp32 = smem_u32(rcp);
         const bool sparse = prm.has_sparse != 0;
         uint32_t ai = 0, ci = 0, di = 0;
@@ -364,6 +399,8 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
             int64_t so0 = 0, so1 = 0;
             int ns = 0;
             if (sparse) { so0 = __ldg(prm.sp_off + gp0); so1 = __ldg(prm.sp_off + gp0 + 1); ns = __ldg(prm.sp_nsub + jp0); }
+            const uint4 *items = reinterpret_cast<const uint4 *>(prm.sp_items) + lane;
+            if (ns > 0) sp_prefetch<RING_D>(ring32, items + so0 * 32, (int)(so1 - so0), cg);   // SCP 0 (later SCPs: one SCP ahead)
 
             for (int p = 0; p < P; p++) {
                 int ta_nxt = 0; bool fast_nxt = false; int64_t so2 = 0; int ns_nxt = 0;
@@ -376,24 +413,32 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                 // ---- sparse walk: the quadrant's row items of this SCP through every part of the column block's dictionary ----
                 const bool np = ns > 0;                    // the same for the 4 warps of the quadrant (and for the whole CTA)
                 if (np) {
-                    const uint4 *slab = reinterpret_cast<const uint4 *>(prm.sp_items) + so0 * 32 + lane;
+                    const uint4 *slab = items + so0 * 32;
                     const int nch = (int)(so1 - so0);
                     for (int k = 0; k < ns; k++) {
-                        uint4 it = make_uint4(0u, 0u, 0u, 0u);
-                        if (cg < nch) it = __ldg(slab + (int64_t)cg * 32);                       // in flight while we wait for the dictionary
+                        if (k > 0) sp_prefetch<RING_D>(ring32, slab, nch, cg);                   // further dictionary parts re-stream the items
                         mbar_wait(dict_full, di & 1u);
                         di++;
+                        int slot = 0;
                         for (int ch = cg; ch < nch; ch += 4) {
-                            const uint4 cur = it;
-                            if (ch + 4 < nch) it = __ldg(slab + (int64_t)(ch + 4) * 32);
+                            cp_async_wait<RING_D - 1>();                                         // the oldest chunk in flight has landed
+                            uint4 cur;
+                            const uint32_t a = ring32 + slot * 512;
+                            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(cur.x), "=r"(cur.y), "=r"(cur.z), "=r"(cur.w) : "r"(a) : "memory");
                             sp_lookup(dict32, cq32, cur.x); sp_lookup(dict32, cq32, cur.y);
                             sp_lookup(dict32, cq32, cur.z); sp_lookup(dict32, cq32, cur.w);
+                            if (ch + 4 * RING_D < nch) cp_async16(a, slab + (int64_t)(ch + 4 * RING_D) * 32);   // refill the slot just read
+                            cp_async_commit();
+                            slot = (slot + 1 == RING_D) ? 0 : slot + 1;
                         }
+                        cp_async_wait<0>();
                         __syncwarp();
                         if (lane == 0) mbar_arrive(dict_empty);
                     }
                     asm volatile("bar.sync %0, 128;" ::"r"(2 + q) : "memory");                   // the quadrant's counters are complete
                 }
+                // the first chunks of the next SCP's items travel while this SCP's epilogue runs
+                if (ns_nxt > 0) sp_prefetch<RING_D>(ring32, items + so1 * 32, (int)(so2 - so1), cg);
                 // ---- column T values ----
                 const uint32_t cs = ci % MM_CT_RING;
                 mbar_wait(&ct_full[cs], (ci / MM_CT_RING) & 1u);

@@ -915,6 +915,7 @@ struct MmaPlan {
     int64_t sparse_est = 0;               // postings on non-dense tetramers (estimate)
     int64_t sparse_items = 0;
     bool has_sparse = false;
+    bool small_dict = false;              // MmCfgDense: few non-dense tetramers per (column block, SCP) -> small dictionary stage, deep operand ring
     double t_mma = 0, t_lists = 0;        // cost-model seconds
     std::vector<unsigned long long> hist; // [0..HMAX] lists per length (sample units when !exact), [HMAX+1] = sum n(n-1)/2
     int stride = 1;
@@ -947,19 +948,26 @@ static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl) {
 
 // The decision rule between the two tile paths (north_star: dense contraction only where the per-SCP tetramer density makes it
 // the denser one).  Inputs: the posting-list length histogram, the number of matrix cells this context computes, |F|.
-// Constants are measured rates of this repository's kernels on B200: the list path performs
-// cells * (|F|/G) / 64 dictionary lookups at 8.2e11/s.  The hybrid path streams K_sum bytes of each operand per cell row/column
-// through the tensor cores (L2-bound: 7.6e14 multiply-accumulates/s) and, concurrently on the other warps, walks the rows'
-// non-dense postings through one sparse dictionary per 128 columns (cells/128 * non-dense postings per genome lookups at
-// PF_WALK_S seconds each) and runs the fp64 epilogue (5.4e-13 s per (cell, SCP)); tau moves tetramers between the two sides.
+// Constants are measured rates of this repository's kernels on B200:
+//   list path    cells * (|F|/G) / 64 dictionary lookups at 8.2e11/s;
+//   hybrid path  per (128 x 128 tile, SCP) three things run concurrently on one SM -- (a) the operand stream of the contraction,
+//                256 bytes per dense tetramer through a bulk-copy ring whose round trip is ~6,400 cycles (17.5 B/cycle with the
+//                112 KB ring of the dense plan, 7.5 B/cycle with the 48 KB ring of the sparse plan); (b) the sparse walk,
+//                rows' non-dense postings / 128 columns lookups at PF_WALK_S seconds each (whole GPU); (c) the fp64 epilogue,
+//                PF_EPI_S seconds per (cell, SCP).  (b) and (c) share the same warps, (a) overlaps them.
+// tau moves tetramers between (a) and (b).
 #ifndef PF_WALK_S
-#define PF_WALK_S 7.0e-13
+#define PF_WALK_S 7.5e-13
+#endif
+#ifndef PF_EPI_S
+#define PF_EPI_S 1.4e-12
 #endif
 static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_blocks, bool force) {
     static const uint32_t cand[] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048, 3072, 4096};
     const int P = c->P, G = c->G;
     const double s = (double)pl.stride, nF = (double)c->nF;
     pl.t_lists = cells * (nF / std::max(1, G)) / 64.0 / 8.2e11 + nF * 1.4e-11;
+    const double sm_hz = 1.9e9 * c->sm_count;
     double best = 1e300;
     for (uint32_t tau : cand) {
         if (c->tau_pref > 0 && tau != cand[0]) break;
@@ -971,8 +979,10 @@ static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_bloc
         const double k_sum = K + 16.0 * P;                                          // padding to 32 per SCP, on average
         const double img_bytes = (double)img_blocks * 128.0 * k_sum;
         if (c->tau_pref == 0 && img_bytes > 48e9) continue;
+        const bool small_dict = 2.0 * sparse_post * SP_COLS / ((double)std::max(1, G) * P) + 64.0 < (double)SP_ENT_MAX_SMALL;
+        const double t_op = cells / 16384.0 * 256.0 * k_sum / ((small_dict ? 17.5 : 7.5) * sm_hz);
         const double lookups = cells / 128.0 * sparse_post / std::max(1, G);
-        const double t = std::max(k_sum * cells / 7.6e14, cells * P * 5.4e-13 + lookups * PF_WALK_S) + img_bytes / 3e12 + sparse_post * 2e-11;
+        const double t = std::max(t_op, cells * P * PF_EPI_S + lookups * PF_WALK_S) + img_bytes / 3e12 + sparse_post * 4e-11;
         if (t < best) { best = t; pl.tau = tau; pl.k_sum = (int64_t)k_sum; pl.sparse_est = (int64_t)sparse_post; }
     }
     pl.t_mma = best + nF * 2e-11;
@@ -1048,6 +1058,7 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
     double e_sparse = 0;
     for (uint32_t L = 1; L < std::min<uint32_t>(pl.tau, MM_HMAX); L++) e_sparse += (double)pl.hist[L] * L;   // non-dense postings
     pl.has_sparse = false; pl.sparse_items = 0;
+    pl.small_dict = 2.0 * e_sparse * SP_COLS / ((double)std::max(1, G) * P) + 64.0 < (double)SP_ENT_MAX_SMALL;
     if (e_sparse > 0 && nrb > 0 && ncb > 0) {
         const int64_t n_gp = (int64_t)nrb * 4 * P;                   // (32-row group, SCP) slabs; groups beyond the last row stay empty
         PF_TRY(ensure(c, c->sp_cnt, sizeof(int32_t) * (size_t)n_gp * SP_ROWS));
@@ -1089,7 +1100,7 @@ static int mma_prepare(Ctx *c, const ModePlan &m, MmaPlan &pl, int n_rows, int n
             PF_CUDA(c, cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), c->stream));
             SpDictParams q;
             q.seg_off = ptr<int64_t>(c->seg_off); q.vals = ptr<uint32_t>(c->vals); q.cols = ptr<int32_t>(c->cols); q.n_cols = n_cols; q.P = P;
-            q.did = ptr<uint16_t>(c->mm_did); q.blob = ptr<unsigned char>(c->sp_blob); q.blob_cap = (unsigned long long)c->sp_blob.cap;
+            q.did = ptr<uint16_t>(c->mm_did); q.ent_max = pl.small_dict ? SP_ENT_MAX_SMALL : SP_ENT_MAX; q.blob = ptr<unsigned char>(c->sp_blob); q.blob_cap = (unsigned long long)c->sp_blob.cap;
             q.cursor = cursor; q.nsub = ptr<int32_t>(c->sp_nsub); q.sub = ptr<SpSub>(c->sp_sub); q.err = sp_err;
             kern<<<(unsigned)n_dict, SD_THREADS, SD_SMEM, c->stream>>>(q);
             PF_LAUNCH_CHECK(c);
@@ -1334,9 +1345,16 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         mp.tiles = ptr<int4>(c->tiles); mp.n_tiles = (int)tiles.size();
         PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
         if (!tiles.empty()) {
-            auto kern = aji_mma_kernel<0>;
-            PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MM_SMEM_TOTAL));
-            kern<<<(unsigned)std::min<int>((int)tiles.size(), c->sm_count), MM_THREADS, MM_SMEM_TOTAL, c->stream>>>(mp);
+            const unsigned grid = (unsigned)std::min<int>((int)tiles.size(), c->sm_count);
+            if (pl.small_dict) {
+                auto kern = aji_mma_kernel<MmCfgDense>;
+                PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mm_smem_total<MmCfgDense>()));
+                kern<<<grid, MM_THREADS, mm_smem_total<MmCfgDense>(), c->stream>>>(mp);
+            } else {
+                auto kern = aji_mma_kernel<MmCfgSparse>;
+                PF_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mm_smem_total<MmCfgSparse>()));
+                kern<<<grid, MM_THREADS, mm_smem_total<MmCfgSparse>(), c->stream>>>(mp);
+            }
             PF_LAUNCH_CHECK(c);
         }
     } else if (c->partitioned && c->exch_event && n_late > 0) {

@@ -24,13 +24,17 @@ constexpr int SP_BM_WORDS = NTETRA / 32;                      // 5000 presence w
 constexpr int SP_BM_BYTES = (SP_BM_WORDS + 4) * 4;            // 20016: + 4 always-zero words (padding items land there)
 constexpr int SP_RK_BYTES = (((SP_BM_WORDS + 4) * 2) + 15) & ~15;   // 10016: uint16 rank of every bitmap word
 constexpr int SP_ENT_OFF = SP_BM_BYTES + SP_RK_BYTES;         // 30032: first entry (slot 0 is never addressed: ranks start at 1)
-constexpr int SP_ENT_MAX = 32766;                             // entries + list slots per blob (15-bit list offsets, 0x7fff reserved)
-constexpr int SP_STAGE_BYTES = SP_ENT_OFF + 2 * (SP_ENT_MAX + 2);   // 95568 (multiple of 16): shared-memory size of the dictionary stage
+// entries + list slots per blob (15-bit list offsets, 0x7fff reserved).  Two stage sizes, chosen per compute call by the expected
+// number of non-dense tetramers per (column block, SCP): the tile kernel gives the rest of its shared memory to the operand ring.
+constexpr int SP_ENT_MAX = 32590;                             // sparse inputs: one 93 KB dictionary stage
+constexpr int SP_ENT_MAX_SMALL = 4990;                        // dense inputs: a 39 KB stage
+__host__ __device__ constexpr int sp_stage_bytes(int ent_max) { return SP_ENT_OFF + 2 * (ent_max + 2); }
+constexpr int SP_STAGE_BYTES = sp_stage_bytes(SP_ENT_MAX);    // 95216
 constexpr int SP_MAXSUB = 8;                                  // column sub-dictionaries per (block, SCP)
 constexpr int SP_CHUNK = 128;                                 // items per chunk (32 lanes x uint4)
 constexpr uint32_t SP_PAD_ITEM = (uint32_t)(SP_BM_WORDS * 4) << 16;   // byte offset 20000 = first always-zero word
 constexpr uint16_t SP_NOT_DENSE = 0xffffu;                    // == MM_NOT_DENSE (dense-id table of mma_index.cuh)
-static_assert(SP_STAGE_BYTES % 16 == 0 && SP_ENT_OFF % 16 == 0, "bulk-copy granularity");
+static_assert(SP_STAGE_BYTES % 16 == 0 && sp_stage_bytes(SP_ENT_MAX_SMALL) % 16 == 0 && SP_ENT_OFF % 16 == 0, "bulk-copy granularity");
 
 // item of (row r of its group, tetramer v): the kernel loads the bitmap word at byte offset item >> 16, shifts it left by
 // item & 31 (presence bit -> bit 31, presence bits of smaller tetramers below it) and takes the row from bits 8..12
@@ -119,6 +123,7 @@ struct SpDictParams {
     const int64_t *seg_off; const uint32_t *vals;
     const int32_t *cols; int n_cols, P;
     const uint16_t *did;
+    int ent_max;          // SP_ENT_MAX or SP_ENT_MAX_SMALL: capacity of the tile kernel's dictionary stage
     unsigned char *blob; unsigned long long blob_cap; unsigned long long *cursor;   // bump allocation; the cursor keeps counting beyond the capacity
     int32_t *nsub;        // [ncb * P]
     SpSub *sub;           // [ncb * P * SP_MAXSUB]
@@ -186,7 +191,7 @@ __device__ __forceinline__ bool sd_build(const SpDictParams &prm, const SdSmem &
     for (int i = w0; i < w1; i++) sum += __popc(s.W[i]);
     uint32_t n;
     uint32_t run = sd_block_scan(s, sum, &n);
-    if (n + 1 > (uint32_t)SP_ENT_MAX) return false;
+    if (n + 1 > (uint32_t)prm.ent_max) return false;
     for (int i = w0; i < w1; i++) { s.rk[i] = (uint16_t)run; run += __popc(s.W[i]); }
     for (int i = SP_BM_WORDS + tid; i < SP_BM_WORDS + 4; i += SD_THREADS) s.rk[i] = 0;
     // multiplicities (number of columns that hold the tetramer) in the entry slots
@@ -204,7 +209,7 @@ __device__ __forceinline__ bool sd_build(const SpDictParams &prm, const SdSmem &
     uint32_t n_list;
     uint32_t at = n + 1 + sd_block_scan(s, need, &n_list);
     const uint32_t n_ent = n + 1 + n_list;
-    if (n_ent > (uint32_t)SP_ENT_MAX) return false;
+    if (n_ent > (uint32_t)prm.ent_max) return false;
     for (uint32_t i = i0; i < i1; i++) {
         const uint32_t m = s.ent[i];
         if (m >= 2u) { s.ent[i] = (uint16_t)(0x8000u | at); s.ent[at] = 0; at += m + 1u; }   // [at] = fill cursor, ends as the count
