@@ -224,6 +224,14 @@ __device__ __forceinline__ void sp_prefetch(uint32_t ring32, const uint4 *slab, 
     }
 }
 
+// One bulk copy moves its bytes at only a few bytes per cycle (a single copy keeps little in flight; measured on B200: a ring of
+// eight 16 KB copies sustained 20 B/cycle per SM, i.e. ~2.5 B/cycle per copy), so large transfers are issued as many small
+// copies that complete on the same mbarrier: their latencies overlap.
+constexpr uint32_t MM_PIECE = 2048;
+__device__ __forceinline__ void bulk_g2s_split(unsigned char *dst, const unsigned char *src, uint32_t bytes, uint64_t *bar) {
+    for (uint32_t o = 0; o < bytes; o += MM_PIECE) bulk_g2s(dst + o, src + o, min(MM_PIECE, bytes - o), bar);
+}
+
 template <class Cfg>
 __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams prm) {
     constexpr int MM_NSTAGE = Cfg::NSTAGE, RING_D = Cfg::RING_D;
@@ -290,8 +298,8 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                         mbar_wait(&empty[s], ph ^ 1u);
                         mbar_expect_tx(&full[s], 2u * bytes);
                         unsigned char *dst = stage_mem + (size_t)s * MM_STAGE_BYTES;
-                        bulk_g2s(dst, a_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
-                        bulk_g2s(dst + MM_OP_BYTES, b_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
+                        bulk_g2s_split(dst, a_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
+                        bulk_g2s_split(dst + MM_OP_BYTES, b_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
                         it++;
                     }
                 }
@@ -340,7 +348,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                         const int64_t off = (int64_t)(((uint64_t)d.y << 32) | d.x);
                         mbar_wait(dict_empty, (di & 1u) ^ 1u);              // every walker warp is done with the previous dictionary
                         mbar_expect_tx(dict_full, d.z);
-                        bulk_g2s(dict_mem, prm.sp_blob + off, d.z, dict_full);
+                        bulk_g2s_split(dict_mem, prm.sp_blob + off, d.z, dict_full);
                         di++;
                     }
                 }

@@ -66,6 +66,8 @@ struct TileParams {
     int n_tiles2;
     int *tile_counter2;
     uint32_t k27, k16;         // 2^27, 2^16 (PF_IMAD_HI: shift-by-multiply constants)
+    uint32_t piece;            // a stage blob travels as bulk copies of this many bytes (multiple of 16), all completing on the stage's
+                               // mbarrier: one copy keeps only a few bytes per cycle in flight, many overlap their latencies
 };
 
 // ---- PTX wrappers: mbarrier + bulk async copy (TMA) ----
@@ -237,7 +239,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
         const uint32_t extra = st_first(st.w) ? COLS_PER_TILE * 4u : 0u;
         const int64_t off = (int64_t)(((uint64_t)st.y << 32) | st.x);
         mbar_expect_tx(&full[slot], st.z + extra);
-        bulk_g2s(stage_mem + (size_t)slot * STAGE_BYTES, prm.blob + off, st.z, &full[slot]);
+        for (uint32_t o = 0; o < st.z; o += prm.piece)
+            bulk_g2s(stage_mem + (size_t)slot * STAGE_BYTES + o, prm.blob + off + o, min(prm.piece, st.z - o), &full[slot]);
         if (extra)
             bulk_g2s(colT + (st_p(st.w) & 3) * COLS_PER_TILE, prm.colT + ((int64_t)cslot * P + st_p(st.w)) * COLS_PER_TILE, extra,
                      &full[slot]);

@@ -962,6 +962,9 @@ static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl) {
 #ifndef PF_EPI_S
 #define PF_EPI_S 1.4e-12
 #endif
+#ifndef PF_INC_S
+#define PF_INC_S 1.2e-12      // one counter increment of the walk (a hit; tetramers held by several columns of a block loop over them)
+#endif
 static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_blocks, bool force) {
     static const uint32_t cand[] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048, 3072, 4096};
     const int P = c->P, G = c->G;
@@ -973,8 +976,9 @@ static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_bloc
         if (c->tau_pref > 0 && tau != cand[0]) break;
         if (c->tau_pref > 0) tau = (uint32_t)std::min(c->tau_pref, MM_HMAX);   // lists of >= MM_HMAX genomes are always dense
         const uint32_t m0 = (uint32_t)std::max(1.0, std::ceil((double)tau / s));   // sample count at which a list is called dense
-        double K = 0, dense_post = 0;
+        double K = 0, dense_post = 0, e_sparse = 0;
         for (uint32_t m = m0; m <= (uint32_t)MM_HMAX; m++) { K += (double)pl.hist[m]; dense_post += (double)pl.hist[m] * m * s; }
+        for (uint32_t m = 2; m < std::min<uint32_t>(m0, MM_HMAX); m++) e_sparse += (double)pl.hist[m] * 0.5 * (m * s) * (m * s);   // pair increments
         const double sparse_post = std::max(0.0, nF - dense_post);                  // includes the lists the sample never saw
         const double k_sum = K + 16.0 * P;                                          // padding to 32 per SCP, on average
         const double img_bytes = (double)img_blocks * 128.0 * k_sum;
@@ -982,7 +986,8 @@ static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_bloc
         const bool small_dict = 2.0 * sparse_post * SP_COLS / ((double)std::max(1, G) * P) + 64.0 < (double)SP_ENT_MAX_SMALL;
         const double t_op = cells / 16384.0 * 256.0 * k_sum / ((small_dict ? 17.5 : 7.5) * sm_hz);
         const double lookups = cells / 128.0 * sparse_post / std::max(1, G);
-        const double t = std::max(t_op, cells * P * PF_EPI_S + lookups * PF_WALK_S) + img_bytes / 3e12 + sparse_post * 4e-11;
+        const double incs = e_sparse * std::min(1.0, cells / std::max(1.0, 0.5 * (double)G * ((double)G - 1.0)));
+        const double t = std::max(t_op, cells * P * PF_EPI_S + lookups * PF_WALK_S + incs * PF_INC_S) + img_bytes / 3e12 + sparse_post * 4e-11;
         if (t < best) { best = t; pl.tau = tau; pl.k_sum = (int64_t)k_sum; pl.sparse_est = (int64_t)sparse_post; }
     }
     pl.t_mma = best + nF * 2e-11;
@@ -1310,6 +1315,10 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
     prm.out = direct_dev ? direct_dev : ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !compact) ? 1 : 0;
     prm.k27 = 1u << 27; prm.k16 = 1u << 16;
+    {   // PFAAI_TILE_PIECE: bytes per bulk copy of a dictionary stage (A/B switch; 0 = the whole blob in one copy)
+        static const uint32_t piece = [] { const char *e = getenv("PFAAI_TILE_PIECE"); const long v = e ? atol(e) : 4096; return (uint32_t)(v <= 0 ? (1 << 30) : ((v + 15) & ~15l)); }();
+        prm.piece = piece;
+    }
     prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
     prm.N_out = want_sn ? ptr<int32_t>(c->N_out) : nullptr;
     prm.counts_out = want_counts ? ptr<int32_t>(c->counts_out) : nullptr;
