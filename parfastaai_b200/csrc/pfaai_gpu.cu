@@ -953,17 +953,19 @@ static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl) {
 //   hybrid path  per (128 x 128 tile, SCP) three things run concurrently on one SM -- (a) the operand stream of the contraction,
 //                256 bytes per dense tetramer through a bulk-copy ring whose round trip is ~6,400 cycles (17.5 B/cycle with the
 //                112 KB ring of the dense plan, 7.5 B/cycle with the 48 KB ring of the sparse plan); (b) the sparse walk,
-//                rows' non-dense postings / 128 columns lookups at PF_WALK_S seconds each (whole GPU); (c) the fp64 epilogue,
-//                PF_EPI_S seconds per (cell, SCP).  (b) and (c) share the same warps, (a) overlaps them.
+//                rows' non-dense postings / 128 columns lookups at PF_WALK_S seconds each (whole GPU) plus PF_INC_S per counter
+//                increment (= co-occurrence on a non-dense tetramer: shared-memory atomics, 2 cycles per lane); (c) the fp64
+//                epilogue, PF_EPI_S seconds per (cell, SCP).  (b) and (c) share the same warps, (a) overlaps them.
 // tau moves tetramers between (a) and (b).
 #ifndef PF_WALK_S
-#define PF_WALK_S 7.5e-13
+#define PF_WALK_S 2.1e-12     // one lookup of the walk: 0.6 SM-cycles (measured, profiles/r2n_*), 148 SMs at 1.9 GHz
 #endif
 #ifndef PF_EPI_S
 #define PF_EPI_S 1.4e-12
 #endif
 #ifndef PF_INC_S
-#define PF_INC_S 1.2e-12      // one counter increment of the walk (a hit; tetramers held by several columns of a block loop over them)
+#define PF_INC_S 7.1e-12      // one counter increment of the walk: a shared-memory atomic costs 2 SM-cycles per lane (measured; the reason
+                              // the sparse synthetic family, ~1 non-dense co-occurrence per (pair, SCP), stays on the list path)
 #endif
 static void mma_choose(const Ctx *c, MmaPlan &pl, double cells, int64_t img_blocks, bool force) {
     static const uint32_t cand[] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048, 3072, 4096};
@@ -1315,8 +1317,9 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
     prm.out = direct_dev ? direct_dev : ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !compact) ? 1 : 0;
     prm.k27 = 1u << 27; prm.k16 = 1u << 16;
-    {   // PFAAI_TILE_PIECE: bytes per bulk copy of a dictionary stage (A/B switch; 0 = the whole blob in one copy)
-        static const uint32_t piece = [] { const char *e = getenv("PFAAI_TILE_PIECE"); const long v = e ? atol(e) : 4096; return (uint32_t)(v <= 0 ? (1 << 30) : ((v + 15) & ~15l)); }();
+    {   // PFAAI_TILE_PIECE: bytes per bulk copy of a dictionary stage (A/B switch; default 0 = the whole blob in one copy.
+        // Measured at config 4: 38.2 ms whole, 41.5 ms in 4 KB pieces, 49.5 ms in 1 KB pieces -- rejected, profiles/r2n_*)
+        static const uint32_t piece = [] { const char *e = getenv("PFAAI_TILE_PIECE"); const long v = e ? atol(e) : 0; return (uint32_t)(v <= 0 ? (1 << 30) : ((v + 15) & ~15l)); }();
         prm.piece = piece;
     }
     prm.S_out = want_sn ? ptr<double>(c->S_out) : nullptr;
