@@ -141,6 +141,13 @@ int  pfaai_gpu_upload_index(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes,
  * PFAAI_ERR_CONSTRUCT. */
 int  pfaai_gpu_upload_triples(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes, const int32_t *tetramer,
                               const pfaai_pg_t *F, int64_t nF, const int32_t *T_or_null);
+/* Device-ready hand-over (the index cache's fast path): the genome-major lists that pfaai_gpu_build
+ * produces -- seg_off [P*G + 1] (64-bit offsets of segment g*P + p) and seg_vals [nF] (tetramers, ascending inside a segment),
+ * exactly what pfaai_gpu_get_arrays returns -- plus Lc and T (NULL: T = segment lengths).  No F is uploaded (half the bytes),
+ * no K1-K3, no sort: the context is "built" when the call returns, after one validation pass over the lists (offsets, order and
+ * range of the tetramers; PFAAI_ERR_CONSTRUCT on a violation).  Serves every compute mode of an unpartitioned context. */
+int  pfaai_gpu_import_lists(pfaai_gpu_ctx *ctx, int n_proteins, int n_genomes, int64_t nF, const int32_t *Lc,
+                            const int32_t *T_or_null, const int64_t *seg_off, const uint32_t *seg_vals);
 /* The same for a caller that fills the index itself on the device (e.g. a broadcast / all-gather over NVLink from
  * the rank that read the database): sizes the context's F [nF], Lc [160000] and T [P x G] buffers and returns their
  * device pointers; the caller writes them on the context's stream (or synchronises) before pfaai_gpu_build().

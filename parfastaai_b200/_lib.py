@@ -32,7 +32,7 @@ EXPORTS = [
     "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
     "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
     "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench", "pfaai_gpu_set_path", "pfaai_gpu_e_size",
-    "pfaai_gpu_host_register", "pfaai_gpu_host_unregister", "pfaai_gpu_upload_triples",
+    "pfaai_gpu_host_register", "pfaai_gpu_host_unregister", "pfaai_gpu_upload_triples", "pfaai_gpu_import_lists",
 ]
 
 
@@ -85,6 +85,7 @@ def load():
     L.pfaai_gpu_set_shard.argtypes = [vp, i32, i32]
     L.pfaai_gpu_upload_index.argtypes = [vp, i32, i32, vp, vp, i64, vp]
     L.pfaai_gpu_upload_triples.argtypes = [vp, i32, i32, vp, vp, i64, vp]
+    L.pfaai_gpu_import_lists.argtypes = [vp, i32, i32, i64, vp, vp, vp, vp]
     L.pfaai_gpu_build.argtypes = [vp]
     L.pfaai_gpu_get_arrays.argtypes = [vp, vp, vp, vp, vp, vp]
     L.pfaai_gpu_compute_device.argtypes = [vp, i32, vp, i32, u32]
@@ -209,6 +210,18 @@ class PfaaiGpu:
             T = np.ascontiguousarray(T, dtype=np.int32)
         self.P, self.G, self.nF = P, G, F.shape[0]
         self._check(self._L.pfaai_gpu_upload_triples(self._h, P, G, _p(tetramer), _p(F), F.shape[0], _p(T)), "upload_triples")
+
+    def import_lists(self, P, G, Lc, seg_off, seg_vals, T=None):
+        """Device-ready hand-over (pfaai_gpu_import_lists): the genome-major lists of get_arrays(); no F, no build."""
+        Lc = np.ascontiguousarray(Lc, dtype=np.int32)
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+        seg_vals = np.ascontiguousarray(seg_vals).view(np.uint32) if seg_vals.dtype.itemsize == 4 else np.ascontiguousarray(seg_vals, dtype=np.uint32)
+        if T is not None:
+            T = np.ascontiguousarray(T, dtype=np.int32)
+        if seg_off.shape[0] != P * G + 1:
+            raise ValueError("seg_off must have P*G + 1 entries")
+        self.P, self.G, self.nF = P, G, int(seg_vals.shape[0])
+        self._check(self._L.pfaai_gpu_import_lists(self._h, P, G, self.nF, _p(Lc), _p(T), _p(seg_off), _p(seg_vals)), "import_lists")
 
     def index_device_buffers(self, P, G, nF, host_T=False):
         """Size the device index buffers and return their pointers (F, Lc, T) for a caller-side fill (NCCL broadcast)."""

@@ -520,4 +520,37 @@ __global__ void __launch_bounds__(256) k_lc_run_ends(const int32_t *__restrict__
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Import of device-ready lists (pfaai_gpu_import_lists: the index cache's fast path): validates what K1-K3 + the sort would
+// have guaranteed -- offsets ascending from 0 to nF, tetramers strictly ascending inside a segment and below NTETRA, T(p, g)
+// == the segment's length unless the caller supplies its own T -- and returns the longest segment.  One pass, HBM-bound.
+// flags[0] = 1 on a violation, flags[1] = max segment length (atomicMax).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_check_lists(const int64_t *__restrict__ seg_off, const uint32_t *__restrict__ vals, int64_t nseg,
+                                                      int64_t nF, int *__restrict__ flags) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    int mx = 0;
+    bool bad = false;
+    for (int64_t sg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; sg < nseg; sg += nwarp) {
+        const int64_t b = seg_off[sg], e = seg_off[sg + 1];
+        if (b < 0 || e < b || e > nF || e - b > (1 << 20) || (sg == 0 && b != 0) || (sg == nseg - 1 && e != nF)) { bad = true; continue; }
+        mx = max(mx, (int)(e - b));
+        for (int64_t k = b + lane; k < e; k += 32) {
+            const uint32_t v = vals[k];
+            if (v >= (uint32_t)NTETRA || (k > b && vals[k - 1] >= v)) bad = true;
+        }
+    }
+    if (bad) flags[0] = 1;
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0 && mx > 0) atomicMax(flags + 1, mx);
+}
+// T[p][g] = length of segment (g, p)
+__global__ void k_t_from_offsets(const int64_t *__restrict__ seg_off, int P, int G, int32_t *__restrict__ T) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)P * G) return;
+    const int g = (int)(i / P), p = (int)(i % P);
+    T[(int64_t)p * G + g] = (int32_t)(seg_off[i + 1] - seg_off[i]);
+}
+
 }  // namespace pfaai

@@ -429,6 +429,51 @@ int pfaai_gpu_upload_triples(pfaai_gpu_ctx *h, int P, int G, const int32_t *tetr
     return PFAAI_OK;
 }
 
+int pfaai_gpu_import_lists(pfaai_gpu_ctx *h, int P, int G, int64_t nF, const int32_t *Lc, const int32_t *T, const int64_t *seg_off,
+                           const uint32_t *seg_vals) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    if (P <= 0 || G <= 0 || nF < 0 || !Lc || !seg_off || (nF > 0 && !seg_vals)) { set_error(c, "import_lists: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
+    if ((int64_t)P * G >= (1ll << 31)) { set_error(c, "import_lists: P*G too large"); return PFAAI_ERR_CONSTRUCT; }
+    PF_CUDA(c, cudaSetDevice(c->device));
+    const int64_t nseg = (int64_t)P * G;
+    c->P = P; c->G = G; c->nF = nF; c->nF_owned = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false;
+    c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr; c->e_size = -1; c->launches = 0;
+    PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
+    PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
+    PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)nseg));
+    PF_TRY(ensure(c, c->seg_off, sizeof(int64_t) * (size_t)(nseg + 1)));
+    PF_TRY(ensure(c, c->vals, sizeof(uint32_t) * (size_t)std::max<int64_t>(nF, 1)));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D0], c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(c->Lc.p, Lc, sizeof(int32_t) * NTETRA, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaMemcpyAsync(c->seg_off.p, seg_off, sizeof(int64_t) * (size_t)(nseg + 1), cudaMemcpyHostToDevice, c->stream));
+    if (nF > 0) PF_CUDA(c, cudaMemcpyAsync(c->vals.p, seg_vals, sizeof(uint32_t) * (size_t)nF, cudaMemcpyHostToDevice, c->stream));
+    if (T) PF_CUDA(c, cudaMemcpyAsync(c->T.p, T, sizeof(int32_t) * (size_t)nseg, cudaMemcpyHostToDevice, c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_H2D1], c->stream));
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B0], c->stream));
+    PF_CUDA(c, cudaMemsetAsync(c->flags.p, 0, 64, c->stream));
+    PF_TRY(launch_scan(c, ptr<int32_t>(c->Lc), NTETRA, ptr<int64_t>(c->Lp64), ptr<int32_t>(c->Lp32)));   // Lp parity hook
+    k_check_lists<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
+        ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), nseg, nF, ptr<int>(c->flags));
+    PF_LAUNCH_CHECK(c);
+    if (!T) {
+        k_t_from_offsets<<<(unsigned)ceil_div64(nseg, 256), 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), P, G, ptr<int32_t>(c->T));
+        PF_LAUNCH_CHECK(c);
+    }
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_B1], c->stream));
+    int fl[4];
+    PF_TRY(read_flags(c, fl));
+    if (fl[0]) { set_error(c, "import_lists: offsets must ascend from 0 to nF and tetramers must ascend strictly inside a segment, below 160000"); return PFAAI_ERR_CONSTRUCT; }
+    c->max_len = fl[1];
+    c->tm.h2d_ms = ev_ms(c, EV_H2D0, EV_H2D1);
+    c->tm.build_ms = ev_ms(c, EV_B0, EV_B1);
+    c->tm.sort_ms = 0.f;
+    c->tm.n_launches = c->launches;
+    c->uploaded = true; c->built = true;
+    return PFAAI_OK;
+}
+
 int pfaai_gpu_index_device_buffers(pfaai_gpu_ctx *h, int P, int G, int64_t nF, int host_T, void **F_dev, void **Lc_dev, void **T_dev) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     if (!c) return PFAAI_ERR_CONSTRUCT;

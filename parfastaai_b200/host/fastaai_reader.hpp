@@ -64,6 +64,10 @@ struct HostIndex {
     std::vector<int32_t> Lc;   // [160000]
     std::vector<pfaai_pg_t> F; // [sum Lc]
     std::vector<int32_t> T;    // [P x nGenomes]
+    // device-ready form (index cache, pfaai_gpu_import_lists): genome-major lists; when present F may be empty
+    std::vector<int64_t> segOff;    // [P*nGenomes + 1]
+    std::vector<uint32_t> segVals;  // [sum Lc]
+    bool haveLists() const { return !segOff.empty(); }
 };
 
 namespace detail {
@@ -212,6 +216,11 @@ class SQLiteSCPDataBase {
     int getDBErrorCode() const { return m_dbErrorCode; }
     std::string getDBPath() const { return m_pathToDb; }
     const DBMetaData &getMeta() const { return m_dbMeta; }
+    // device-ready lists cache (index_cache.hpp): the driver announces whether it can take the genome-major lists instead of F
+    // (single-context or replicated builds) and hands the lists of a fresh device build back for the next run
+    virtual void preferLists(bool) const {}
+    virtual bool wantsLists() const { return false; }
+    virtual bool storeLists(const HostIndex &, const int64_t *, const uint32_t *) const { return false; }
 
     int closeDB() {
         if (m_sqltDbPtr == nullptr) {

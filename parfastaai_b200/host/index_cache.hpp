@@ -72,7 +72,7 @@ inline bool write_index_cache(const std::string &path, const IndexCacheKey &key,
 
 // true: meta and ix hold the cached index of the database identified by `key`; false: no usable cache (missing, other
 // database version, truncated, checksum mismatch) -- the caller falls back to SQLite and rewrites it
-inline bool read_index_cache(const std::string &path, const IndexCacheKey &key, DBMetaData &meta, HostIndex &ix) {
+inline bool read_index_cache(const std::string &path, const IndexCacheKey &key, DBMetaData &meta, HostIndex &ix, bool skip_F = false) {
     FILE *f = std::fopen(path.c_str(), "rb");
     if (!f) return false;
     bool ok = true;
@@ -102,7 +102,8 @@ inline bool read_index_cache(const std::string &path, const IndexCacheKey &key, 
         ok = ok && total == nF;
     }
     if (ok) {
-        x.F.resize(nF); get(x.F.data(), x.F.size() * sizeof(pfaai_pg_t));
+        if (skip_F) ok = ok && fseeko(f, (off_t)(nF * sizeof(pfaai_pg_t)), SEEK_CUR) == 0;    // the caller holds the device-ready lists instead
+        else { x.F.resize(nF); get(x.F.data(), x.F.size() * sizeof(pfaai_pg_t)); }
         x.T.resize((size_t)P * G); get(x.T.data(), x.T.size() * sizeof(int32_t));
         char extra;
         ok = ok && std::fread(&extra, 1, 1, f) == 0;              // nothing may follow
@@ -115,6 +116,63 @@ inline bool read_index_cache(const std::string &path, const IndexCacheKey &key, 
     return true;
 }
 
+// ---- device-ready sidecar (<cache>.lists): the genome-major lists a device build produced (pfaai_gpu_get_arrays), so that the next
+// run hands them straight to pfaai_gpu_import_lists -- no F over PCIe (4 instead of 8 bytes per posting), no K1-K3, no sort.
+//   char[8] "PFLST001" | u64 db_size | i64 db_mtime_ns | i32 P | i32 G | u64 nF | u64 checksum(seg_off) | i64 seg_off[P*G+1] | u32 vals[nF]
+inline bool write_lists_cache(const std::string &path, const IndexCacheKey &key, int32_t P, int32_t G, uint64_t nF, const int64_t *seg_off,
+                              const uint32_t *vals) {
+    const std::string tmp = path + ".tmp";
+    FILE *f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return false;
+    bool ok = true;
+    auto put = [&](const void *p, size_t n) { if (ok && n) ok = std::fwrite(p, 1, n, f) == n; };
+    const size_t nseg1 = (size_t)P * G + 1;
+    const uint64_t sum = detail::fnv1a(1469598103934665603ull, seg_off, nseg1 * sizeof(int64_t));
+    put("PFLST001", 8); put(&key.size, 8); put(&key.mtime_ns, 8); put(&P, 4); put(&G, 4); put(&nF, 8); put(&sum, 8);
+    put(seg_off, nseg1 * sizeof(int64_t));
+    put(vals, (size_t)nF * sizeof(uint32_t));
+    ok = (std::fclose(f) == 0) && ok;
+    if (ok) ok = std::rename(tmp.c_str(), path.c_str()) == 0;
+    if (!ok) std::remove(tmp.c_str());
+    return ok;
+}
+
+// cheap test (header only): does a sidecar for this database version exist?
+inline bool lists_cache_header_ok(const std::string &path, const IndexCacheKey &key) {
+    FILE *f = std::fopen(path.c_str(), "rb");
+    if (!f) return false;
+    char magic[8]; IndexCacheKey k;
+    const bool ok = std::fread(magic, 1, 8, f) == 8 && std::fread(&k.size, 1, 8, f) == 8 && std::fread(&k.mtime_ns, 1, 8, f) == 8 &&
+                    std::memcmp(magic, "PFLST001", 8) == 0 && k.size == key.size && k.mtime_ns == key.mtime_ns;
+    std::fclose(f);
+    return ok;
+}
+
+inline bool read_lists_cache(const std::string &path, const IndexCacheKey &key, int32_t P, int32_t G, uint64_t nF, std::vector<int64_t> &seg_off,
+                             std::vector<uint32_t> &vals) {
+    FILE *f = std::fopen(path.c_str(), "rb");
+    if (!f) return false;
+    bool ok = true;
+    auto get = [&](void *p, size_t n) { if (ok && n) ok = std::fread(p, 1, n, f) == n; };
+    char magic[8]; IndexCacheKey k; int32_t p2 = 0, g2 = 0; uint64_t n2 = 0, sum = 0;
+    get(magic, 8); get(&k.size, 8); get(&k.mtime_ns, 8); get(&p2, 4); get(&g2, 4); get(&n2, 8); get(&sum, 8);
+    ok = ok && std::memcmp(magic, "PFLST001", 8) == 0 && k.size == key.size && k.mtime_ns == key.mtime_ns && p2 == P && g2 == G && n2 == nF;
+    std::vector<int64_t> so; std::vector<uint32_t> v;
+    if (ok) {
+        so.resize((size_t)P * G + 1); get(so.data(), so.size() * sizeof(int64_t));
+        ok = ok && detail::fnv1a(1469598103934665603ull, so.data(), so.size() * sizeof(int64_t)) == sum && so.front() == 0 && (uint64_t)so.back() == nF;
+    }
+    if (ok) {
+        v.resize((size_t)nF); get(v.data(), v.size() * sizeof(uint32_t));
+        char extra;
+        ok = ok && std::fread(&extra, 1, 1, f) == 0;
+    }
+    std::fclose(f);
+    if (!ok) return false;
+    seg_off = std::move(so); vals = std::move(v);
+    return true;
+}
+
 // SQLiteSCPDataBase with an index cache in front of it (par_fastaai.x --index-cache PATH): a valid cache serves the name
 // tables and Lc / F / T without opening SQLite at all; otherwise the database is read as usual and the cache (re)written.
 class CachedSCPDataBase : public SQLiteSCPDataBase {
@@ -123,26 +181,55 @@ class CachedSCPDataBase : public SQLiteSCPDataBase {
     bool m_haveKey = false, m_cached = false;
     mutable HostIndex m_cachedIx;       // handed to the first loadIndex() by move
     mutable bool m_cachedIxValid = false;
+    mutable bool m_preferLists = false;
+    bool m_skippedF = false;
+    size_t cachedPostings() const { uint64_t n = 0; for (int32_t v : m_cachedIx.Lc) n += (uint64_t)v; return (size_t)n; }
 
   public:
     CachedSCPDataBase(const std::string &dbPath, const std::string &cachePath)
         : SQLiteSCPDataBase(dbPath, DeferOpen{}), m_cachePath(cachePath) {
         m_haveKey = index_cache_key(dbPath, m_key);
-        if (m_haveKey && read_index_cache(m_cachePath, m_key, m_dbMeta, m_cachedIx)) {
+        // with a device-ready sidecar next to it the 8-byte-per-posting F section is not even read from disk
+        m_skippedF = m_haveKey && lists_cache_header_ok(listsPath(), m_key);
+        if (m_haveKey && read_index_cache(m_cachePath, m_key, m_dbMeta, m_cachedIx, m_skippedF)) {
             m_cached = m_cachedIxValid = true;
             std::printf("Index cache         : loaded %s (%zu genomes x %zu SCPs, |F| = %zu); SQLite not opened\n", m_cachePath.c_str(),
-                        m_dbMeta.genomeSet.size(), m_dbMeta.proteinSet.size(), m_cachedIx.F.size());
+                        m_dbMeta.genomeSet.size(), m_dbMeta.proteinSet.size(), cachedPostings());
             return;
         }
         openAndReadNames();
     }
     bool fromCache() const { return m_cached; }
+    std::string listsPath() const { return m_cachePath + ".lists"; }
+    void preferLists(bool on) const override { m_preferLists = on; }
+    bool wantsLists() const override { return m_haveKey; }
+    bool storeLists(const HostIndex &ix, const int64_t *seg_off, const uint32_t *vals) const override {
+        if (!m_haveKey) return false;
+        uint64_t nF = 0;
+        for (int32_t v : ix.Lc) nF += (uint64_t)v;
+        const bool ok = write_lists_cache(listsPath(), m_key, ix.nProteins, ix.nGenomes, nF, seg_off, vals);
+        if (ok) std::printf("Index cache         : device-ready lists written to %s\n", listsPath().c_str());
+        return ok;
+    }
     pfaai_status validate() const override { return m_cached ? PFAAI_OK : SQLiteSCPDataBase::validate(); }
     int loadIndex(HostIndex &ix) const override {
         if (m_cached) {
-            if (m_cachedIxValid) { ix = std::move(m_cachedIx); m_cachedIxValid = false; return SQLITE_OK; }
-            DBMetaData meta;
-            return read_index_cache(m_cachePath, m_key, meta, ix) ? SQLITE_OK : SQLITE_ERROR;
+            if (m_cachedIxValid) { ix = std::move(m_cachedIx); m_cachedIxValid = false; }
+            else {
+                DBMetaData meta;
+                if (!read_index_cache(m_cachePath, m_key, meta, ix)) return SQLITE_ERROR;
+            }
+            uint64_t nF = 0;
+            for (int32_t v : ix.Lc) nF += (uint64_t)v;
+            if (m_preferLists && read_lists_cache(listsPath(), m_key, ix.nProteins, ix.nGenomes, nF, ix.segOff, ix.segVals)) {
+                std::printf("Index cache         : device-ready lists loaded from %s (no F upload, no device sort)\n", listsPath().c_str());
+                return SQLITE_OK;
+            }
+            if (ix.F.size() != nF) {            // F was skipped for a sidecar that cannot be used after all: read the full cache
+                DBMetaData meta;
+                if (!read_index_cache(m_cachePath, m_key, meta, ix)) return SQLITE_ERROR;
+            }
+            return SQLITE_OK;
         }
         const int rc = SQLiteSCPDataBase::loadIndex(ix);
         if (rc == SQLITE_OK && m_haveKey) {

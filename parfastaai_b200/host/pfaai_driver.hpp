@@ -86,6 +86,7 @@ class DataStructBase {
     bool m_hostT = false;   // query-DB mode: T comes from the host (F is inner-joined, T is not)
 
     virtual int loadHostIndex(HostIndex &ix) = 0;   // SQLite rc
+    virtual const SQLiteSCPDataBase *cacheDb() const { return nullptr; }   // single-DB modes: the database object (index cache hooks)
 
   public:
     explicit DataStructBase(const DBMetaData &meta) : m_dbMeta(meta) {}
@@ -131,6 +132,11 @@ class DataStructBase {
     // == construct() (interface.hpp:306-327): host load, then upload + device build behind the C-ABI
     virtual pfaai_status construct() {
         PhaseTimer tm;
+        const int n = (int)m_devices.size();
+        // device-ready lists from the index cache (no F upload, no K1-K3, no sort) serve every build but the routed multi-GPU one
+        const SQLiteSCPDataBase *cdb = m_hostT ? nullptr : cacheDb();
+        const bool routed_possible = n > 1 && mode() == PFAAI_ALL_VS_ALL && !m_hostT;
+        if (cdb) cdb->preferLists(!routed_possible);
         if (loadHostIndex(m_ix) != SQLITE_OK) {
             std::cerr << "Error in Lc, F, T host load ; Error code : " << PFAAI_ERR_SQLITE_DB << std::endl;
             return m_errorCode = PFAAI_ERR_SQLITE_DB;
@@ -143,20 +149,24 @@ class DataStructBase {
         print_ref_phase("Lc & Lp contruction : ", load_ms);
         print_ref_phase("F contruction       : ", 0.0);
         print_ref_phase("T construction      : ", 0.0);
-        std::printf("  Lc, F, T host load  : %10.3f ms; |F| = %zu\n", load_ms, m_ix.F.size());
+        int64_t nF_all = 0;
+        for (int32_t v : m_ix.Lc) nF_all += v;
+        std::printf("  Lc, F, T host load  : %10.3f ms; |F| = %lld%s\n", load_ms, (long long)nF_all, m_ix.haveLists() ? " (device-ready lists from the index cache)" : "");
         // one host thread per GPU (the C-ABI is one-thread-per-context): upload + device build on every GPU in parallel
-        const int n = (int)m_devices.size();
         m_ctxs.assign(n, nullptr);
         std::vector<int> rcs(n, PFAAI_OK);
         std::vector<std::string> errs(n);
         // several GPUs, all-vs-all: routed + partitioned build -- every GPU gets a slice of F, sorts the postings and builds the
         // column dictionaries of its own row blocks only; postings and dictionaries move by peer copies; otherwise replicated build
-        const bool partitioned = n > 1 && mode() == PFAAI_ALL_VS_ALL && !m_hostT;
+        const bool partitioned = routed_possible && !m_ix.haveLists();
         auto work = [&](int k) {
             int rc = pfaai_gpu_create(&m_ctxs[k], m_devices[k], 0);
             if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(nullptr); return; }
             rc = pfaai_gpu_set_shard(m_ctxs[k], k, n);
-            if (rc == PFAAI_OK && partitioned) {
+            if (rc == PFAAI_OK && m_ix.haveLists()) {
+                rc = pfaai_gpu_import_lists(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, nF_all, m_ix.Lc.data(), nullptr, m_ix.segOff.data(),
+                                            m_ix.segVals.data());
+            } else if (rc == PFAAI_OK && partitioned) {
                 // routed build: GPU k receives only the k-th slice of F (|F| bytes cross PCIe once, not once per GPU); the
                 // postings are routed to the GPU that owns their genome afterwards (pfaai_gpu_route_local)
                 const int64_t nF = (int64_t)m_ix.F.size(), lo = nF * k / n, hi = nF * (k + 1) / n;
@@ -217,7 +227,17 @@ class DataStructBase {
         pfaai_timings_t t;
         pfaai_gpu_get_timings(m_ctx, &t);
         const double build_ms = tm.lap_ms();
+        if (cdb && cdb->wantsLists() && !partitioned && !m_ix.haveLists()) {
+            // first run with an index cache: keep the device-ready lists for the next one
+            std::vector<int64_t> so((size_t)m_ix.nProteins * m_ix.nGenomes + 1);
+            std::vector<uint32_t> sv((size_t)nF_all);
+            if (pfaai_gpu_get_arrays(m_ctx, nullptr, nullptr, nullptr, so.data(), reinterpret_cast<int32_t *>(sv.data())) == PFAAI_OK)
+                cdb->storeLists(m_ix, so.data(), sv.data());
+            tm.lap_ms();
+        }
         std::fflush(stdout);
+        print_ref_phase(" E construction      : ", std::max(0.0, build_ms - (double)t.sort_ms));   // ds_helper.hpp:412 (here: upload + K1-K3)
+        print_ref_phase("E parallel sorting  : ", (double)t.sort_ms);                               // ds_helper.hpp:419 (here: the device radix sort)
         print_ref_phase("E constr.   (fin)   : ", build_ms);
         std::printf("  Device index build  : %10.3f ms; (%d GPU(s); GPU %d: H2D %.3f ms, build kernels %.3f ms, of which sort %.3f ms)\n",
                     build_ms, n, m_devices[0], t.h2d_ms, t.build_ms, t.sort_ms);
@@ -231,6 +251,7 @@ class ParFAAIData : public DataStructBase {
     std::vector<int32_t> m_noIds;
     int m_nGenomes;
     int loadHostIndex(HostIndex &ix) override { return m_DBIf.loadIndex(ix); }
+    const SQLiteSCPDataBase *cacheDb() const override { return &m_DBIf; }
 
   public:
     ParFAAIData(const SQLiteSCPDataBase &dbif, const DBMetaData &dbMeta)
@@ -260,6 +281,7 @@ class ParFAAIQSubData : public DataStructBase {
     std::vector<int> m_genomeIndexMap;       // genome id -> query index | index among the non-query genomes
     std::vector<char> m_qryIndicator;
     int loadHostIndex(HostIndex &ix) override { return m_DBIf.loadIndex(ix); }
+    const SQLiteSCPDataBase *cacheDb() const override { return &m_DBIf; }
 
   public:
     ParFAAIQSubData(const SQLiteSCPDataBase &dbif, const DBMetaData &dbMeta, const std::vector<std::string> &qryGenomeSet)

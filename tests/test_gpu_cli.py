@@ -35,7 +35,14 @@ def test_all_vs_all_csv_bytes(cli, tmp_path):
         out = tmp_path / ("out_" + gold)
         r = run(cli, db, str(out))
         assert out.read_bytes() == gu.csv_bytes(gold), gold
-        assert "Writing output with" in r.stdout and "JAC Construction" in r.stdout
+        assert "Writing output with" in r.stdout
+        # the reference's phase lines, prefix and number format (interface.hpp:307-325, algorithm_impl.hpp:304, utils.hpp:136-200)
+        import re
+        for prefix in ("Lc & Lp contruction : ", "F contruction       : ", "T construction      : ", " E construction      : ",
+                       "E parallel sorting  : ", "E constr.   (fin)   : ",
+                       "JAC Construction    : "):
+            assert re.search(r"^" + re.escape(prefix) + r" *[0-9.e+-]+ ms \( *[0-9.e+-]+ sec/ *[0-9.e+-]+ min\);  *\d+ KB \( *\d+ MB/ *\d+ GB\)\.$",
+                             r.stdout, re.M), (prefix, r.stdout)
 
 
 def test_query_subset_csv_bytes(cli, tmp_path):
@@ -105,10 +112,29 @@ def test_index_cache_gives_identical_csv(cli, tmp_path):
         run(cli, db, plain, *extra)
         if os.path.exists(cache):
             os.remove(cache)
+        for f in (cache, cache + ".lists"):
+            if os.path.exists(f):
+                os.remove(f)
         r1 = run(cli, db, first, *extra, "--index-cache", cache)
         r2 = run(cli, db, second, *extra, "--index-cache", cache)
-        assert "written" in r1.stdout and "SQLite not opened" in r2.stdout
+        assert "written" in r1.stdout and "device-ready lists written" in r1.stdout and os.path.exists(cache + ".lists")
+        # second run: SQLite never opened, F neither read nor uploaded, no K1-K3 / sort -- the device-ready lists are imported
+        assert "SQLite not opened" in r2.stdout and "device-ready lists loaded" in r2.stdout
         assert open(plain, "rb").read() == open(first, "rb").read() == open(second, "rb").read()
+        # a damaged sidecar is ignored (the run falls back to F from the cache) and the result is still the same
+        blob = bytearray(open(cache + ".lists", "rb").read()); blob[60] ^= 0xff
+        open(cache + ".lists", "wb").write(bytes(blob))
+        third = str(tmp_path / "third.csv")
+        r3 = run(cli, db, third, *extra, "--index-cache", cache)
+        assert r3.returncode == 0 and "device-ready lists loaded" not in r3.stdout
+        assert open(third, "rb").read() == open(plain, "rb").read()
+        # two contexts, replicated import of the cached lists, sharded compute
+        os.remove(cache + ".lists")
+        run(cli, db, first, *extra, "--index-cache", cache)
+        fourth = str(tmp_path / "fourth.csv")
+        r4 = run(cli, db, fourth, *extra, "--index-cache", cache, "--gpus", "2", "--same-device")
+        assert r4.returncode == 0, r4.stdout + r4.stderr
+        assert open(fourth, "rb").read() == open(plain, "rb").read()
     assert open(plain, "rb").read() != b""
 
 

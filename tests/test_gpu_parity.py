@@ -90,6 +90,40 @@ def test_lc_built_on_the_device_from_tetramer_keys(pf, name):
     ctx.close()
 
 
+def test_device_ready_lists_import_equals_the_built_index(pf, orc):
+    """pfaai_gpu_import_lists (the index cache's fast path): the lists exported from a built context, imported into a fresh one
+    -- no F, no K1-K3, no sort -- give the same arrays and bit-identical results in all three modes; damaged lists fail loudly."""
+    g = gu.load("xanthodb")
+    ctx, P, G = _ctx_for(pf, g)
+    a = ctx.get_arrays()
+    full = ctx.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+    qids = gu.query_subset_ids()
+    sub = ctx.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=True)
+    ctx.close()
+    c2 = pf.PfaaiGpu(0)
+    c2.import_lists(P, G, a["Lc"], a["seg_off"], a["seg_vals"])          # T derived from the segment lengths
+    b = c2.get_arrays()
+    for k in ("Lc", "Lp", "T", "seg_off", "seg_vals"):
+        assert np.array_equal(a[k], b[k]), k
+    for path in (pf.PATH_LISTS, pf.PATH_MMA):
+        c2.set_path(path)
+        r = c2.compute(pf.ALL_VS_ALL, want_jac=True, want_counts=True)
+        assert np.array_equal(r["counts"], full["counts"]) and np.array_equal(r["aji"], full["aji"]) and np.array_equal(r["matrix"], full["matrix"])
+    c2.set_path(pf.PATH_AUTO)
+    r = c2.compute(pf.QUERY_SUBSET, qry_ids=qids, want_jac=True)
+    assert np.array_equal(r["aji"], sub["aji"]) and np.array_equal(r["matrix"], sub["matrix"])
+    assert c2.e_size() == int(full["counts"].sum())
+    c2.import_lists(P, G, a["Lc"], a["seg_off"], a["seg_vals"], T=a["T"])   # caller-supplied T
+    assert np.array_equal(c2.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], full["matrix"])
+    bad = a["seg_vals"].copy(); bad[[0, 1]] = bad[[1, 0]]
+    with pytest.raises(pf.PfaaiError):
+        c2.import_lists(P, G, a["Lc"], a["seg_off"], bad)
+    bad_off = a["seg_off"].copy(); bad_off[-1] -= 1
+    with pytest.raises(pf.PfaaiError):
+        c2.import_lists(P, G, a["Lc"], bad_off, a["seg_vals"])
+    c2.close()
+
+
 @pytest.mark.parametrize("name", ["xanthodb", "xdb_subset1", "xdb_subset2"])
 def test_all_vs_all_golden(pf, orc, name):
     g = gu.load(name)
