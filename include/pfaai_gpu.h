@@ -118,6 +118,15 @@ int  pfaai_gpu_host_unregister(void *ptr, size_t bytes);
  * least tau genomes become tensor-core columns, shorter ones patch records); 0 = chosen by the cost model. */
 enum pfaai_path { PFAAI_PATH_AUTO = 0, PFAAI_PATH_LISTS = 1, PFAAI_PATH_MMA = 2 };
 int  pfaai_gpu_set_path(pfaai_gpu_ctx *ctx, int path, int tau);
+/* Streaming output (printOutput, main.cpp:156-174): with progress enabled, an unsharded ALL_VS_ALL compute
+ * into a PINNED host matrix (the tile kernels store straight into it) maintains device-side counters of finished tiles per block
+ * of output rows; every store is fenced (__threadfence_system) before its tile is counted.  pfaai_gpu_progress_poll may be
+ * called from ANOTHER host thread while pfaai_gpu_compute blocks its caller: rows [0, rows_final) of the matrix are complete
+ * (direct and mirrored cells) and will not be written again, so a CSV writer can format them while later row blocks are still
+ * being computed; *finished = 1 once the compute has returned (rows_final = all rows).  Other modes / sharded contexts /
+ * pageable matrices report rows_final = 0 until the compute has finished. */
+int  pfaai_gpu_set_progress(pfaai_gpu_ctx *ctx, int enable);
+int  pfaai_gpu_progress_poll(pfaai_gpu_ctx *ctx, int64_t *rows_final, int *finished);
 /* |E| of the built index for all-vs-all (sum over (SCP, tetramer) posting lists of n(n-1)/2: the size of the reference's E
  * array, countTetramerTuples ds_helper.hpp:206-265) -- the layout-independent work unit of SURVEY 8(d). */
 int  pfaai_gpu_e_size(pfaai_gpu_ctx *ctx, int64_t *e_size);

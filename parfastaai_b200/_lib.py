@@ -32,7 +32,7 @@ EXPORTS = [
     "pfaai_gpu_set_partition_chunk", "pfaai_gpu_finish_partitioned_async",
     "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
     "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench", "pfaai_gpu_set_path", "pfaai_gpu_e_size",
-    "pfaai_gpu_host_register", "pfaai_gpu_host_unregister", "pfaai_gpu_upload_triples", "pfaai_gpu_import_lists",
+    "pfaai_gpu_host_register", "pfaai_gpu_host_unregister", "pfaai_gpu_upload_triples", "pfaai_gpu_import_lists", "pfaai_gpu_set_progress", "pfaai_gpu_progress_poll",
 ]
 
 
@@ -116,6 +116,8 @@ def load():
     L.pfaai_gpu_host_register.argtypes = [vp, C.c_size_t]
     L.pfaai_gpu_host_unregister.argtypes = [vp, C.c_size_t]
     L.pfaai_gpu_e_size.argtypes = [vp, C.POINTER(i64)]
+    L.pfaai_gpu_set_progress.argtypes = [vp, i32]
+    L.pfaai_gpu_progress_poll.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_int)]
     L.pfaai_gpu_microbench.argtypes = [vp, i32, C.c_double, i32, C.POINTER(Microbench)]
     _lib = L
     return L
@@ -222,6 +224,15 @@ class PfaaiGpu:
             raise ValueError("seg_off must have P*G + 1 entries")
         self.P, self.G, self.nF = P, G, int(seg_vals.shape[0])
         self._check(self._L.pfaai_gpu_import_lists(self._h, P, G, self.nF, _p(Lc), _p(T), _p(seg_off), _p(seg_vals)), "import_lists")
+
+    def set_progress(self, on=True):
+        self._check(self._L.pfaai_gpu_set_progress(self._h, int(on)), "set_progress")
+
+    def progress_poll(self):
+        """-> (rows_final, finished); callable from another thread while compute() blocks (pfaai_gpu_progress_poll)."""
+        r, f = C.c_int64(), C.c_int()
+        self._check(self._L.pfaai_gpu_progress_poll(self._h, C.byref(r), C.byref(f)), "progress_poll")
+        return int(r.value), bool(f.value)
 
     def index_device_buffers(self, P, G, nF, host_T=False):
         """Size the device index buffers and return their pointers (F, Lc, T) for a caller-side fill (NCCL broadcast)."""

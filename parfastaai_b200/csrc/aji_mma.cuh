@@ -107,6 +107,7 @@ struct MmaParams {
     double *S_out; int32_t *N_out; int32_t *counts_out;
     const int4 *tiles;                  // (row block I, column block J, first output row of block I, unused)
     int n_tiles;
+    int *progress;                      // streaming output: finished tiles per 128-row granule (see TileParams::progress); NULL = off
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
@@ -577,8 +578,13 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                     }
                 }
             }
+            if (prm.progress) __threadfence_system();
             asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");
-            // the staging area doubles as the patch counters: clear what the last round left behind
+            if (prm.progress && tid == 0) {
+                atomicAdd(prm.progress + tile.x, 1);
+                if (prm.mirror) atomicAdd(prm.progress + tile.y, 1);
+            }
+            // the staging area doubles as the sparse counters: clear what the last round left behind
             for (int i = tid; i < MM_SMEM_CNT / 4; i += MM_EPI_WARPS * 32) reinterpret_cast<uint32_t *>(cnt_mem)[i] = 0u;
             asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");
         }

@@ -66,6 +66,10 @@ struct TileParams {
     int n_tiles2;
     int *tile_counter2;
     uint32_t k27, k16;         // 2^27, 2^16 (PF_IMAD_HI: shift-by-multiply constants)
+    // streaming output (pfaai_gpu_set_progress): progress[g] counts the finished tiles that store into output rows 64g .. 64g+63
+    // (the tile's own 6 granules; in mirror mode also granule J, where the transposed cells land).  NULL = off.
+    int *progress;
+    int n_gran;
     uint32_t piece;            // a stage blob travels as bulk copies of this many bytes (multiple of 16), all completing on the stage's
                                // mbarrier: one copy keeps only a few bytes per cycle in flight, many overlap their latencies
 };
@@ -627,7 +631,13 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                 }
             }
         }
+        if (prm.progress) __threadfence_system();   // this thread's stores (device or mapped host memory) before the counters move
         __syncthreads();   // staging, col_g and colT are free again before the next tile refills the slots
+        if (prm.progress && tid == 0) {
+            constexpr int GPR = TILE_ROWS / COLS_PER_TILE;
+            for (int k = 0; k < GPR; k++) { const int g = tile.x * GPR + k; if (g < prm.n_gran) atomicAdd(prm.progress + g, 1); }
+            if (prm.mirror) atomicAdd(prm.progress + tile.y, 1);
+        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();

@@ -1,6 +1,7 @@
 // pfaai_gpu.cu -- C-ABI (include/pfaai_gpu.h) and host orchestration of the sm_100a AJI path.
 // No CPU fallback: every entry point either runs the CUDA kernels or returns PFAAI_ERR_CONSTRUCT.
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -47,6 +48,17 @@ struct Ctx {
     int64_t slot_cap = 0;                 // dictionary slots (column blocks) per shard chunk
     void *exch_event = nullptr;           // pfaai_gpu_finish_partitioned_async: the exchange is complete when this cudaEvent_t fires
     DevBuf tile_ctr;
+    // streaming output (pfaai_gpu_set_progress / pfaai_gpu_progress_poll): per-granule counters of finished tiles, what they must
+    // reach, and a private stream + pinned buffer for polling from another host thread while compute blocks its caller
+    DevBuf prog;
+    bool prog_enabled = false;
+    std::atomic<int> prog_state{0};          // 0 = no compute under way / not armed, 1 = armed (counters valid), 2 = compute finished
+    std::vector<int32_t> prog_need;
+    int prog_gran = 0;                        // output rows per granule
+    int64_t prog_rows = 0;                    // output rows of the armed compute
+    cudaStream_t prog_stream = nullptr;
+    int32_t *prog_host = nullptr;
+    size_t prog_host_cap = 0;
     // dense-contraction path (K5): planning + operands + patches
     int path_pref = PFAAI_PATH_AUTO, tau_pref = 0;
     DevBuf mm_len, mm_hist, mm_did, mm_kcnt, mm_kpad, mm_koff, mm_img_rows, mm_img_cols, mm_colT, mm_rowmax, mm_colmax,
@@ -296,8 +308,10 @@ void pfaai_gpu_destroy(pfaai_gpu_ctx *h) {
                      &c->owner_tbl, &c->warp_cnt, &c->warp_off, &c->cb_list, &c->tile_ctr, &c->route_hist, &c->recv,
                      &c->mm_len, &c->mm_hist, &c->mm_did, &c->mm_kcnt, &c->mm_kpad, &c->mm_koff, &c->mm_img_rows, &c->mm_img_cols,
                      &c->mm_colT, &c->mm_rowmax, &c->mm_colmax, &c->mm_owned, &c->sp_cnt, &c->sp_nch, &c->sp_tot, &c->sp_off, &c->sp_items,
-                     &c->sp_nsub, &c->sp_sub, &c->sp_blob};
+                     &c->sp_nsub, &c->sp_sub, &c->sp_blob, &c->prog};
     for (DevBuf *b : all) release(*b);
+    if (c->prog_stream) cudaStreamDestroy(c->prog_stream);
+    if (c->prog_host) cudaFreeHost(c->prog_host);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
@@ -1353,7 +1367,35 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         PF_TRY(ensure(c, c->counts_out, sizeof(int32_t) * nk * P));
         PF_CUDA(c, cudaMemsetAsync(c->counts_out.p, 0, sizeof(int32_t) * nk * P, c->stream));
     }
+    // ---- streaming output: arm the per-granule progress counters (unsharded all-vs-all into a pinned host matrix only) ----
+    c->prog_state.store(0, std::memory_order_release);
+    int *prog_dev = nullptr;
+    int n_gran = 0;
+    if (c->prog_enabled && direct_dev && m.symmetric && !sharded && !tiles.empty() && c->nF > 0) {
+        n_gran = (n_cols + TC - 1) / TC;
+        const int gpr = TR / TC;
+        std::vector<int32_t> need(n_gran, 0);
+        for (const int4 &t : tiles) {
+            for (int k = 0; k < gpr; k++) if (t.x * gpr + k < n_gran) need[t.x * gpr + k]++;
+            need[t.y]++;                                            // the mirror image lands in the rows of column block J
+        }
+        PF_TRY(ensure(c, c->prog, sizeof(int32_t) * (size_t)n_gran));
+        PF_CUDA(c, cudaMemsetAsync(c->prog.p, 0, sizeof(int32_t) * (size_t)n_gran, c->stream));
+        if (!c->prog_stream) PF_CUDA(c, cudaStreamCreateWithFlags(&c->prog_stream, cudaStreamNonBlocking));
+        if (c->prog_host_cap < (size_t)n_gran) {
+            if (c->prog_host) cudaFreeHost(c->prog_host);
+            c->prog_host = nullptr; c->prog_host_cap = 0;
+            PF_CUDA(c, cudaMallocHost(reinterpret_cast<void **>(&c->prog_host), sizeof(int32_t) * (size_t)n_gran));
+            c->prog_host_cap = (size_t)n_gran;
+        }
+        PF_CUDA(c, cudaStreamSynchronize(c->stream));               // counters are zero before anybody polls
+        c->prog_need = std::move(need);
+        c->prog_gran = TC; c->prog_rows = n_rows;
+        prog_dev = ptr<int>(c->prog);
+        c->prog_state.store(1, std::memory_order_release);
+    }
     TileParams prm;
+    prm.progress = prog_dev; prm.n_gran = n_gran;
     prm.ell = ptr<uint4>(c->ell); prm.ell_off = ptr<int64_t>(c->ell_off);
     prm.rows = ptr<int32_t>(c->rows); prm.row_t = ptr<int32_t>(c->row_t); prm.n_rows = n_rows; prm.n_groups = n_groups;
     prm.cols = ptr<int32_t>(c->cols); prm.n_cols = n_cols;
@@ -1400,6 +1442,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         mp.out = prm.out; mp.out_rs = prm.out_rs; mp.out_cs = prm.out_cs; mp.symmetric = prm.symmetric; mp.mirror = prm.mirror;
         mp.S_out = prm.S_out; mp.N_out = prm.N_out; mp.counts_out = prm.counts_out;
         mp.tiles = ptr<int4>(c->tiles); mp.n_tiles = (int)tiles.size();
+        mp.progress = prog_dev;
         PF_CUDA(c, cudaEventRecord(c->ev[EV_T0], c->stream));
         if (!tiles.empty()) {
             const unsigned grid = (unsigned)std::min<int>((int)tiles.size(), c->sm_count);
@@ -1436,6 +1479,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     c->exch_event = nullptr;   // consumed: later computes on this build find the dictionaries in place
     PF_CUDA(c, cudaEventRecord(c->ev[EV_T1], c->stream));
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (prog_dev) c->prog_state.store(2, std::memory_order_release);
     c->tm.pack_ms = use_mma ? 0.f : ev_ms(c, EV_P0, EV_P1);
     if (!c->partitioned) c->tm.dict_ms = use_mma ? 0.f : ev_ms(c, EV_K0, EV_K1);
     c->tm.prep_ms = use_mma ? ev_ms(c, EV_K0, EV_K1) : 0.f;
@@ -1555,6 +1599,34 @@ int pfaai_gpu_compute(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_
         for (int q = 0; q < n_qry; q++) for (int t = 0; t < nT; t++)
             emit(quirk ? q : nT + q, quirk ? n_qry + t : t, (size_t)t * n_cols + q);
     }
+    return PFAAI_OK;
+}
+
+int pfaai_gpu_set_progress(pfaai_gpu_ctx *h, int enable) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return PFAAI_ERR_CONSTRUCT;
+    c->prog_enabled = enable != 0;
+    c->prog_state.store(0, std::memory_order_release);
+    return PFAAI_OK;
+}
+
+// May be called from another host thread while pfaai_gpu_compute blocks its caller: touches only the context's private polling
+// stream, its pinned counter copy and data published (release / acquire) before the tile kernel was launched.
+int pfaai_gpu_progress_poll(pfaai_gpu_ctx *h, int64_t *rows_final, int *finished) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !rows_final) return PFAAI_ERR_CONSTRUCT;
+    const int st = c->prog_state.load(std::memory_order_acquire);
+    if (finished) *finished = (st == 2) ? 1 : 0;
+    if (st == 0) { *rows_final = 0; return PFAAI_OK; }
+    if (st == 2) { *rows_final = c->prog_rows; return PFAAI_OK; }
+    if (cudaSetDevice(c->device) != cudaSuccess) return PFAAI_ERR_CONSTRUCT;
+    const int n = (int)c->prog_need.size();
+    if (cudaMemcpyAsync(c->prog_host, c->prog.p, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, c->prog_stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->prog_stream) != cudaSuccess)
+        return PFAAI_ERR_CONSTRUCT;
+    int g = 0;
+    while (g < n && c->prog_host[g] >= c->prog_need[g]) g++;
+    *rows_final = std::min<int64_t>(c->prog_rows, (int64_t)g * c->prog_gran);
     return PFAAI_OK;
 }
 

@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -62,24 +63,23 @@ inline std::string format_double(double v) {
     return s;
 }
 
-// header: <sep> + target names joined by <sep>; rows: query name, <sep>, values joined by <sep>; '\n' endings.
-// Returns false when the file cannot be opened / written.
-inline bool write_aji_csv(const std::string &path, const std::string &sep, const std::vector<std::string> &qryNames,
-                          const std::vector<std::string> &tgtNames, const double *matrix /*[nQ x nT] row-major*/) {
-    FILE *fp = std::fopen(path.c_str(), "w");
-    if (!fp) return false;
-    const size_t nQ = qryNames.size(), nT = tgtNames.size();
+namespace detail {
+inline bool write_header(FILE *fp, const std::string &sep, const std::vector<std::string> &tgtNames) {
     std::string hdr = sep;
-    for (size_t j = 0; j < nT; j++) { if (j) hdr += sep; hdr += tgtNames[j]; }
+    for (size_t j = 0; j < tgtNames.size(); j++) { if (j) hdr += sep; hdr += tgtNames[j]; }
     hdr += '\n';
-    bool ok = std::fwrite(hdr.data(), 1, hdr.size(), fp) == hdr.size();
-    const size_t batch = (size_t)std::max(1, omp_get_max_threads()) * 8;
-    std::vector<std::string> lines(batch);
-    for (size_t r0 = 0; r0 < nQ && ok; r0 += batch) {
-        const size_t r1 = std::min(nQ, r0 + batch);
+    return std::fwrite(hdr.data(), 1, hdr.size(), fp) == hdr.size();
+}
+// rows [r0, r1): formatted in parallel (OpenMP) in batches, written in order
+inline bool write_rows(FILE *fp, const std::string &sep, const std::vector<std::string> &qryNames, size_t nT, const double *matrix,
+                       size_t r0, size_t r1, std::vector<std::string> &lines) {
+    const size_t batch = lines.size();
+    bool ok = true;
+    for (size_t b0 = r0; b0 < r1 && ok; b0 += batch) {
+        const size_t b1 = std::min(r1, b0 + batch);
 #pragma omp parallel for schedule(dynamic, 1)
-        for (size_t r = r0; r < r1; r++) {
-            std::string &s = lines[r - r0];
+        for (size_t r = b0; r < b1; r++) {
+            std::string &s = lines[r - b0];
             s.clear();
             s.reserve(qryNames[r].size() + nT * 20 + 8);
             s += qryNames[r];
@@ -88,8 +88,54 @@ inline bool write_aji_csv(const std::string &path, const std::string &sep, const
             for (size_t j = 0; j < nT; j++) { if (j) s += sep; append_double(s, row[j]); }
             s += '\n';
         }
-        for (size_t r = r0; r < r1 && ok; r++) ok = std::fwrite(lines[r - r0].data(), 1, lines[r - r0].size(), fp) == lines[r - r0].size();
+        for (size_t r = b0; r < b1 && ok; r++) ok = std::fwrite(lines[r - b0].data(), 1, lines[r - b0].size(), fp) == lines[r - b0].size();
     }
+    return ok;
+}
+}  // namespace detail
+
+// header: <sep> + target names joined by <sep>; rows: query name, <sep>, values joined by <sep>; '\n' endings.
+// Returns false when the file cannot be opened / written.
+inline bool write_aji_csv(const std::string &path, const std::string &sep, const std::vector<std::string> &qryNames,
+                          const std::vector<std::string> &tgtNames, const double *matrix /*[nQ x nT] row-major*/) {
+    FILE *fp = std::fopen(path.c_str(), "w");
+    if (!fp) return false;
+    std::vector<std::string> lines((size_t)std::max(1, omp_get_max_threads()) * 8);
+    bool ok = detail::write_header(fp, sep, tgtNames);
+    ok = ok && detail::write_rows(fp, sep, qryNames, tgtNames.size(), matrix, 0, qryNames.size(), lines);
+    return (std::fclose(fp) == 0) && ok;
+}
+
+// The same file, written WHILE the matrix is being computed: poll(rows_final, finished) reports how many
+// leading rows of `matrix` are complete (pfaai_gpu_progress_poll); every batch of finished rows is formatted and written at
+// once, so formatting and file I/O overlap the GPU and the device-to-host stores of the later row blocks.
+// *overlapped_rows = rows that were written before the compute had finished.
+template <class Poll>
+inline bool write_aji_csv_streaming(const std::string &path, const std::string &sep, const std::vector<std::string> &qryNames,
+                                    const std::vector<std::string> &tgtNames, const double *matrix, Poll poll, size_t *overlapped_rows) {
+    FILE *fp = std::fopen(path.c_str(), "w");
+    if (!fp) return false;
+    const size_t nQ = qryNames.size();
+    std::vector<std::string> lines((size_t)std::max(1, omp_get_max_threads()) * 8);
+    bool ok = detail::write_header(fp, sep, tgtNames);
+    size_t written = 0, overlapped = 0;
+    while (ok && written < nQ) {
+        int64_t rows_final = 0; int finished = 0;
+        if (!poll(rows_final, finished)) { ok = false; break; }
+        const size_t upto = std::min(nQ, (size_t)std::max<int64_t>(rows_final, 0));
+        if (upto > written) {
+            ok = detail::write_rows(fp, sep, qryNames, tgtNames.size(), matrix, written, upto, lines);
+            if (!finished) overlapped = upto;
+            written = upto;
+        } else if (finished) {
+            break;                                                  // finished but rows missing: the caller reports the failure
+        } else {
+            struct timespec ts = {0, 500000};                       // 0.5 ms
+            nanosleep(&ts, nullptr);
+        }
+    }
+    if (overlapped_rows) *overlapped_rows = overlapped;
+    ok = ok && written == nQ;
     return (std::fclose(fp) == 0) && ok;
 }
 

@@ -36,7 +36,7 @@ struct AppParams {
     std::vector<std::string> qryGenomeSet;
     std::string dumpIndexPrefix, formatDoublesFile, indexCachePath;
     int device = 0, nGpus = 1;
-    bool refCompat = true, sameDevice = false;
+    bool refCompat = true, sameDevice = false, noStreamCsv = false;
 
     static bool is_file(const std::string &p) {
         struct stat st;
@@ -55,6 +55,7 @@ struct AppParams {
            << "  --device INT [0]            first CUDA device ordinal\n"
            << "  --gpus INT [1]              number of GPUs (devices device..device+gpus-1); output row blocks are sharded over them\n"
            << "  --no-ref-compat             query-DB mode: corrected T lookup (default reproduces the reference)\n"
+           << "  --no-stream-csv             write the CSV after the computation (default, one GPU all-vs-all: rows are written while later row blocks are computed)\n"
            << "  --index-cache TEXT          single-DB modes: device-ready index cache of the input DB (read if valid, else written)\n"
            << "  --dump-index TEXT           host only: write PREFIX.{lc,f,t}.bin and exit\n";
     }
@@ -99,6 +100,7 @@ struct AppParams {
                 nGpus = std::max(1, std::atoi(d.c_str()));
             } else if (a == "--same-device") sameDevice = true;   // test hook: all shards on one GPU
             else if (a == "--no-ref-compat") refCompat = false;
+            else if (a == "--no-stream-csv") noStreamCsv = true;
             else if (a == "--index-cache") {
                 if (!need(indexCachePath)) return fail(114, "--index-cache: 1 required TEXT missing");
             } else if (a == "--dump-index") {
@@ -168,7 +170,14 @@ void printOutput(const DataStructBase &pfdata, const ParFAAIImpl &impl, const Ap
     std::printf("Writing output with %d query genomes and %d target genomes. \n", pfdata.qrySetSize(), pfdata.tgtSetSize());
     std::fflush(stdout);
     PhaseTimer tm;
-    if (!write_aji_csv(args.pathToOutputFile, args.outFieldSeparator, pfdata.refQuerySet(), pfdata.refTargetSet(), impl.getMatrix().data()))
+    if (impl.streamed()) {
+        // the rows were formatted and written by the writer thread while the GPU computed (pfaai_driver.hpp, csv_writer.hpp)
+        if (!impl.streamOk()) std::cerr << "Error in writing " << args.pathToOutputFile << std::endl;
+        std::printf("CSV output          : %10.3f ms; (streamed: %zu of %d rows were written while the tile kernel was still running)\n",
+                    impl.streamTailMs(), impl.streamOverlapRows(), pfdata.qrySetSize());
+        return;
+    }
+    if (!write_aji_csv(args.pathToOutputFile, args.outFieldSeparator, pfdata.refQuerySet(), pfdata.refTargetSet(), impl.matrixData()))
         std::cerr << "Error in writing " << args.pathToOutputFile << std::endl;
     std::printf("CSV output          : %10.3f ms;\n", tm.lap_ms());
 }
@@ -178,6 +187,7 @@ template <typename DataT> int construct_run_print(DataT &data, const AppParams &
     const pfaai_status rc = data.construct();    // (the reference tests the wrong variable here; we return the code)
     if (rc != PFAAI_OK) return rc;
     ParFAAIImpl impl(data);
+    if (!args.pathToOutputFile.empty() && !args.noStreamCsv) impl.setStreamingOutput(args.pathToOutputFile, args.outFieldSeparator);
     const int rrc = impl.run();
     if (rrc != PFAAI_OK) return rrc;
 #ifndef NDEBUG

@@ -12,8 +12,11 @@
 // run() executes the tile kernel and brings back the dense AJI matrix (plus JAC/AJI lists for small inputs).
 // All CUDA work happens behind the C-ABI; this header contains no CUDA.  No CPU fallback.
 #pragma once
+#include <atomic>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <iomanip>
 #include <iostream>
 #include <memory>
@@ -368,9 +371,29 @@ class ParFAAIImpl {
     std::vector<double> m_AJI;
     std::vector<double> m_matrix;   // [qrySetSize x tgtSetSize] row-major == printOutput's ajiMatrix (main.cpp:143-154)
     bool m_haveLists = false;
+    // streaming CSV output: one GPU, all-vs-all -- the matrix lives in page-locked memory, the tile kernel
+    // stores straight into it and a writer thread formats / writes every finished block of rows while later blocks are computed
+    std::string m_streamPath, m_streamSep;
+    double *m_pinned = nullptr;
+    size_t m_pinnedBytes = 0;
+    bool m_streamed = false, m_streamOk = false;
+    size_t m_streamOverlapRows = 0;
+    double m_streamTailMs = 0.0;
 
   public:
     explicit ParFAAIImpl(const DataStructBase &ds) : c_pfDSRef(ds) {}
+    ParFAAIImpl(const ParFAAIImpl &) = delete;
+    ParFAAIImpl &operator=(const ParFAAIImpl &) = delete;
+    ~ParFAAIImpl() {
+        if (m_pinned) { pfaai_gpu_host_unregister(m_pinned, m_pinnedBytes); std::free(m_pinned); }
+    }
+    // ask for the CSV to be written while the matrix is computed (takes effect for one GPU in all-vs-all mode)
+    void setStreamingOutput(const std::string &path, const std::string &sep) { m_streamPath = path; m_streamSep = sep; }
+    bool streamed() const { return m_streamed; }
+    bool streamOk() const { return m_streamOk; }
+    size_t streamOverlapRows() const { return m_streamOverlapRows; }
+    double streamTailMs() const { return m_streamTailMs; }
+    const double *matrixData() const { return m_pinned ? m_pinned : m_matrix.data(); }
 
     int computeJAC() {
         PhaseTimer tm;
@@ -380,15 +403,53 @@ class ParFAAIImpl {
         const int64_t np = c_pfDSRef.nGenomePairs();
         const std::vector<int32_t> &q = c_pfDSRef.queryIds();
         const size_t nQ = (size_t)c_pfDSRef.qrySetSize(), nT = (size_t)c_pfDSRef.tgtSetSize();
-        m_matrix.assign(nQ * nT, 0.0);
         pfaai_timings_t t;
+        // streaming: a page-locked matrix (the tile kernel's stores are the D2H transfer) + a writer thread behind the progress counters
+        bool stream = n == 1 && !m_streamPath.empty() && c_pfDSRef.mode() == PFAAI_ALL_VS_ALL && nQ * nT > 0;
+        if (stream) {
+            const size_t bytes = (nQ * nT * sizeof(double) + 4095) & ~(size_t)4095;
+            void *mem = nullptr;
+            if (posix_memalign(&mem, 4096, bytes) == 0 && mem) {
+                std::memset(mem, 0, bytes);                                  // fault the pages in before they are page-locked
+                if (pfaai_gpu_host_register(mem, bytes) == PFAAI_OK) { m_pinned = static_cast<double *>(mem); m_pinnedBytes = bytes; }
+                else std::free(mem);
+            }
+            stream = m_pinned != nullptr && pfaai_gpu_set_progress(ctx, 1) == PFAAI_OK;
+        }
+        if (!m_pinned) m_matrix.assign(nQ * nT, 0.0);
         if (n == 1) {
             m_haveLists = np <= JAC_LIST_MAX_PAIRS;
             std::vector<pfaai_jac_t> jac;
             if (m_haveLists) { jac.resize((size_t)np); m_AJI.assign((size_t)np, 0.0); }
+            std::atomic<int> compute_state{0};                               // 0 = running, 1 = returned OK, 2 = failed
+            std::thread writer;
+            std::chrono::steady_clock::time_point t_done;
+            if (stream) {
+                writer = std::thread([&] {
+                    auto poll = [&](int64_t &rows, int &fin) {
+                        const int st = compute_state.load(std::memory_order_acquire);
+                        if (st == 2) return false;
+                        if (st == 1) { rows = (int64_t)nQ; fin = 1; return true; }
+                        int f = 0;
+                        if (pfaai_gpu_progress_poll(ctx, &rows, &f) != PFAAI_OK) rows = 0;   // not fatal: the rows come when the compute ends
+                        fin = 0;
+                        return true;
+                    };
+                    m_streamOk = write_aji_csv_streaming(m_streamPath, m_streamSep, c_pfDSRef.refQuerySet(), c_pfDSRef.refTargetSet(), m_pinned, poll,
+                                                         &m_streamOverlapRows);
+                });
+            }
             const int rc = pfaai_gpu_compute(ctx, c_pfDSRef.mode(), q.empty() ? nullptr : q.data(), (int)q.size(), c_pfDSRef.computeFlags(),
-                                             m_matrix.data(), m_haveLists ? jac.data() : nullptr, m_haveLists ? m_AJI.data() : nullptr,
-                                             nullptr);
+                                             m_pinned ? m_pinned : m_matrix.data(), m_haveLists ? jac.data() : nullptr,
+                                             m_haveLists ? m_AJI.data() : nullptr, nullptr);
+            if (stream) {
+                compute_state.store(rc == PFAAI_OK ? 1 : 2, std::memory_order_release);
+                t_done = std::chrono::steady_clock::now();
+                writer.join();
+                m_streamTailMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_done).count();
+                m_streamed = rc == PFAAI_OK;
+                pfaai_gpu_set_progress(ctx, 0);
+            }
             if (rc != PFAAI_OK) { std::cerr << "Error in JAC Construction ; " << pfaai_gpu_last_error(ctx) << std::endl; return rc; }
             m_JAC.resize(jac.size());
             for (size_t i = 0; i < jac.size(); i++) { m_JAC[i].genomeA = jac[i].gA; m_JAC[i].genomeB = jac[i].gB; m_JAC[i].S = jac[i].S; m_JAC[i].N = jac[i].N; }
@@ -436,7 +497,7 @@ class ParFAAIImpl {
             }
             pfaai_gpu_get_timings(ctx, &t);
         }
-        const double jac_ms = tm.lap_ms();
+        const double jac_ms = tm.lap_ms() - m_streamTailMs;                // the writer's tail after the last tile is CSV time, not JAC time
         std::fflush(stdout);
         print_ref_phase("JAC Construction    : ", jac_ms);                 // algorithm_impl.hpp:304
         std::printf("  JAC on %d GPU(s)     : %10.3f ms; (GPU 0: %s, row slabs %.3f ms, dictionaries %.3f ms, dense-path prep %.3f ms, tile kernel %.3f ms over %d tiles, D2H %.3f ms)\n",

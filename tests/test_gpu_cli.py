@@ -97,6 +97,23 @@ def test_against_reference_binary_on_synthetic_db(cli, tmp_path):
         assert open(a, "rb").read() == open(b, "rb").read(), extra
 
 
+def test_streamed_csv_equals_the_csv_written_afterwards(cli, tmp_path):
+    """One GPU, all-vs-all: by default the CSV rows are written by a writer thread while later row blocks are still computed
+    (progress counters of the tile kernel); --no-stream-csv writes after the computation.  Same bytes; the streamed run says so."""
+    from parfastaai_b200 import fastaai_db, synth
+    N, P = 1800, 12
+    off, vals = synth.generate(N, P, seed=5)
+    gn, sn = fastaai_db.synthetic_names(N, P)
+    db = str(tmp_path / "syn.db")
+    fastaai_db.write_db(db, gn, sn, off, vals)
+    a, b = str(tmp_path / "streamed.csv"), str(tmp_path / "after.csv")
+    r1 = run(cli, db, a)
+    r2 = run(cli, db, b, "--no-stream-csv")
+    assert "streamed:" in r1.stdout and "streamed:" not in r2.stdout
+    assert open(a, "rb").read() == open(b, "rb").read()
+    assert open(a, "rb").read().count(b"\n") == N + 1
+
+
 def test_index_cache_gives_identical_csv(cli, tmp_path):
     """--index-cache: a run served from the cache (SQLite never opened) writes the same CSV bytes, in all-vs-all and in
     query-subset mode (the cache holds the whole database)."""

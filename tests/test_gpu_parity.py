@@ -90,6 +90,54 @@ def test_lc_built_on_the_device_from_tetramer_keys(pf, name):
     ctx.close()
 
 
+@pytest.mark.parametrize("path", ["lists", "mma"])
+def test_progress_counters_report_only_finished_rows(pf, path):
+    """Streaming output (pfaai_gpu_set_progress / pfaai_gpu_progress_poll): while compute() runs, another thread polls; every
+    row reported final is copied at that moment and must equal the finished matrix bit for bit (direct AND mirrored cells);
+    the reported prefix never shrinks and ends at G."""
+    import threading
+    import torch
+    from parfastaai_b200 import synth
+    N, P = 2600, 40
+    off, vals = synth.generate(N, P, seed=11, dense=(path == "mma"))
+    Lc, F = synth.to_reference(N, P, off, vals)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    ctx.set_path(pf.PATH_LISTS if path == "lists" else pf.PATH_MMA)
+    want = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
+    pin = torch.full((N, N), -7.0, dtype=torch.float64).pin_memory()
+    M = pin.numpy()
+    ctx.set_progress(True)
+    snaps, seen, stop = [], [0], threading.Event()
+
+    def poller():
+        while not stop.is_set():
+            r, fin = ctx.progress_poll()
+            assert r >= seen[-1]
+            if r > seen[-1]:
+                snaps.append((seen[-1], r, M[seen[-1]:r].copy(), fin))
+                seen.append(r)
+            if fin:
+                break
+
+    th = threading.Thread(target=poller)
+    th.start()
+    ctx.compute(pf.ALL_VS_ALL, want_jac=False, matrix_out=M)
+    th.join(timeout=60)
+    stop.set()
+    assert not th.is_alive()
+    r, fin = ctx.progress_poll()
+    assert fin and r == N and seen[-1] == N
+    assert np.array_equal(M, want)
+    for a, b, rows, _fin in snaps:
+        assert np.array_equal(rows, want[a:b]), (a, b)
+    assert len(snaps) >= 1
+    ctx.set_progress(False)
+    assert ctx.progress_poll() == (0, False)
+    ctx.close()
+
+
 def test_device_ready_lists_import_equals_the_built_index(pf, orc):
     """pfaai_gpu_import_lists (the index cache's fast path): the lists exported from a built context, imported into a fresh one
     -- no F, no K1-K3, no sort -- give the same arrays and bit-identical results in all three modes; damaged lists fail loudly."""
