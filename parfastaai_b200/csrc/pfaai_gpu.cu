@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "aji_tile.cuh"
@@ -727,10 +728,13 @@ int pfaai_gpu_route_local(pfaai_gpu_ctx **hs, int n) {
         if (!cs[i] || cs[i]->n_shards != n || cs[i]->shard != i) { set_error(cs[i], "route_local: contexts must be the shards 0..n-1 in order"); return PFAAI_ERR_CONSTRUCT; }
         PF_TRY(pfaai_gpu_route_prepare(hs[i], &rt[i]));
     }
+    // all peer copies first (every destination's copies on its own stream: they overlap across the GPUs) ...
+    std::vector<int64_t> totals(n, 0);
     for (int d = 0; d < n; d++) {
         Ctx *dst = cs[d];
         int64_t total = 0;
         for (int si = 0; si < n; si++) total += rt[si].send_offset[d + 1] - rt[si].send_offset[d];
+        totals[d] = total;
         void *recv = nullptr;
         PF_TRY(pfaai_gpu_route_recv_buffer(hs[d], total, &recv));
         int64_t at = 0;
@@ -742,9 +746,23 @@ int pfaai_gpu_route_local(pfaai_gpu_ctx **hs, int n) {
                                                  sizeof(uint64_t) * (size_t)cnt, dst->stream));
             at += cnt;
         }
-        PF_CUDA(dst, cudaStreamSynchronize(dst->stream));
-        PF_TRY(pfaai_gpu_build_routed(hs[d], total));
     }
+    // ... then every shard's histogram / sort / dictionary build on its own host thread (pfaai_gpu_build_routed is
+    // host-synchronous; one thread per context keeps the N device builds concurrent)
+    std::vector<int> rcs(n, PFAAI_OK);
+    auto work = [&](int d) {
+        if (cudaSetDevice(cs[d]->device) != cudaSuccess || cudaStreamSynchronize(cs[d]->stream) != cudaSuccess) {
+            set_error(cs[d], "route_local: peer copies failed"); rcs[d] = PFAAI_ERR_CONSTRUCT; return;
+        }
+        rcs[d] = pfaai_gpu_build_routed(hs[d], totals[d]);
+    };
+    {
+        std::vector<std::thread> th;
+        for (int d = 1; d < n; d++) th.emplace_back(work, d);
+        work(0);
+        for (auto &t : th) t.join();
+    }
+    for (int d = 0; d < n; d++) if (rcs[d] != PFAAI_OK) return rcs[d];
     return PFAAI_OK;
 }
 

@@ -395,6 +395,18 @@ class ParFAAIImpl {
     double streamTailMs() const { return m_streamTailMs; }
     const double *matrixData() const { return m_pinned ? m_pinned : m_matrix.data(); }
 
+    // the dense matrix in page-locked (and device-mapped) host memory; false = not possible, callers fall back to m_matrix
+    bool pinGlobalMatrix(size_t nQ, size_t nT) {
+        if (m_pinned) return true;
+        const size_t bytes = (nQ * nT * sizeof(double) + 4095) & ~(size_t)4095;
+        void *mem = nullptr;
+        if (bytes == 0 || posix_memalign(&mem, 4096, bytes) != 0 || !mem) return false;
+        std::memset(mem, 0, bytes);                                          // fault the pages in before they are page-locked
+        if (pfaai_gpu_host_register(mem, bytes) != PFAAI_OK) { std::free(mem); return false; }
+        m_pinned = static_cast<double *>(mem); m_pinnedBytes = bytes;
+        return true;
+    }
+
     int computeJAC() {
         PhaseTimer tm;
         const int n = c_pfDSRef.nDevices();
@@ -406,17 +418,8 @@ class ParFAAIImpl {
         pfaai_timings_t t;
         // streaming: a page-locked matrix (the tile kernel's stores are the D2H transfer) + a writer thread behind the progress counters
         bool stream = n == 1 && !m_streamPath.empty() && c_pfDSRef.mode() == PFAAI_ALL_VS_ALL && nQ * nT > 0;
-        if (stream) {
-            const size_t bytes = (nQ * nT * sizeof(double) + 4095) & ~(size_t)4095;
-            void *mem = nullptr;
-            if (posix_memalign(&mem, 4096, bytes) == 0 && mem) {
-                std::memset(mem, 0, bytes);                                  // fault the pages in before they are page-locked
-                if (pfaai_gpu_host_register(mem, bytes) == PFAAI_OK) { m_pinned = static_cast<double *>(mem); m_pinnedBytes = bytes; }
-                else std::free(mem);
-            }
-            stream = m_pinned != nullptr && pfaai_gpu_set_progress(ctx, 1) == PFAAI_OK;
-        }
-        if (!m_pinned) m_matrix.assign(nQ * nT, 0.0);
+        if (stream) stream = pinGlobalMatrix(nQ, nT) && pfaai_gpu_set_progress(ctx, 1) == PFAAI_OK;
+        if (!m_pinned && n == 1) m_matrix.assign(nQ * nT, 0.0);
         if (n == 1) {
             m_haveLists = np <= JAC_LIST_MAX_PAIRS;
             std::vector<pfaai_jac_t> jac;
@@ -454,9 +457,30 @@ class ParFAAIImpl {
             m_JAC.resize(jac.size());
             for (size_t i = 0; i < jac.size(); i++) { m_JAC[i].genomeA = jac[i].gA; m_JAC[i].genomeB = jac[i].gB; m_JAC[i].S = jac[i].S; m_JAC[i].N = jac[i].N; }
             pfaai_gpu_get_timings(ctx, &t);
+        } else if (c_pfDSRef.mode() == PFAAI_ALL_VS_ALL && pinGlobalMatrix(nQ, nT)) {
+            // several GPUs, all-vs-all: ONE page-locked G x G host matrix; every GPU's tile kernel stores the cells of its own row
+            // blocks AND their mirror images straight into it (pfaai_gpu_set_global_matrix): no device copy of the matrix, no
+            // gather, no host mirror pass -- the matrix is complete when the last GPU returns
+            m_haveLists = false; m_JAC.clear(); m_AJI.clear();
+            std::vector<int> rcs(n, PFAAI_OK);
+            auto work = [&](int k) {
+                pfaai_gpu_ctx *c = c_pfDSRef.ctx(k);
+                int rc = pfaai_gpu_set_global_matrix(c, 1);
+                if (rc == PFAAI_OK) rc = pfaai_gpu_compute(c, PFAAI_ALL_VS_ALL, nullptr, 0, c_pfDSRef.computeFlags(), m_pinned, nullptr, nullptr, nullptr);
+                pfaai_gpu_set_global_matrix(c, 0);
+                rcs[k] = rc;
+            };
+            std::vector<std::thread> th;
+            for (int k = 1; k < n; k++) th.emplace_back(work, k);
+            work(0);
+            for (auto &x : th) x.join();
+            for (int k = 0; k < n; k++)
+                if (rcs[k] != PFAAI_OK) { std::cerr << "Error in JAC Construction ; " << pfaai_gpu_last_error(c_pfDSRef.ctx(k)) << std::endl; return rcs[k]; }
+            pfaai_gpu_get_timings(ctx, &t);
         } else {
             // every GPU computes its own output row blocks (all-vs-all: upper triangle only); the host scatters the compact
             // parts into the dense matrix and mirrors -- "only the final matrix is gathered to the host writer"
+            if (m_matrix.empty()) m_matrix.assign(nQ * nT, 0.0);
             m_haveLists = false; m_JAC.clear(); m_AJI.clear();
             std::vector<int> rcs(n, PFAAI_OK);
             std::vector<std::vector<double>> parts(n);
@@ -467,7 +491,7 @@ class ParFAAIImpl {
                 int rc = pfaai_gpu_compute_device(c, c_pfDSRef.mode(), q.empty() ? nullptr : q.data(), (int)q.size(), c_pfDSRef.computeFlags());
                 int64_t rows = 0, cols = 0, cnt = 0;
                 if (rc == PFAAI_OK) rc = pfaai_gpu_matrix_shape(c, &rows, &cols);
-                if (rc == PFAAI_OK) { parts[k].resize((size_t)rows * cols); rc = pfaai_gpu_download_matrix(c, parts[k].data()); }
+                if (rc == PFAAI_OK && rows * cols > 0) { parts[k].resize((size_t)rows * cols); rc = pfaai_gpu_download_matrix(c, parts[k].data()); }   // a shard may own no row block
                 if (rc == PFAAI_OK) rc = pfaai_gpu_shard_layout(c, &axes[k], &cnt, nullptr);
                 if (rc == PFAAI_OK) { ids[k].resize((size_t)cnt); rc = pfaai_gpu_shard_layout(c, &axes[k], &cnt, ids[k].data()); }
                 rcs[k] = rc;
