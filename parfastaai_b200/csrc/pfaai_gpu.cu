@@ -1571,12 +1571,20 @@ int pfaai_gpu_compute(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_
     // a pinned (page-locked, mapped) host matrix is written by the tile kernel itself: the D2H transfer is the kernel's
     // store stream and overlaps the computation; pageable memory goes through a device buffer + one copy
     double *direct_dev = nullptr;
+    // the pointer query needs the context's device current on THIS thread (a fresh host thread -- one per context in the C++
+    // driver -- has none yet, and the query then does not recognise page-locked memory: the matrix would silently take the
+    // staged path and, for a shared global matrix, overwrite the other shards' cells)
+    PF_CUDA(c, cudaSetDevice(c->device));
     if (aji_matrix) {
         cudaPointerAttributes attr;
         if (cudaPointerGetAttributes(&attr, aji_matrix) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer)
             direct_dev = reinterpret_cast<double *>(attr.devicePointer);
         else
             cudaGetLastError();
+    }
+    if (aji_matrix && !direct_dev && c->global_out && c->n_shards > 1 && mode == PFAAI_ALL_VS_ALL) {
+        set_error(c, "compute: a shared global matrix must be page-locked, device-mapped host memory (pfaai_gpu_host_register)");
+        return PFAAI_ERR_CONSTRUCT;
     }
     PF_TRY(compute_internal(c, mode, qry_ids, n_qry, flags, want_sn, counts != nullptr, m, direct_dev));
     c->tm.d2h_ms = 0.f;
