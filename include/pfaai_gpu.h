@@ -99,7 +99,9 @@ int  pfaai_gpu_set_shard(pfaai_gpu_ctx *ctx, int shard, int n_shards);
  * processes of a box -- can address) and stores its cells AND their mirror images M[j][i] straight into it.  The shards' cell
  * sets are disjoint and together cover the whole matrix (zero diagonal included), so when the last shard returns the matrix is
  * complete in host memory: no gather, no host-side mirror pass (src/main.cpp:143-154 done by the kernels' own stores).
- * pfaai_gpu_matrix_shape then reports G x G.  Off (default): compact per-shard matrices as described above. */
+ * pfaai_gpu_matrix_shape then reports G x G.  Off (default): compact per-shard matrices as described above.
+ * A PAGEABLE matrix goes through a device copy of the whole G x G matrix (zeros outside the shard's cells) and one download:
+ * correct for a matrix private to the shard, but it would overwrite the other shards' cells of a SHARED one -- page-lock it. */
 int  pfaai_gpu_set_global_matrix(pfaai_gpu_ctx *ctx, int on);
 /* Page-lock (and map for device access) a host range the caller allocated itself -- e.g. the POSIX shared-memory mapping of
  * the global matrix above, once in every process that stores into it.  The range is registered in 1 GiB pieces (one

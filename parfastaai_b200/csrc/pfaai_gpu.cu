@@ -1582,10 +1582,6 @@ int pfaai_gpu_compute(pfaai_gpu_ctx *h, int mode, const int32_t *qry_ids, int n_
         else
             cudaGetLastError();
     }
-    if (aji_matrix && !direct_dev && c->global_out && c->n_shards > 1 && mode == PFAAI_ALL_VS_ALL) {
-        set_error(c, "compute: a shared global matrix must be page-locked, device-mapped host memory (pfaai_gpu_host_register)");
-        return PFAAI_ERR_CONSTRUCT;
-    }
     PF_TRY(compute_internal(c, mode, qry_ids, n_qry, flags, want_sn, counts != nullptr, m, direct_dev));
     c->tm.d2h_ms = 0.f;
     if (aji_matrix && c->out_on_device) PF_TRY(pfaai_gpu_download_matrix(h, aji_matrix));
