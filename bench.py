@@ -331,7 +331,10 @@ def main():
                     help="N>1: every rank builds the whole index (the pre-partitioning path) instead of pfaai_gpu_build_partitioned")
     ap.add_argument("--sliced-index", action="store_true",
                     help="N>1: routed build -- every rank keeps only its 1/N slice of F resident, the postings travel to the rank that "
-                         "owns their genome by an NCCL all-to-all (no all-gather of F, no filter passes)")
+                         "owns their genome by an NCCL all-to-all (no all-gather of F, no filter passes).  Default at N >= 8, where it "
+                         "was measured faster end to end (316.5 vs 335.4 ms per step at config 5, same device-resident step); at 2 and 4 "
+                         "GPUs the partitioned build on the all-gathered F is at least as fast (DESIGN.md section 6)")
+    ap.add_argument("--no-sliced-index", action="store_true", help="N>=8: the partitioned build on the all-gathered F instead of the routed build")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: finish the dictionary exchange before the tile kernel starts")
     ap.add_argument("--verify", action="store_true", help="N>1: gather the shards on rank 0 and compare with an unsharded compute")
     ap.add_argument("--dense", action="store_true",
@@ -507,9 +510,9 @@ def main():
             F_slice_pin[:8 * (hi - lo)].copy_(F_dev[8 * lo:8 * hi], non_blocking=True)
             Lc_pin_r.copy_(Lc_dev, non_blocking=True)
         stream.synchronize()
-        if rank == 0 and not (args.verify and args.sliced_index):
+        if rank == 0 and not (args.verify and (args.sliced_index or world >= 8)):
             del F_pin, F
-        sliced = args.sliced_index and not args.replicated_build and args.path != "mma"
+        sliced = (args.sliced_index or (world >= 8 and not args.no_sliced_index)) and not args.replicated_build and args.path != "mma"
         if sliced:
             # from here on the context holds only this rank's slice of F (the buffer of the full F is reused)
             fs_ptr, lcs_ptr = ctx.index_slice_buffers(P, G, nF, lo, hi - lo)
@@ -766,10 +769,11 @@ def main():
                                f"SURVEY 8(d) recipe, {'DENSE real-like family, ' if args.dense else ''}seed {SEED})",
                    "family": "dense" if args.dense else "sparse",
                    "genomes": G, "scps": P, "postings": nF, "pairs": pairs_total, "mode": "all-vs-all",
-                   "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); F replicated "
-                                   f"on every GPU (N>1, inside the e2e region: every rank uploads its 1/N slice of F, NCCL all-gather over NVLink); "
-                                   + ("routed build: every rank keeps only its 1/N slice of F, the postings go to the rank that owns their genome by "
-                                      "an NCCL all-to-all; " if sliced else "")
+                   "parallelism": (f"output row blocks (384 genomes, folded assignment) sharded over {world} rank(s); "
+                                   + ("routed build: every rank uploads and keeps only its 1/N slice of F (inside the e2e region), the postings go "
+                                      "to the rank that owns their genome by an NCCL all-to-all; " if sliced else
+                                      "F replicated on every GPU (N>1, inside the e2e region: every rank uploads its 1/N slice of F, NCCL all-gather "
+                                      "over NVLink); ")
                                    + ("partitioned index build: every rank sorts / builds the column dictionaries of its own row blocks, "
                                       "the dictionaries are all-gathered over NVLink (NCCL, in place, on a second stream) while the tiles on the rank's "
                                       "own dictionaries are computed; " if partitioned else
