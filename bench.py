@@ -817,7 +817,10 @@ def main():
                             "ncu": onchip},
         "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
                       "exchange": exchange_ms, "exchange_bytes_per_rank": exchange_bytes,
-                      "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"]},
+                      "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"],
+                      # the same tile kernel inside the e2e step, where its stores go to page-locked HOST memory (rank 0's last step):
+                      # the difference to "tile" is what the host-side write bandwidth costs when N GPUs store 8*G*G bytes at once
+                      "e2e_tile": tm_e2e["tile_ms"], "e2e_build": tm_e2e["build_ms"]},
     }
 
     line["verify"] = vq

@@ -161,7 +161,7 @@ class DataStructBase {
         std::vector<std::string> errs(n);
         // several GPUs, all-vs-all: routed + partitioned build -- every GPU gets a slice of F, sorts the postings and builds the
         // column dictionaries of its own row blocks only; postings and dictionaries move by peer copies; otherwise replicated build
-        const bool partitioned = routed_possible && !m_ix.haveLists();
+        bool partitioned = routed_possible && !m_ix.haveLists();
         auto work = [&](int k) {
             int rc = pfaai_gpu_create(&m_ctxs[k], m_devices[k], 0);
             if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(nullptr); return; }
@@ -195,13 +195,31 @@ class DataStructBase {
         pfaai_gpu_ctx *m_ctx = m_ctxs[0];
         int rc;
         if (partitioned) {
-            rc = pfaai_gpu_route_local(m_ctxs.data(), n);                       // group by owner, peer copies, sort + own dictionaries
+            // (PFAAI_TEST_FAIL_ROUTED: test hook for the fall-back below)
+            rc = std::getenv("PFAAI_TEST_FAIL_ROUTED") ? (int)PFAAI_ERR_CONSTRUCT
+                                                       : pfaai_gpu_route_local(m_ctxs.data(), n);   // group by owner, peer copies, sort + own dictionaries
             if (rc == PFAAI_OK) rc = pfaai_gpu_exchange_local(m_ctxs.data(), n);  // dictionaries to every GPU
             if (rc != PFAAI_OK) {
+                // e.g. a skewed database whose heaviest shard overflows the agreed dictionary chunk: do not fail the run, fall
+                // back to the replicated build (every GPU uploads F and builds the whole index; the compute stays sharded)
                 std::string msg;
                 for (int k = 0; k < n; k++) { const char *e = pfaai_gpu_last_error(m_ctxs[k]); if (e && *e) { msg = e; break; } }
-                std::cerr << "Error in device index routing / exchange ; " << msg << std::endl;
-                return m_errorCode = (pfaai_status)rc;
+                std::cerr << "Warning: routed / partitioned index build not possible (" << msg << "); falling back to the replicated build" << std::endl;
+                partitioned = false;
+                std::vector<std::thread> th;
+                auto rebuild = [&](int k) {
+                    int r = pfaai_gpu_upload_index(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(), nullptr);
+                    if (r == PFAAI_OK) r = pfaai_gpu_build(m_ctxs[k]);
+                    rcs[k] = r;
+                };
+                for (int k = 1; k < n; k++) th.emplace_back(rebuild, k);
+                rebuild(0);
+                for (auto &t : th) t.join();
+                for (int k = 0; k < n; k++)
+                    if (rcs[k] != PFAAI_OK) {
+                        std::cerr << "Error in device index build (GPU " << m_devices[k] << ") ; " << pfaai_gpu_last_error(m_ctxs[k]) << std::endl;
+                        return m_errorCode = (pfaai_status)rcs[k];
+                    }
             }
         }
         m_Lp.resize(NTETRAMERS);
