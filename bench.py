@@ -343,7 +343,7 @@ def main():
                     help="N>1: keep compact per-rank matrices (upper-triangle cells only) instead of one shared host matrix")
     ap.add_argument("--tau", type=int, default=0, help="dense path: posting-list length threshold (0 = cost model)")
     ap.add_argument("--path", default="auto", choices=["auto", "lists", "mma"],
-                    help="tile path: lists = dictionary walk (K4), mma = dense tcgen05 contraction + patches (K5), auto = by density")
+                    help="tile path: lists = dictionary walk (K4), mma = dense tcgen05 contraction + in-kernel sparse walk (K5), auto = by density")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         log("[bench] note: fewer than 3 warm-up steps requested; the timing rules ask for W >= 3")
@@ -791,7 +791,7 @@ def main():
         "gpu_launches": int(launches),
         "clocks": {"sm_mhz": clocks["sm_mhz"], "sm_max_mhz": clocks["sm_max_mhz"], "reasons": clocks["reasons"],
                    "samples": clocks["samples"], "power_w_max": clocks.get("power_w_max")},
-        "path": {"tile_kernel": "aji_mma_kernel (K5: tcgen05 u8 dense contraction + patch records)" if tm["path"] == pf.PATH_MMA
+        "path": {"tile_kernel": "aji_mma_kernel (K5: tcgen05 u8 dense contraction + in-kernel sparse walk)" if tm["path"] == pf.PATH_MMA
                  else "aji_tile_kernel (K4: dictionary walk, bit-sliced counters)",
                  "requested": args.path, "dense_tau": tm["dense_tau"], "dense_k_sum": tm["dense_k_sum"],
                  "sparse_items": tm["sparse_items"], "prep_ms": tm["prep_ms"]},

@@ -74,7 +74,7 @@ typedef struct {
     int64_t dense_k_sum; /* dense path: dense tetramers over all SCPs (padded to 32 per SCP)                    */
     int64_t sparse_items; /* dense path: postings on non-dense tetramers (walked in-kernel as sparse row items)  */
     int64_t e_size;      /* |E| = sum over posting lists of n(n-1)/2 (the reference's E array, all-vs-all), when known, else -1 */
-    float prep_ms;       /* dense path: list lengths + dense ids + operand images + patches inside compute      */
+    float prep_ms;       /* dense path: list lengths, dense ids, operand images, sparse items + dictionaries */
     int32_t reserved2_;
 } pfaai_timings_t;
 
@@ -113,11 +113,11 @@ int  pfaai_gpu_host_unregister(void *ptr, size_t bytes);
 /* Which tile kernel the next computes use (BASELINE north_star: "ncu evidence decides between the two paths"):
  *   PFAAI_PATH_AUTO   (default) a cost model on the measured posting-list length distribution picks per compute call;
  *   PFAAI_PATH_LISTS  the dictionary walk (aji_tile_kernel: bit-sliced counters, no tensor cores) -- sparse inputs;
- *   PFAAI_PATH_MMA    the dense contraction (aji_mma_kernel: 0/1 u8 operands on tcgen05 tensor cores + exact patch records
- *                     for the non-dense tetramers) -- real-like inputs whose per-SCP vocabulary is dense.  Needs an
+ *   PFAAI_PATH_MMA    the dense contraction (aji_mma_kernel: 0/1 u8 operands on tcgen05 tensor cores + an exact in-kernel
+ *                     sparse walk for the non-dense tetramers) -- real-like inputs whose per-SCP vocabulary is dense.  Needs an
  *                     unpartitioned build and at most 255 SCPs; fails with PFAAI_ERR_CONSTRUCT otherwise.
  * Both paths produce identical counts / S / N / AJI.  tau > 0 fixes the density threshold of the dense path (posting lists of at
- * least tau genomes become tensor-core columns, shorter ones patch records); 0 = chosen by the cost model. */
+ * least tau genomes become tensor-core columns, shorter ones are counted by the sparse walk); 0 = chosen by the cost model. */
 enum pfaai_path { PFAAI_PATH_AUTO = 0, PFAAI_PATH_LISTS = 1, PFAAI_PATH_MMA = 2 };
 int  pfaai_gpu_set_path(pfaai_gpu_ctx *ctx, int path, int tau);
 /* Streaming output (printOutput, main.cpp:156-174): with progress enabled, an unsharded ALL_VS_ALL compute

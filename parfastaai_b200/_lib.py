@@ -181,7 +181,7 @@ class PfaaiGpu:
 
     def set_path(self, path=PATH_AUTO, tau=0):
         """Tile path of the next computes: PATH_AUTO (cost model), PATH_LISTS (dictionary walk), PATH_MMA (tcgen05 dense
-        contraction + patches); tau > 0 fixes the dense path's posting-list length threshold."""
+        contraction + sparse walk); tau > 0 fixes the dense path's posting-list length threshold."""
         self._check(self._L.pfaai_gpu_set_path(self._h, int(path), int(tau)), "set_path")
 
     def e_size(self):

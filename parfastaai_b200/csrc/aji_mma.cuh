@@ -67,7 +67,7 @@ constexpr int MM_STG_PITCH = 33;                      // output staging [128][33
 constexpr int MM_SMEM_MISC = 1024;
 constexpr int MM_SMEM_CT = MM_CT_RING * MM_COLS * 4;
 constexpr int MM_SMEM_CNT = 4 * MM_CNT_QUAD;              // 34816 >= 128*33*8 = 33792 (staging shares it)
-static_assert(MM_SMEM_CNT >= MM_ROWS * MM_STG_PITCH * 8, "output staging does not fit the patch-counter area");
+static_assert(MM_SMEM_CNT >= MM_ROWS * MM_STG_PITCH * 8, "output staging does not fit the sparse-counter area");
 constexpr int MM_SMEM_RCP = SMEM_RCP;                   // RN(1/den) per denominator
 constexpr int MM_SMEM_KP = 1024;                        // kpad[p] of every SCP (P <= 255)
 constexpr int MM_SMEM_FIXED = MM_SMEM_MISC + MM_SMEM_CT + MM_SMEM_RCP + MM_SMEM_KP + MM_SMEM_CNT;
@@ -225,14 +225,6 @@ __device__ __forceinline__ void sp_prefetch(uint32_t ring32, const uint4 *slab, 
     }
 }
 
-// One bulk copy moves its bytes at only a few bytes per cycle (a single copy keeps little in flight; measured on B200: a ring of
-// eight 16 KB copies sustained 20 B/cycle per SM, i.e. ~2.5 B/cycle per copy), so large transfers are issued as many small
-// copies that complete on the same mbarrier: their latencies overlap.
-constexpr uint32_t MM_PIECE = 2048;
-__device__ __forceinline__ void bulk_g2s_split(unsigned char *dst, const unsigned char *src, uint32_t bytes, uint64_t *bar) {
-    for (uint32_t o = 0; o < bytes; o += MM_PIECE) bulk_g2s(dst + o, src + o, min(MM_PIECE, bytes - o), bar);
-}
-
 template <class Cfg>
 __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams prm) {
     constexpr int MM_NSTAGE = Cfg::NSTAGE, RING_D = Cfg::RING_D;
@@ -299,8 +291,8 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                         mbar_wait(&empty[s], ph ^ 1u);
                         mbar_expect_tx(&full[s], 2u * bytes);
                         unsigned char *dst = stage_mem + (size_t)s * MM_STAGE_BYTES;
-                        bulk_g2s_split(dst, a_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
-                        bulk_g2s_split(dst + MM_OP_BYTES, b_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
+                        bulk_g2s(dst, a_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
+                        bulk_g2s(dst + MM_OP_BYTES, b_img + ko + (int64_t)k0 * 128, bytes, &full[s]);
                         it++;
                     }
                 }
@@ -349,7 +341,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                         const int64_t off = (int64_t)(((uint64_t)d.y << 32) | d.x);
                         mbar_wait(dict_empty, (di & 1u) ^ 1u);              // every walker warp is done with the previous dictionary
                         mbar_expect_tx(dict_full, d.z);
-                        bulk_g2s_split(dict_mem, prm.sp_blob + off, d.z, dict_full);
+                        bulk_g2s(dict_mem, prm.sp_blob + off, d.z, dict_full);
                         di++;
                     }
                 }
@@ -398,7 +390,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
                 if (row_ok && gj >= 0 && gj != gi) valid |= 1u << j;
             }
             // per-SCP scalars are fetched one SCP ahead (their latency hides behind the previous SCP's epilogue): the row's T value,
-            // the extent of the sub-tile's patch records and this lane's first record
+            // the fast-division guard, the slab extents of the row items and the number of dictionary parts
             const int tileP_r = tile.x * P, tileP_c = tile.y * P;
             const bool never_fast = prm.quirk != 0, all_fast = prm.all_fast != 0;
             int ta = row_ok ? __ldg(prm.T + ti) : 0;
@@ -476,7 +468,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
 #pragma unroll
                         for (int u = 0; u < 16; u++) cv[u] = 0u;
                     }
-                    if (np) {                               // warp-uniform: add this row's patch counters, then clear them
+                    if (np) {                               // uniform over the quadrant: add this row's sparse counters, then clear them
 #pragma unroll
                         for (int v4 = 0; v4 < 2; v4++) {
                             uint32_t w[4];
@@ -524,7 +516,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) aji_mma_kernel(const MmaParams 
             const int nrow = min(MM_ROWS, prm.n_rows - row0);
             const int64_t ro0 = (int64_t)tile.z;
             for (int round = 0; round < 4; round++) {
-                asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");      // staging (== patch counters) is free
+                asm volatile("bar.sync 1, %0;" ::"n"(MM_EPI_WARPS * 32) : "memory");      // staging (== sparse counters) is free
                 if (cg == round) {
 #pragma unroll
                     for (int g = 0; g < 4; g++) {

@@ -52,6 +52,7 @@ struct Ctx {
     // streaming output (pfaai_gpu_set_progress / pfaai_gpu_progress_poll): per-granule counters of finished tiles, what they must
     // reach, and a private stream + pinned buffer for polling from another host thread while compute blocks its caller
     DevBuf prog;
+    bool lists_only = false;                  // pfaai_gpu_import_lists: no F on the device (no partitioned / routed build possible)
     bool prog_enabled = false;
     std::atomic<int> prog_state{0};          // 0 = no compute under way / not armed, 1 = armed (counters valid), 2 = compute finished
     std::vector<int32_t> prog_need;
@@ -60,7 +61,7 @@ struct Ctx {
     cudaStream_t prog_stream = nullptr;
     int32_t *prog_host = nullptr;
     size_t prog_host_cap = 0;
-    // dense-contraction path (K5): planning + operands + patches
+    // dense-contraction path (K5): planning + operands + sparse row items / dictionaries
     int path_pref = PFAAI_PATH_AUTO, tau_pref = 0;
     DevBuf mm_len, mm_hist, mm_did, mm_kcnt, mm_kpad, mm_koff, mm_img_rows, mm_img_cols, mm_colT, mm_rowmax, mm_colmax,
            mm_owned, sp_cnt, sp_nch, sp_tot, sp_off, sp_items, sp_nsub, sp_sub, sp_blob;
@@ -200,6 +201,7 @@ static int sort_and_finish(Ctx *c, uint64_t *src, uint64_t *dst, int64_t n_items
 static int build_internal(Ctx *c, bool partitioned) {
     if (!c) return PFAAI_ERR_CONSTRUCT;
     if (!c->uploaded) { set_error(c, "build: no index uploaded"); return PFAAI_ERR_CONSTRUCT; }
+    if (c->lists_only) { set_error(c, "build: the context holds imported lists, not F (pfaai_gpu_import_lists leaves it built; upload F to rebuild)"); return PFAAI_ERR_CONSTRUCT; }
     if (c->sliced) { set_error(c, "build: the context holds a slice of F (use pfaai_gpu_route_prepare / pfaai_gpu_build_routed)"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
     const int P = c->P, G = c->G;
@@ -386,7 +388,7 @@ int pfaai_gpu_upload_index(pfaai_gpu_ctx *h, int P, int G, const pfaai_pg_t *F, 
     if (P <= 0 || G <= 0 || nF < 0 || !Lc || (nF > 0 && !F)) { set_error(c, "upload_index: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
     if ((int64_t)P * G >= (1ll << 31)) { set_error(c, "upload_index: P*G too large"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
-    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false;
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false; c->lists_only = false;
     PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
@@ -407,7 +409,7 @@ int pfaai_gpu_upload_triples(pfaai_gpu_ctx *h, int P, int G, const int32_t *tetr
     if (P <= 0 || G <= 0 || nF < 0 || (nF > 0 && (!F || !tetramer))) { set_error(c, "upload_triples: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
     if ((int64_t)P * G >= (1ll << 31)) { set_error(c, "upload_triples: P*G too large"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
-    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false;
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false; c->lists_only = false;
     PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
@@ -452,8 +454,9 @@ int pfaai_gpu_import_lists(pfaai_gpu_ctx *h, int P, int G, int64_t nF, const int
     if ((int64_t)P * G >= (1ll << 31)) { set_error(c, "import_lists: P*G too large"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
     const int64_t nseg = (int64_t)P * G;
-    c->P = P; c->G = G; c->nF = nF; c->nF_owned = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false;
+    c->P = P; c->G = G; c->nF = nF; c->nF_owned = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false; c->lists_only = false;
     c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr; c->e_size = -1; c->launches = 0;
+    c->lists_only = true;
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
     PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
@@ -494,7 +497,7 @@ int pfaai_gpu_index_device_buffers(pfaai_gpu_ctx *h, int P, int G, int64_t nF, i
     if (!c) return PFAAI_ERR_CONSTRUCT;
     if (P <= 0 || G <= 0 || nF < 0 || (int64_t)P * G >= (1ll << 31)) { set_error(c, "index_device_buffers: bad arguments"); return PFAAI_ERR_CONSTRUCT; }
     PF_CUDA(c, cudaSetDevice(c->device));
-    c->P = P; c->G = G; c->nF = nF; c->host_T = (host_T != 0); c->built = false; c->uploaded = false; c->sliced = false;
+    c->P = P; c->G = G; c->nF = nF; c->host_T = (host_T != 0); c->built = false; c->uploaded = false; c->sliced = false; c->lists_only = false;
     PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)nF));
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
@@ -596,7 +599,7 @@ int pfaai_gpu_index_slice_buffers(pfaai_gpu_ctx *h, int P, int G, int64_t nF_tot
     }
     PF_CUDA(c, cudaSetDevice(c->device));
     c->P = P; c->G = G; c->nF = nF_total; c->nF_total = nF_total; c->host_T = false; c->built = false; c->uploaded = false;
-    c->sliced = true; c->slice_begin = slice_begin; c->n_slice = n_slice;
+    c->sliced = true; c->lists_only = false; c->slice_begin = slice_begin; c->n_slice = n_slice;
     PF_TRY(ensure(c, c->F, sizeof(pfaai_pg_t) * (size_t)n_slice));
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->T, sizeof(int32_t) * (size_t)P * G));
@@ -1263,7 +1266,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
                 PF_TRY(mma_length_hist(c, 1, pl));
                 mma_choose(c, pl, cells, img_blocks, force);
             }
-            if (force && !pl.use) { set_error(c, "compute: the dense path does not fit this input (operand images / patch records too large)"); return PFAAI_ERR_CONSTRUCT; }
+            if (force && !pl.use) { set_error(c, "compute: the dense path does not fit this input (operand images too large)"); return PFAAI_ERR_CONSTRUCT; }
             use_mma = pl.use;
         }
     }
@@ -1448,7 +1451,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     };
     const int n_late = (int)tiles.size() - n_early;
     if (use_mma) {
-        // ---- K5: operands + patches (timed as "prep"), then the tensor-core tile kernel ----
+        // ---- K5: operands + sparse row items / dictionaries (timed as "prep"), then the tensor-core tile kernel ----
         MmaParams mp;
         std::vector<int32_t> kpad_host;
         PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));

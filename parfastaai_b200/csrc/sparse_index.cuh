@@ -210,16 +210,25 @@ __device__ __forceinline__ bool sd_build(const SpDictParams &prm, const SdSmem &
     uint32_t at = n + 1 + sd_block_scan(s, need, &n_list);
     const uint32_t n_ent = n + 1 + n_list;
     if (n_ent > (uint32_t)prm.ent_max) return false;
+    // single-column slots are cleared, multi-column slots point at their list [cursor/count, e1 .. em], all zero for now
     for (uint32_t i = i0; i < i1; i++) {
         const uint32_t m = s.ent[i];
-        if (m >= 2u) { s.ent[i] = (uint16_t)(0x8000u | at); s.ent[at] = 0; at += m + 1u; }   // [at] = fill cursor, ends as the count
+        if (m >= 2u) {
+            s.ent[i] = (uint16_t)(0x8000u | at);
+            for (uint32_t k = 0; k <= m; k++) s.ent[at + k] = 0;
+            at += m + 1u;
+        } else {
+            s.ent[i] = 0;
+        }
     }
     __syncthreads();
+    // the fill pass touches the entry array with 32-bit atomic adds only (a 16-bit value is "stored" by adding it to its zeroed
+    // half-word): no plain 16-bit store ever shares a word with a concurrent atomic
     sd_for_each(prm, s, D, c0, c1, [&](int c, uint32_t v) {
-        const uint32_t i = slot(v), e = s.ent[i];
-        // a single-column slot still holds its multiplicity 1 (or the entry, if c is small ... never read again: one writer)
-        if (e & 0x8000u) { const uint32_t l = e & 0x7fffu; const uint32_t k = sd_add16(s.ent, l, 1u); s.ent[l + 1 + k] = (uint16_t)sp_entry((uint32_t)c); }
-        else s.ent[i] = (uint16_t)sp_entry((uint32_t)c);
+        const uint32_t i = slot(v);
+        const uint32_t e = reinterpret_cast<volatile uint16_t *>(s.ent)[i];
+        if (e & 0x8000u) { const uint32_t l = e & 0x7fffu; const uint32_t k = sd_add16(s.ent, l, 1u); sd_add16(s.ent, l + 1 + k, sp_entry((uint32_t)c)); }
+        else sd_add16(s.ent, i, sp_entry((uint32_t)c));
     });
     __syncthreads();
     const uint32_t bytes = (uint32_t)SP_ENT_OFF + ((2u * n_ent + 15u) & ~15u);

@@ -5,9 +5,11 @@
 // -4 <= e10 < 16 and in exponent notation (d.ddde-05, at least two exponent digits) otherwise; integral values
 // print without a decimal point ("0", "1").  std::to_chars(double) yields the same shortest digit string
 // (the shortest round-trip digits are unique), so only the layout rule is restated here.
-// Rows are formatted in parallel (OpenMP) and written in order.
+// Rows are formatted AND written in parallel (OpenMP, one buffer and one file offset per thread).
 #pragma once
+#include <fcntl.h>
 #include <omp.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <charconv>
@@ -20,41 +22,52 @@
 
 namespace pfaai_host {
 
-// appends fmt::format("{}", v) to out
-inline void append_double(std::string &out, double v) {
-    if (std::isnan(v)) { out += std::signbit(v) ? "-nan" : "nan"; return; }
-    if (std::isinf(v)) { out += v < 0 ? "-inf" : "inf"; return; }
-    if (std::signbit(v)) { out += '-'; v = -v; }
-    if (v == 0.0) { out += '0'; return; }
+// writes fmt::format("{}", v) at p (at most 32 characters) and returns the end
+inline char *put_double(char *p, double v) {
+    if (std::isnan(v)) { if (std::signbit(v)) *p++ = '-'; std::memcpy(p, "nan", 3); return p + 3; }
+    if (std::isinf(v)) { if (v < 0) *p++ = '-'; std::memcpy(p, "inf", 3); return p + 3; }
+    if (std::signbit(v)) { *p++ = '-'; v = -v; }
+    if (v == 0.0) { *p++ = '0'; return p; }
     char buf[40];
     auto res = std::to_chars(buf, buf + sizeof(buf), v, std::chars_format::scientific);   // d[.ddd]e[+-]XX, shortest
-    const char *e = static_cast<const char *>(std::memchr(buf, 'e', (size_t)(res.ptr - buf)));
+    // exponent: the last characters are e[+-]XX[X]
+    const char *e = res.ptr - 1;
+    while (*e != 'e') e--;
     int e10 = 0;
-    std::from_chars(e + 1 + (e[1] == '+' ? 1 : 0), res.ptr, e10);
+    for (const char *q = e + 2; q < res.ptr; q++) e10 = e10 * 10 + (*q - '0');
+    if (e[1] == '-') e10 = -e10;
+    // digits: buf[0], then buf[2 .. e) when there is a fraction
+    const int nd = (e - buf > 1) ? (int)(e - buf) - 1 : 1;
     char digits[24];
-    int nd = 0;
-    for (const char *p = buf; p < e; p++)
-        if (*p != '.') digits[nd++] = *p;
+    digits[0] = buf[0];
+    if (nd > 1) std::memcpy(digits + 1, buf + 2, (size_t)(nd - 1));
     if (e10 < -4 || e10 >= 16) {                       // exponent notation
-        out += digits[0];
-        if (nd > 1) { out += '.'; out.append(digits + 1, (size_t)(nd - 1)); }
-        out += 'e';
-        out += e10 < 0 ? '-' : '+';
-        const int a = e10 < 0 ? -e10 : e10;
-        if (a < 10) out += '0';
-        out += std::to_string(a);
+        *p++ = digits[0];
+        if (nd > 1) { *p++ = '.'; std::memcpy(p, digits + 1, (size_t)(nd - 1)); p += nd - 1; }
+        *p++ = 'e';
+        *p++ = e10 < 0 ? '-' : '+';
+        int a = e10 < 0 ? -e10 : e10;
+        if (a >= 100) { *p++ = (char)('0' + a / 100); a %= 100; *p++ = (char)('0' + a / 10); *p++ = (char)('0' + a % 10); }
+        else { *p++ = (char)('0' + a / 10); *p++ = (char)('0' + a % 10); }
     } else if (e10 >= nd - 1) {                        // integral: digits followed by zeros, no decimal point
-        out.append(digits, (size_t)nd);
-        out.append((size_t)(e10 - (nd - 1)), '0');
+        std::memcpy(p, digits, (size_t)nd); p += nd;
+        for (int k = 0; k < e10 - (nd - 1); k++) *p++ = '0';
     } else if (e10 >= 0) {                             // ddd.ddd
-        out.append(digits, (size_t)(e10 + 1));
-        out += '.';
-        out.append(digits + e10 + 1, (size_t)(nd - e10 - 1));
+        std::memcpy(p, digits, (size_t)(e10 + 1)); p += e10 + 1;
+        *p++ = '.';
+        std::memcpy(p, digits + e10 + 1, (size_t)(nd - e10 - 1)); p += nd - e10 - 1;
     } else {                                           // 0.000ddd
-        out += "0.";
-        out.append((size_t)(-e10 - 1), '0');
-        out.append(digits, (size_t)nd);
+        *p++ = '0'; *p++ = '.';
+        for (int k = 0; k < -e10 - 1; k++) *p++ = '0';
+        std::memcpy(p, digits, (size_t)nd); p += nd;
     }
+    return p;
+}
+
+// appends fmt::format("{}", v) to out
+inline void append_double(std::string &out, double v) {
+    char buf[40];
+    out.append(buf, (size_t)(put_double(buf, v) - buf));
 }
 
 inline std::string format_double(double v) {
@@ -63,47 +76,104 @@ inline std::string format_double(double v) {
     return s;
 }
 
-namespace detail {
-inline bool write_header(FILE *fp, const std::string &sep, const std::vector<std::string> &tgtNames) {
-    std::string hdr = sep;
-    for (size_t j = 0; j < tgtNames.size(); j++) { if (j) hdr += sep; hdr += tgtNames[j]; }
-    hdr += '\n';
-    return std::fwrite(hdr.data(), 1, hdr.size(), fp) == hdr.size();
-}
-// rows [r0, r1): formatted in parallel (OpenMP) in batches, written in order
-inline bool write_rows(FILE *fp, const std::string &sep, const std::vector<std::string> &qryNames, size_t nT, const double *matrix,
-                       size_t r0, size_t r1, std::vector<std::string> &lines) {
-    const size_t batch = lines.size();
-    bool ok = true;
-    for (size_t b0 = r0; b0 < r1 && ok; b0 += batch) {
-        const size_t b1 = std::min(r1, b0 + batch);
-#pragma omp parallel for schedule(dynamic, 1)
-        for (size_t r = b0; r < b1; r++) {
-            std::string &s = lines[r - b0];
-            s.clear();
-            s.reserve(qryNames[r].size() + nT * 20 + 8);
-            s += qryNames[r];
-            s += sep;
-            const double *row = matrix + r * nT;
-            for (size_t j = 0; j < nT; j++) { if (j) s += sep; append_double(s, row[j]); }
-            s += '\n';
-        }
-        for (size_t r = b0; r < b1 && ok; r++) ok = std::fwrite(lines[r - b0].data(), 1, lines[r - b0].size(), fp) == lines[r - b0].size();
-    }
-    return ok;
-}
-}  // namespace detail
+// The output file.  Rows are formatted by all OpenMP threads at once, every thread into its own buffer (raw character writes, no
+// string appends), and each thread then writes its buffer at its own file offset (pwrite): neither formatting nor writing is
+// serial, and a batch costs one parallel region.  header: <sep> + target names joined by <sep>; rows: query name, <sep>,
+// values joined by <sep>; '\n' endings -- the bytes of the reference's printOutput (main.cpp:156-174).
+class CsvFile {
+    int m_fd = -1;
+    off_t m_off = 0;
+    bool m_ok = false;
+    std::vector<std::vector<char>> m_buf;     // one per thread
 
-// header: <sep> + target names joined by <sep>; rows: query name, <sep>, values joined by <sep>; '\n' endings.
+  public:
+    explicit CsvFile(const std::string &path) {
+        m_fd = ::open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
+        m_ok = m_fd >= 0;
+        m_buf.resize((size_t)std::max(1, omp_get_max_threads()));
+    }
+    CsvFile(const CsvFile &) = delete;
+    CsvFile &operator=(const CsvFile &) = delete;
+    ~CsvFile() { if (m_fd >= 0) ::close(m_fd); }
+    bool ok() const { return m_ok; }
+    bool close() {
+        if (m_fd >= 0) { if (::close(m_fd) != 0) m_ok = false; m_fd = -1; }
+        return m_ok;
+    }
+    static bool pwrite_all(int fd, const char *p, size_t n, off_t off) {
+        while (n > 0) {
+            const ssize_t w = ::pwrite(fd, p, n, off);
+            if (w <= 0) return false;
+            p += w; n -= (size_t)w; off += w;
+        }
+        return true;
+    }
+    bool header(const std::string &sep, const std::vector<std::string> &tgtNames) {
+        std::string hdr = sep;
+        for (size_t j = 0; j < tgtNames.size(); j++) { if (j) hdr += sep; hdr += tgtNames[j]; }
+        hdr += '\n';
+        m_ok = m_ok && pwrite_all(m_fd, hdr.data(), hdr.size(), m_off);
+        m_off += (off_t)hdr.size();
+        return m_ok;
+    }
+    // rows [r0, r1) of the row-major matrix [.. x nT]
+    bool rows(const std::string &sep, const std::vector<std::string> &qryNames, size_t nT, const double *matrix, size_t r0, size_t r1) {
+        if (!m_ok || r1 <= r0) return m_ok;
+        const size_t T = m_buf.size();
+        size_t name_max = 0;
+        for (size_t r = r0; r < r1; r++) name_max = std::max(name_max, qryNames[r].size());
+        const size_t row_cap = name_max + sep.size() + nT * (32 + sep.size()) + 2;
+        // rows per thread and step: bounded by ~8 MB of buffer per thread, at least 1
+        const size_t per = std::max<size_t>(1, std::min<size_t>((r1 - r0 + T - 1) / T, ((size_t)8 << 20) / row_cap + 1));
+        std::vector<size_t> len(T, 0);
+        std::vector<off_t> at(T, 0);
+        bool ok = true;
+        off_t base = m_off;
+#pragma omp parallel num_threads((int)T)
+        {
+            const size_t t = (size_t)omp_get_thread_num();
+            std::vector<char> &buf = m_buf[t];
+            if (buf.size() < per * row_cap) buf.resize(per * row_cap);
+            for (size_t b0 = r0; b0 < r1; b0 += per * T) {
+                const size_t my0 = std::min(r1, b0 + t * per), my1 = std::min(r1, my0 + per);
+                char *p = buf.data();
+                for (size_t r = my0; r < my1; r++) {
+                    std::memcpy(p, qryNames[r].data(), qryNames[r].size()); p += qryNames[r].size();
+                    std::memcpy(p, sep.data(), sep.size()); p += sep.size();
+                    const double *row = matrix + r * nT;
+                    for (size_t j = 0; j < nT; j++) {
+                        if (j) { std::memcpy(p, sep.data(), sep.size()); p += sep.size(); }
+                        p = put_double(p, row[j]);
+                    }
+                    *p++ = '\n';
+                }
+                len[t] = (size_t)(p - buf.data());
+#pragma omp barrier
+#pragma omp single
+                {
+                    for (size_t k = 0; k < T; k++) { at[k] = base; base += (off_t)len[k]; }
+                }
+                if (len[t] && !pwrite_all(m_fd, buf.data(), len[t], at[t])) {
+#pragma omp atomic write
+                    ok = false;
+                }
+#pragma omp barrier
+            }
+        }
+        m_off = base;
+        m_ok = m_ok && ok;
+        return m_ok;
+    }
+};
+
 // Returns false when the file cannot be opened / written.
 inline bool write_aji_csv(const std::string &path, const std::string &sep, const std::vector<std::string> &qryNames,
                           const std::vector<std::string> &tgtNames, const double *matrix /*[nQ x nT] row-major*/) {
-    FILE *fp = std::fopen(path.c_str(), "w");
-    if (!fp) return false;
-    std::vector<std::string> lines((size_t)std::max(1, omp_get_max_threads()) * 8);
-    bool ok = detail::write_header(fp, sep, tgtNames);
-    ok = ok && detail::write_rows(fp, sep, qryNames, tgtNames.size(), matrix, 0, qryNames.size(), lines);
-    return (std::fclose(fp) == 0) && ok;
+    CsvFile f(path);
+    if (!f.ok()) return false;
+    f.header(sep, tgtNames);
+    f.rows(sep, qryNames, tgtNames.size(), matrix, 0, qryNames.size());
+    return f.close();
 }
 
 // The same file, written WHILE the matrix is being computed: poll(rows_final, finished) reports how many
@@ -113,18 +183,17 @@ inline bool write_aji_csv(const std::string &path, const std::string &sep, const
 template <class Poll>
 inline bool write_aji_csv_streaming(const std::string &path, const std::string &sep, const std::vector<std::string> &qryNames,
                                     const std::vector<std::string> &tgtNames, const double *matrix, Poll poll, size_t *overlapped_rows) {
-    FILE *fp = std::fopen(path.c_str(), "w");
-    if (!fp) return false;
+    CsvFile f(path);
+    if (!f.ok()) return false;
     const size_t nQ = qryNames.size();
-    std::vector<std::string> lines((size_t)std::max(1, omp_get_max_threads()) * 8);
-    bool ok = detail::write_header(fp, sep, tgtNames);
+    bool ok = f.header(sep, tgtNames);
     size_t written = 0, overlapped = 0;
     while (ok && written < nQ) {
         int64_t rows_final = 0; int finished = 0;
         if (!poll(rows_final, finished)) { ok = false; break; }
         const size_t upto = std::min(nQ, (size_t)std::max<int64_t>(rows_final, 0));
         if (upto > written) {
-            ok = detail::write_rows(fp, sep, qryNames, tgtNames.size(), matrix, written, upto, lines);
+            ok = f.rows(sep, qryNames, tgtNames.size(), matrix, written, upto);
             if (!finished) overlapped = upto;
             written = upto;
         } else if (finished) {
@@ -136,7 +205,7 @@ inline bool write_aji_csv_streaming(const std::string &path, const std::string &
     }
     if (overlapped_rows) *overlapped_rows = overlapped;
     ok = ok && written == nQ;
-    return (std::fclose(fp) == 0) && ok;
+    return f.close() && ok;
 }
 
 }  // namespace pfaai_host

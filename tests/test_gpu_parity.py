@@ -163,6 +163,8 @@ def test_device_ready_lists_import_equals_the_built_index(pf, orc):
     assert c2.e_size() == int(full["counts"].sum())
     c2.import_lists(P, G, a["Lc"], a["seg_off"], a["seg_vals"], T=a["T"])   # caller-supplied T
     assert np.array_equal(c2.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], full["matrix"])
+    with pytest.raises(pf.PfaaiError):                                    # no F on the device: nothing to rebuild from
+        c2.build()
     bad = a["seg_vals"].copy(); bad[[0, 1]] = bad[[1, 0]]
     with pytest.raises(pf.PfaaiError):
         c2.import_lists(P, G, a["Lc"], a["seg_off"], bad)
