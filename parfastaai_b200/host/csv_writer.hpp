@@ -76,21 +76,23 @@ inline std::string format_double(double v) {
     return s;
 }
 
-// The output file.  Rows are formatted by all OpenMP threads at once, every thread into its own buffer (raw character writes, no
-// string appends), and each thread then writes its buffer at its own file offset (pwrite): neither formatting nor writing is
-// serial, and a batch costs one parallel region.  header: <sep> + target names joined by <sep>; rows: query name, <sep>,
-// values joined by <sep>; '\n' endings -- the bytes of the reference's printOutput (main.cpp:156-174).
+// The output file.  header: <sep> + target names joined by <sep>; rows: query name, <sep>, values joined by <sep>; '\n'
+// endings -- the bytes of the reference's printOutput (main.cpp:156-174).
+// Rows are formatted by the whole OpenMP team, in chunks handed out dynamically, every chunk into its own buffer (raw character
+// writes, no string appends).  Buffered writes to ONE file serialise in the kernel whatever the number of writers, so the writing
+// is a pipeline stage instead: when batch k is formatted, one thread writes its chunks in order while the others already format
+// batch k+1 into the second buffer set (the writer joins them when it is done and simply takes fewer chunks).
 class CsvFile {
     int m_fd = -1;
     off_t m_off = 0;
     bool m_ok = false;
-    std::vector<std::vector<char>> m_buf;     // one per thread
+    std::vector<std::vector<char>> m_buf[2];   // two buffer sets x chunks per batch
+    std::vector<size_t> m_len[2];
 
   public:
     explicit CsvFile(const std::string &path) {
         m_fd = ::open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
         m_ok = m_fd >= 0;
-        m_buf.resize((size_t)std::max(1, omp_get_max_threads()));
     }
     CsvFile(const CsvFile &) = delete;
     CsvFile &operator=(const CsvFile &) = delete;
@@ -100,7 +102,7 @@ class CsvFile {
         if (m_fd >= 0) { if (::close(m_fd) != 0) m_ok = false; m_fd = -1; }
         return m_ok;
     }
-    static bool pwrite_all(int fd, const char *p, size_t n, off_t off) {
+    static bool write_all(int fd, const char *p, size_t n, off_t off) {
         while (n > 0) {
             const ssize_t w = ::pwrite(fd, p, n, off);
             if (w <= 0) return false;
@@ -112,55 +114,65 @@ class CsvFile {
         std::string hdr = sep;
         for (size_t j = 0; j < tgtNames.size(); j++) { if (j) hdr += sep; hdr += tgtNames[j]; }
         hdr += '\n';
-        m_ok = m_ok && pwrite_all(m_fd, hdr.data(), hdr.size(), m_off);
+        m_ok = m_ok && write_all(m_fd, hdr.data(), hdr.size(), m_off);
         m_off += (off_t)hdr.size();
         return m_ok;
     }
     // rows [r0, r1) of the row-major matrix [.. x nT]
     bool rows(const std::string &sep, const std::vector<std::string> &qryNames, size_t nT, const double *matrix, size_t r0, size_t r1) {
         if (!m_ok || r1 <= r0) return m_ok;
-        const size_t T = m_buf.size();
+        const size_t T = (size_t)std::max(1, omp_get_max_threads());
         size_t name_max = 0;
         for (size_t r = r0; r < r1; r++) name_max = std::max(name_max, qryNames[r].size());
         const size_t row_cap = name_max + sep.size() + nT * (32 + sep.size()) + 2;
-        // rows per thread and step: bounded by ~8 MB of buffer per thread, at least 1
-        const size_t per = std::max<size_t>(1, std::min<size_t>((r1 - r0 + T - 1) / T, ((size_t)8 << 20) / row_cap + 1));
-        std::vector<size_t> len(T, 0);
-        std::vector<off_t> at(T, 0);
+        const size_t C = 2 * T;                                                    // chunks per batch
+        // rows per chunk: the range split evenly, bounded by ~4 MB of buffer per chunk, at least 1
+        const size_t per = std::max<size_t>(1, std::min<size_t>((r1 - r0 + C - 1) / C, ((size_t)4 << 20) / row_cap + 1));
+        const size_t batch_rows = per * C, n_batches = (r1 - r0 + batch_rows - 1) / batch_rows;
+        for (int k = 0; k < 2; k++) { m_buf[k].resize(C); m_len[k].assign(C, 0); }
         bool ok = true;
-        off_t base = m_off;
+        off_t off = m_off;
+        std::vector<int> next(n_batches, 0);                                       // next chunk of every batch (dynamic hand-out)
 #pragma omp parallel num_threads((int)T)
         {
-            const size_t t = (size_t)omp_get_thread_num();
-            std::vector<char> &buf = m_buf[t];
-            if (buf.size() < per * row_cap) buf.resize(per * row_cap);
-            for (size_t b0 = r0; b0 < r1; b0 += per * T) {
-                const size_t my0 = std::min(r1, b0 + t * per), my1 = std::min(r1, my0 + per);
-                char *p = buf.data();
-                for (size_t r = my0; r < my1; r++) {
-                    std::memcpy(p, qryNames[r].data(), qryNames[r].size()); p += qryNames[r].size();
-                    std::memcpy(p, sep.data(), sep.size()); p += sep.size();
-                    const double *row = matrix + r * nT;
-                    for (size_t j = 0; j < nT; j++) {
-                        if (j) { std::memcpy(p, sep.data(), sep.size()); p += sep.size(); }
-                        p = put_double(p, row[j]);
+            for (size_t b = 0; b < n_batches; b++) {
+                const size_t b0 = r0 + b * batch_rows;
+                std::vector<std::vector<char>> &bufs = m_buf[b & 1];
+                std::vector<size_t> &lens = m_len[b & 1];
+                for (;;) {
+                    int c;
+#pragma omp atomic capture
+                    c = next[b]++;
+                    if ((size_t)c >= C) break;
+                    const size_t my0 = std::min(r1, b0 + (size_t)c * per), my1 = std::min(r1, my0 + per);
+                    std::vector<char> &buf = bufs[(size_t)c];
+                    if (buf.size() < per * row_cap) buf.resize(per * row_cap);
+                    char *p = buf.data();
+                    for (size_t r = my0; r < my1; r++) {
+                        std::memcpy(p, qryNames[r].data(), qryNames[r].size()); p += qryNames[r].size();
+                        std::memcpy(p, sep.data(), sep.size()); p += sep.size();
+                        const double *row = matrix + r * nT;
+                        for (size_t j = 0; j < nT; j++) {
+                            if (j) { std::memcpy(p, sep.data(), sep.size()); p += sep.size(); }
+                            p = put_double(p, row[j]);
+                        }
+                        *p++ = '\n';
                     }
-                    *p++ = '\n';
+                    lens[(size_t)c] = (size_t)(p - buf.data());
                 }
-                len[t] = (size_t)(p - buf.data());
+                // batch b is complete behind this barrier; the thread that wrote batch b-1 has passed it too, so that write is over
+                // and its buffer set is free for batch b+1
 #pragma omp barrier
-#pragma omp single
+#pragma omp single nowait
                 {
-                    for (size_t k = 0; k < T; k++) { at[k] = base; base += (off_t)len[k]; }
+                    for (size_t c = 0; c < C; c++) {
+                        if (lens[c] && !write_all(m_fd, bufs[c].data(), lens[c], off)) ok = false;
+                        off += (off_t)lens[c];
+                    }
                 }
-                if (len[t] && !pwrite_all(m_fd, buf.data(), len[t], at[t])) {
-#pragma omp atomic write
-                    ok = false;
-                }
-#pragma omp barrier
             }
         }
-        m_off = base;
+        m_off = off;
         m_ok = m_ok && ok;
         return m_ok;
     }
