@@ -150,9 +150,18 @@ def run_ref_once(db, threads, tmpdir):
     return phases, wall
 
 
+REF_PATH_PHASES = ["E constr.   (fin)", "JAC Construction"]
+
+
 def ref_path_seconds(phases):
-    # construct() + run(): Lc/Lp + F + T + E (generation + sort) + JAC/AJI  (interface.hpp:306-327, algorithm_impl.hpp:281-329)
-    return sum(phases[p.strip()] for p in REF_PHASES) / 1e3
+    # the part of construct() + run() the GPU arm covers: from Lc / F / T in host memory to JAC / AJI, i.e. E generation + sort and
+    # computeJAC / computeAJI (interface.hpp:319-323, algorithm_impl.hpp:281-329).  The SQLite-facing phases (Lc & Lp, F, T
+    # construction) are parsed and reported, not counted: the GPU arm starts from host arrays too (like for like).
+    return sum(phases[p.strip()] for p in REF_PATH_PHASES) / 1e3
+
+
+def ref_ingest_seconds(phases):
+    return sum(phases[p.strip()] for p in REF_PHASES if p not in REF_PATH_PHASES) / 1e3
 
 
 def port_baseline(P, off, vals, T, n_rows, n_cols, gpu_matrix=None):
@@ -252,8 +261,9 @@ def reference_baseline(P, n_genomes, threads, tmpdir):
     secs = ref_path_seconds(phases)
     return {"value": pairs / secs, "unit": UNIT, "cores": threads, "kind": "reference",
             "sample": f"unmodified reference par_fastaai.x (oracle/_ref) on synthetic FastAAI SQLite DB {n_genomes} genomes x {P} SCPs "
-                      f"all-vs-all ({pairs} pairs), OMP_NUM_THREADS={threads}; path time = sum of its own phase timers {secs:.2f} s "
-                      f"(process wall {wall:.2f} s); phases ms: " + ", ".join(f"{k}={v:.0f}" for k, v in phases.items()),
+                      f"all-vs-all ({pairs} pairs), OMP_NUM_THREADS={threads}; path time = its own timers for E construction + sort + JAC/AJI "
+                      f"{secs:.2f} s (from host arrays, like the GPU arm; its SQLite ingest took another {ref_ingest_seconds(phases):.2f} s; "
+                      f"process wall {wall:.2f} s); phases ms: " + ", ".join(f"{k}={v:.0f}" for k, v in phases.items()),
             "pairs_per_s_wall": pairs / wall}
 
 
@@ -299,7 +309,8 @@ def run_reference_arm(args, rank, emit):
             v = pairs * len(secs) / sum(secs)
             cb = {"value": v, "unit": UNIT, "cores": threads, "kind": "reference",
                   "sample": f"unmodified reference par_fastaai.x (oracle/_ref), synthetic FastAAI SQLite DB {n} genomes x {P} SCPs all-vs-all "
-                            f"({pairs} pairs/step), OMP_NUM_THREADS={threads}; step time = sum of its own phase timers; "
+                            f"({pairs} pairs/step), OMP_NUM_THREADS={threads}; step time = its own timers for E construction + sort + JAC/AJI (from host arrays, like the "
+                            f"GPU arm; SQLite ingest not counted); "
                             f"last step phases ms: " + ", ".join(f"{k}={x:.0f}" for k, x in last.items()),
                   "pairs_per_s_wall": pairs * len(walls) / sum(walls)}
             line.update(value=v, ms_per_step=1e3 * sum(secs) / len(secs), cpu_baseline=cb,
