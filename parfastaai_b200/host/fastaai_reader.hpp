@@ -278,6 +278,7 @@ class SQLiteSCPDataBase {
 // Main (target) database + attached query database (-r)
 // ---------------------------------------------------------------------------------------------------
 class QTSQLiteSCPDataBase {
+  protected:
     std::string m_pathToTgtDb, m_pathToQryDb;
     sqlite3 *m_sqltDbPtr = nullptr;
     int m_dbErrorCode = SQLITE_OK;
@@ -299,9 +300,11 @@ class QTSQLiteSCPDataBase {
         return db;
     }
 
-  public:
-    QTSQLiteSCPDataBase(const std::string &tgtDBPath, const std::string &qryDBPath)
-        : m_pathToTgtDb(tgtDBPath), m_pathToQryDb(qryDBPath) {
+    struct DeferOpen {};
+    QTSQLiteSCPDataBase(const std::string &tgtDBPath, const std::string &qryDBPath, DeferOpen)   // a subclass decides whether the pair is opened
+        : m_pathToTgtDb(tgtDBPath), m_pathToQryDb(qryDBPath) {}
+    void openPairAndReadNames() {
+        m_dbMeta = DBMetaData();
         m_sqltDbPtr = open_pair(&m_dbErrorCode, true);
         if (m_dbErrorCode != SQLITE_OK) return;
         // SCPs present in BOTH databases, same statement as db_helper.hpp:139-146
@@ -318,9 +321,15 @@ class QTSQLiteSCPDataBase {
             m_dbErrorCode = detail::query_strings(
                 m_sqltDbPtr, "SELECT " + m_dbNames.GMTTAB_COLUMN_GNAME + " FROM `QueryDB`." + m_dbNames.GMTTAB, m_dbMeta.qyGenomeSet);
     }
+
+  public:
+    QTSQLiteSCPDataBase(const std::string &tgtDBPath, const std::string &qryDBPath)
+        : m_pathToTgtDb(tgtDBPath), m_pathToQryDb(qryDBPath) {
+        openPairAndReadNames();
+    }
     QTSQLiteSCPDataBase(const QTSQLiteSCPDataBase &) = delete;
     QTSQLiteSCPDataBase &operator=(const QTSQLiteSCPDataBase &) = delete;
-    ~QTSQLiteSCPDataBase() { if (m_sqltDbPtr) closeDB(); }
+    virtual ~QTSQLiteSCPDataBase() { if (m_sqltDbPtr) closeDB(); }
 
     int getDBErrorCode() const { return m_dbErrorCode; }
     std::string getDBPath() const { return m_pathToTgtDb; }
@@ -337,7 +346,7 @@ class QTSQLiteSCPDataBase {
         return SQLITE_OK;
     }
 
-    pfaai_status validate() const {
+    virtual pfaai_status validate() const {
         if (m_dbErrorCode != SQLITE_OK || m_sqltDbPtr == nullptr) {
             std::cerr << "Error in opening " << getDBPath() << std::endl;
             if (m_dbErrorCode != SQLITE_OK) std::cerr << "DB ERROR: " << sqlite3_errstr(m_dbErrorCode) << std::endl;
@@ -348,7 +357,7 @@ class QTSQLiteSCPDataBase {
 
     // targets keep ids 0..nT-1, queries become nT + id; per SCP only tetramers present in BOTH databases
     // are indexed (inner join, scp_db.hpp:408-414,459-466), T is unrestricted.
-    int loadIndex(HostIndex &ix) const {
+    virtual int loadIndex(HostIndex &ix) const {
         const int P = (int)m_dbMeta.proteinSet.size();
         const int nT = (int)m_dbMeta.genomeSet.size(), nQ = (int)m_dbMeta.qyGenomeSet.size(), G = nT + nQ;
         ix.nProteins = P; ix.nGenomes = G; ix.nTargets = nT; ix.nQueries = nQ;

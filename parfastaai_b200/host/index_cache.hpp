@@ -18,7 +18,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "fastaai_reader.hpp"
@@ -237,6 +239,114 @@ class CachedSCPDataBase : public SQLiteSCPDataBase {
             else std::cerr << "Warning: could not write the index cache " << m_cachePath << std::endl;
         }
         return rc;
+    }
+};
+
+// Query-DB mode on top of the cached main index -- the incremental "add query genomes" path of SURVEY 8(f) rank 3.  The reference
+// re-reads the whole main database for every query database (main.cpp:302-335 -> scp_db.hpp:402-589, ATTACH + per-SCP inner
+// joins); here a valid `.pfidx` + `.lists` pair of the main database serves the targets' device-ready lists, name tables and T,
+// only the (small) query database is read from SQLite, and the query genomes' lists are appended behind the targets':
+//   proteins : those of the main database that the query database also has, in the main database's order (what the reference's
+//              join statement returns, db_helper.hpp:139-146);
+//   genomes  : targets keep ids 0..nT-1, queries become nT + id;
+//   lists    : every tetramer of every genome, not only those present in both databases -- a tetramer that one side lacks never
+//              co-occurs in a (target, query) pair, so counts, S, N and AJI equal the inner-join index's (scp_db.hpp:408-414);
+//   T        : unrestricted on both sides, as in the reference.
+// Lc is the tetramer histogram of these lists (a parity hook only; the inner-join Lc of the uncached path differs by design).
+// Anything missing or stale (no cache, no sidecar, changed main database) falls back to the ATTACH path.
+class CachedQTDataBase : public QTSQLiteSCPDataBase {
+    std::string m_cachePath;
+    IndexCacheKey m_key;
+    bool m_cached = false;
+    std::unique_ptr<SQLiteSCPDataBase> m_qdb;       // the query database alone
+    DBMetaData m_mainMeta;
+    mutable HostIndex m_mainIx;                     // names checked, Lc / T loaded, F skipped
+    std::vector<int> m_pm, m_pq;                    // common protein -> index in the main / query database
+
+  public:
+    CachedQTDataBase(const std::string &tgtDBPath, const std::string &qryDBPath, const std::string &cachePath)
+        : QTSQLiteSCPDataBase(tgtDBPath, qryDBPath, DeferOpen{}), m_cachePath(cachePath) {
+        const std::string lists = cachePath + ".lists";
+        if (index_cache_key(tgtDBPath, m_key) && lists_cache_header_ok(lists, m_key) &&
+            read_index_cache(m_cachePath, m_key, m_mainMeta, m_mainIx, /*skip_F=*/true)) {
+            m_qdb.reset(new SQLiteSCPDataBase(qryDBPath));
+            if (m_qdb->getDBErrorCode() == SQLITE_OK) {
+                const DBMetaData &qm = m_qdb->getMeta();
+                std::unordered_map<std::string, int> qidx;
+                for (size_t i = 0; i < qm.proteinSet.size(); i++) qidx.emplace(qm.proteinSet[i], (int)i);
+                for (size_t i = 0; i < m_mainMeta.proteinSet.size(); i++) {
+                    auto it = qidx.find(m_mainMeta.proteinSet[i]);
+                    if (it == qidx.end()) continue;
+                    m_dbMeta.proteinSet.push_back(m_mainMeta.proteinSet[i]);
+                    m_pm.push_back((int)i); m_pq.push_back(it->second);
+                }
+                m_dbMeta.genomeSet = m_mainMeta.genomeSet;
+                m_dbMeta.qyGenomeSet = qm.genomeSet;
+                m_cached = true;
+                std::printf("Index cache         : main database served from %s (+ .lists); only the query database is read from SQLite\n",
+                            m_cachePath.c_str());
+                return;
+            }
+            m_qdb.reset();
+        }
+        openPairAndReadNames();
+    }
+    bool fromCache() const { return m_cached; }
+    pfaai_status validate() const override { return m_cached ? m_qdb->validate() : QTSQLiteSCPDataBase::validate(); }
+
+    int loadIndex(HostIndex &ix) const override {
+        if (!m_cached) return QTSQLiteSCPDataBase::loadIndex(ix);
+        const int Pm = m_mainIx.nProteins, nT = m_mainIx.nGenomes, Pc = (int)m_pm.size();
+        uint64_t nFm = 0;
+        for (int32_t v : m_mainIx.Lc) nFm += (uint64_t)v;
+        std::vector<int64_t> so_m; std::vector<uint32_t> sv_m;
+        HostIndex q;
+        if (!read_lists_cache(m_cachePath + ".lists", m_key, Pm, nT, nFm, so_m, sv_m) || m_qdb->loadIndex(q) != SQLITE_OK) {
+            // cannot happen after the constructor's checks unless the files changed underneath us: take the reference's route
+            std::cerr << "Warning: index cache unusable for the query-DB run; reading both databases from SQLite" << std::endl;
+            QTSQLiteSCPDataBase fresh(m_pathToTgtDb, m_pathToQryDb);
+            return fresh.getDBErrorCode() == SQLITE_OK ? fresh.loadIndex(ix) : fresh.getDBErrorCode();
+        }
+        const int Pq = q.nProteins, nQ = q.nGenomes, G = nT + nQ;
+        // the query database's own lists, genome-major: a stable counting sort of its (tetramer, protein, genome) postings
+        std::vector<int64_t> so_q((size_t)nQ * Pq + 1, 0);
+        for (const pfaai_pg_t &e : q.F) so_q[(size_t)e.genome * Pq + e.protein + 1]++;
+        for (size_t i = 1; i < so_q.size(); i++) so_q[i] += so_q[i - 1];
+        std::vector<uint32_t> sv_q(q.F.size());
+        {
+            std::vector<int64_t> cur(so_q.begin(), so_q.end() - 1);
+            size_t k = 0;
+            for (uint32_t t = 0; t < (uint32_t)NTETRAMERS; t++)
+                for (int32_t c = 0; c < q.Lc[t]; c++, k++) sv_q[(size_t)cur[(size_t)q.F[k].genome * Pq + q.F[k].protein]++] = t;
+        }
+        ix = HostIndex();
+        ix.nProteins = Pc; ix.nGenomes = G; ix.nTargets = nT; ix.nQueries = nQ;
+        ix.segOff.assign((size_t)G * Pc + 1, 0);
+        for (int g = 0; g < G; g++)
+            for (int pc = 0; pc < Pc; pc++) {
+                const int64_t len = g < nT ? so_m[(size_t)g * Pm + m_pm[pc] + 1] - so_m[(size_t)g * Pm + m_pm[pc]]
+                                           : so_q[(size_t)(g - nT) * Pq + m_pq[pc] + 1] - so_q[(size_t)(g - nT) * Pq + m_pq[pc]];
+                ix.segOff[(size_t)g * Pc + pc + 1] = len;
+            }
+        for (size_t i = 1; i < ix.segOff.size(); i++) ix.segOff[i] += ix.segOff[i - 1];
+        ix.segVals.resize((size_t)ix.segOff.back());
+#pragma omp parallel for schedule(static)
+        for (int g = 0; g < G; g++)
+            for (int pc = 0; pc < Pc; pc++) {
+                const int64_t dst = ix.segOff[(size_t)g * Pc + pc], len = ix.segOff[(size_t)g * Pc + pc + 1] - dst;
+                const uint32_t *src = g < nT ? sv_m.data() + so_m[(size_t)g * Pm + m_pm[pc]] : sv_q.data() + so_q[(size_t)(g - nT) * Pq + m_pq[pc]];
+                std::memcpy(ix.segVals.data() + dst, src, (size_t)len * sizeof(uint32_t));
+            }
+        ix.T.assign((size_t)Pc * G, 0);
+        for (int pc = 0; pc < Pc; pc++) {
+            std::memcpy(ix.T.data() + (size_t)pc * G, m_mainIx.T.data() + (size_t)m_pm[pc] * nT, (size_t)nT * sizeof(int32_t));
+            std::memcpy(ix.T.data() + (size_t)pc * G + nT, q.T.data() + (size_t)m_pq[pc] * nQ, (size_t)nQ * sizeof(int32_t));
+        }
+        ix.Lc.assign(NTETRAMERS, 0);
+        for (uint32_t v : ix.segVals) ix.Lc[v]++;
+        std::printf("Index cache         : %d query genomes added to the cached index of %d targets (%d common SCPs, %zu postings)\n", nQ, nT, Pc,
+                    ix.segVals.size());
+        return SQLITE_OK;
     }
 };
 

@@ -56,7 +56,8 @@ struct AppParams {
            << "  --gpus INT [1]              number of GPUs (devices device..device+gpus-1); output row blocks are sharded over them\n"
            << "  --no-ref-compat             query-DB mode: corrected T lookup (default reproduces the reference)\n"
            << "  --no-stream-csv             write the CSV after the computation (default, one GPU all-vs-all: rows are written while later row blocks are computed)\n"
-           << "  --index-cache TEXT          single-DB modes: device-ready index cache of the input DB (read if valid, else written)\n"
+           << "  --index-cache TEXT          device-ready index cache of the input DB (read if valid, else written by the single-DB modes; with -r the\n"
+           << "                              cached main DB is reused and only the query DB is read)\n"
            << "  --dump-index TEXT           host only: write PREFIX.{lc,f,t}.bin and exit\n";
     }
     // returns -1 to continue, otherwise the process exit code
@@ -255,7 +256,11 @@ int parallel_subset_fastaai(const AppParams &args) {                // main.cpp:
 }
 
 int parallel_qry2tgt_fastaai(const AppParams &args) {               // main.cpp:302-335
-    QTSQLiteSCPDataBase db(args.pathToDatabase, args.pathToQryDatabase);
+    // with --index-cache: the main database comes from its cache, only the query database is read (index_cache.hpp)
+    std::unique_ptr<QTSQLiteSCPDataBase> dbp(args.indexCachePath.empty() || !args.dumpIndexPrefix.empty()
+                                                 ? new QTSQLiteSCPDataBase(args.pathToDatabase, args.pathToQryDatabase)
+                                                 : new CachedQTDataBase(args.pathToDatabase, args.pathToQryDatabase, args.indexCachePath));
+    QTSQLiteSCPDataBase &db = *dbp;
     if (db.validate() != PFAAI_OK) return PFAAI_ERR_SQLITE_DB;
     const DBMetaData &meta = db.getMeta();
     std::unordered_set<std::string> have(meta.genomeSet.begin(), meta.genomeSet.end());

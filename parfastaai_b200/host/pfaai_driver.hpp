@@ -167,8 +167,8 @@ class DataStructBase {
             if (rc != PFAAI_OK) { rcs[k] = rc; errs[k] = pfaai_gpu_last_error(nullptr); return; }
             rc = pfaai_gpu_set_shard(m_ctxs[k], k, n);
             if (rc == PFAAI_OK && m_ix.haveLists()) {
-                rc = pfaai_gpu_import_lists(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, nF_all, m_ix.Lc.data(), nullptr, m_ix.segOff.data(),
-                                            m_ix.segVals.data());
+                rc = pfaai_gpu_import_lists(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, nF_all, m_ix.Lc.data(), m_hostT ? m_ix.T.data() : nullptr,
+                                            m_ix.segOff.data(), m_ix.segVals.data());
             } else if (rc == PFAAI_OK && partitioned) {
                 // routed build: GPU k receives only the k-th slice of F (|F| bytes cross PCIe once, not once per GPU); the
                 // postings are routed to the GPU that owns their genome afterwards (pfaai_gpu_route_local)

@@ -72,6 +72,66 @@ int main(int argc, char **argv) {
         auto shortfall = [&](int64_t &rows, int &fin) { rows = 3; fin = 1; return true; };
         CHECK(!write_aji_csv_streaming(b, ";", names, names, M.data(), shortfall, nullptr));
     }
+    // ---- query-DB mode on the cached main index (CachedQTDataBase) == the ATTACH path, up to the tetramers only one side has ----
+    if (argc >= 4) {
+        const std::string mainDb = argv[2], qryDb = argv[3], cache = dir + "/main.pfidx";
+        auto genome_major = [](const HostIndex &x, std::vector<int64_t> &so, std::vector<uint32_t> &sv) {
+            const int P = x.nProteins, G = x.nGenomes;
+            so.assign((size_t)G * P + 1, 0);
+            for (const pfaai_pg_t &e : x.F) so[(size_t)e.genome * P + e.protein + 1]++;
+            for (size_t i = 1; i < so.size(); i++) so[i] += so[i - 1];
+            sv.resize(x.F.size());
+            std::vector<int64_t> cur(so.begin(), so.end() - 1);
+            size_t k = 0;
+            for (uint32_t t = 0; t < (uint32_t)NTETRAMERS; t++)
+                for (int32_t c = 0; c < x.Lc[t]; c++, k++) sv[(size_t)cur[(size_t)x.F[k].genome * P + x.F[k].protein]++] = t;
+        };
+        {   // what a first single-DB run leaves behind: .pfidx (names, Lc, F, T) + .lists (device-ready lists)
+            SQLiteSCPDataBase m(mainDb);
+            CHECK(m.getDBErrorCode() == SQLITE_OK);
+            HostIndex ix;
+            CHECK(m.loadIndex(ix) == SQLITE_OK);
+            IndexCacheKey key;
+            CHECK(index_cache_key(mainDb, key));
+            CHECK(write_index_cache(cache, key, m.getMeta(), ix));
+            std::vector<int64_t> so; std::vector<uint32_t> sv;
+            genome_major(ix, so, sv);
+            CHECK(write_lists_cache(cache + ".lists", key, ix.nProteins, ix.nGenomes, sv.size(), so.data(), sv.data()));
+        }
+        QTSQLiteSCPDataBase ref(mainDb, qryDb);
+        CachedQTDataBase inc(mainDb, qryDb, cache);
+        CHECK(ref.validate() == PFAAI_OK && inc.validate() == PFAAI_OK && inc.fromCache());
+        CHECK(ref.getMeta().proteinSet == inc.getMeta().proteinSet);            // same SCPs in the same (summation) order
+        CHECK(ref.getMeta().genomeSet == inc.getMeta().genomeSet && ref.getMeta().qyGenomeSet == inc.getMeta().qyGenomeSet);
+        HostIndex a, b;
+        CHECK(ref.loadIndex(a) == SQLITE_OK && inc.loadIndex(b) == SQLITE_OK);
+        CHECK(a.nProteins == b.nProteins && a.nGenomes == b.nGenomes && a.nTargets == b.nTargets && a.nQueries == b.nQueries);
+        CHECK(a.T == b.T && b.haveLists() && b.F.empty());
+        // per SCP: restrict the incremental lists to the tetramers that occur on BOTH sides -> the inner-join index of the reference
+        std::vector<int64_t> so; std::vector<uint32_t> sv;
+        genome_major(a, so, sv);
+        const int P = a.nProteins, G = a.nGenomes, nT = a.nTargets;
+        size_t at = 0;
+        for (int p = 0; p < P; p++) {
+            std::vector<char> inT(NTETRAMERS, 0), inQ(NTETRAMERS, 0);
+            for (int g = 0; g < G; g++)
+                for (int64_t k = b.segOff[(size_t)g * P + p]; k < b.segOff[(size_t)g * P + p + 1]; k++) (g < nT ? inT : inQ)[b.segVals[(size_t)k]] = 1;
+            for (int g = 0; g < G; g++) {
+                std::vector<uint32_t> kept;
+                for (int64_t k = b.segOff[(size_t)g * P + p]; k < b.segOff[(size_t)g * P + p + 1]; k++)
+                    if (inT[b.segVals[(size_t)k]] && inQ[b.segVals[(size_t)k]]) kept.push_back(b.segVals[(size_t)k]);
+                const std::vector<uint32_t> want(sv.begin() + so[(size_t)g * P + p], sv.begin() + so[(size_t)g * P + p + 1]);
+                CHECK(kept == want);
+                at += kept.size();
+            }
+        }
+        CHECK(at == a.F.size());
+        // a main database that changed after the cache was written: the cache is ignored, the ATTACH path answers
+        IndexCacheKey stale; CHECK(index_cache_key(mainDb, stale)); stale.size += 1;
+        { HostIndex ix; DBMetaData meta; SQLiteSCPDataBase m(mainDb); CHECK(m.loadIndex(ix) == SQLITE_OK); CHECK(write_index_cache(cache, stale, m.getMeta(), ix)); }
+        CachedQTDataBase fallback(mainDb, qryDb, cache);
+        CHECK(!fallback.fromCache() && fallback.validate() == PFAAI_OK && fallback.getMeta().proteinSet == ref.getMeta().proteinSet);
+    }
     std::puts("OK");
     return 0;
 }

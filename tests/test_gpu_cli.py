@@ -77,6 +77,32 @@ def test_query_db_mode_reference_values(cli, tmp_path):
     assert M2.max() <= 1.0 and 0 < np.abs(M2 - M).max() < 1e-2
 
 
+def test_query_db_mode_on_the_cached_main_index(cli, tmp_path):
+    """The incremental "add query genomes" path: once a single-DB run has left `.pfidx` + `.lists` of the
+    main database, `-r query.db --index-cache` reads only the query database, appends its genomes' lists to the cached
+    device-ready index and must write the same CSV bytes as the uncached run (incl. the label quirk and --no-ref-compat);
+    two contexts (replicated import, sharded compute) too."""
+    import shutil
+    main_db = str(tmp_path / "main.db")
+    shutil.copy(gu.db_path("xdb_subset1.db"), main_db)
+    qry_db = gu.db_path("xdb_subset2.db")
+    cache = str(tmp_path / "main.pfidx")
+    run(cli, main_db, str(tmp_path / "all.csv"), "--index-cache", cache)            # first run: writes the cache and the sidecar
+    assert os.path.exists(cache) and os.path.exists(cache + ".lists")
+    for extra in ([], ["--no-ref-compat"], ["--gpus", "2", "--same-device"]):
+        plain, inc = str(tmp_path / "plain.csv"), str(tmp_path / "inc.csv")
+        run(cli, main_db, plain, "-r", qry_db, *extra)
+        r = run(cli, main_db, inc, "-r", qry_db, "--index-cache", cache, *extra)
+        assert "only the query database is read from SQLite" in r.stdout and "query genomes added to the cached index" in r.stdout
+        assert open(plain, "rb").read() == open(inc, "rb").read(), extra
+    # stale cache (main database touched): ignored, the ATTACH path answers, same bytes
+    os.utime(main_db, (1, 1))
+    r = run(cli, main_db, inc, "-r", qry_db, "--index-cache", cache)
+    assert "only the query database is read" not in r.stdout
+    run(cli, main_db, plain, "-r", qry_db)
+    assert open(plain, "rb").read() == open(inc, "rb").read()
+
+
 def test_against_reference_binary_on_synthetic_db(cli, tmp_path):
     ref = os.path.join(ROOT, "oracle", "_ref", "par_fastaai_ref.x")
     if not os.access(ref, os.X_OK):
