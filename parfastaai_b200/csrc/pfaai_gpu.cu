@@ -1455,7 +1455,24 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         MmaParams mp;
         std::vector<int32_t> kpad_host;
         PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
-        PF_TRY(mma_prepare(c, m, pl, n_rows, n_cols, rb_owned, kpad_host, mp));
+        {
+            // (PFAAI_TEST_FAIL_MMA_PREP: test hook for the fall-back below)
+            const int prc = getenv("PFAAI_TEST_FAIL_MMA_PREP") ? (set_error(c, "dense path: preparation failed (test hook)"), (int)PFAAI_ERR_CONSTRUCT)
+                                                               : mma_prepare(c, m, pl, n_rows, n_cols, rb_owned, kpad_host, mp);
+            if (prc != PFAAI_OK) {
+                // the cost model picked the dense path but it cannot be prepared for this input (a sparse dictionary that does not
+                // fit a stage, no memory for the operand images, ...): when the choice was ours, serve the call on the list path
+                // instead of failing it; a caller who forced PFAAI_PATH_MMA gets the error
+                if (c->path_pref != PFAAI_PATH_AUTO) return prc;
+                c->prog_state.store(0, std::memory_order_release);
+                c->path_pref = PFAAI_PATH_LISTS;
+                ModePlan m2;
+                const int rc2 = compute_internal(c, mode, qry_ids, nQ, flags, want_sn, want_counts, m2, direct_dev);
+                c->path_pref = PFAAI_PATH_AUTO;
+                m = std::move(m2);
+                return rc2;
+            }
+        }
         PF_CUDA(c, cudaEventRecord(c->ev[EV_K1], c->stream));
         mp.rows = prm.rows; mp.row_t = prm.row_t; mp.cols = prm.cols; mp.col_t = ptr<int32_t>(c->col_t);
         mp.n_rows = n_rows; mp.n_cols = n_cols; mp.T = prm.T; mp.t_ld = prm.t_ld; mp.P = P;

@@ -12,6 +12,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <cerrno>
 #include <charconv>
 #include <cmath>
 #include <cstdio>
@@ -102,10 +103,13 @@ class CsvFile {
         if (m_fd >= 0) { if (::close(m_fd) != 0) m_ok = false; m_fd = -1; }
         return m_ok;
     }
+    // all writes of this class are issued in file order by one thread at a time, so a plain write() is equivalent where the
+    // target cannot seek (a pipe, /dev/stdout)
     static bool write_all(int fd, const char *p, size_t n, off_t off) {
         while (n > 0) {
-            const ssize_t w = ::pwrite(fd, p, n, off);
-            if (w <= 0) return false;
+            ssize_t w = ::pwrite(fd, p, n, off);
+            if (w < 0 && errno == ESPIPE) w = ::write(fd, p, n);
+            if (w <= 0) { if (w < 0 && errno == EINTR) continue; return false; }
             p += w; n -= (size_t)w; off += w;
         }
         return true;

@@ -189,6 +189,31 @@ def test_auto_path_picks_by_density_and_agrees(pf, orc):
     assert picked[False] in (pf.PATH_LISTS, pf.PATH_MMA)
 
 
+def test_auto_path_falls_back_to_lists_when_the_dense_path_cannot_be_prepared(pf, orc, monkeypatch):
+    """PATH_AUTO on the dense family picks K5; when its preparation fails (test hook) the call is served by the list path
+    with identical results instead of failing; a forced PATH_MMA reports the error."""
+    from parfastaai_b200 import synth
+    N, P = 700, 5
+    off, vals = synth.generate(N, P, seed=5, dense=True)
+    Lc, F = synth.to_reference(N, P, off, vals)
+    ctx = pf.PfaaiGpu(0)
+    ctx.upload_index(P, N, F, Lc)
+    ctx.build()
+    want = ctx.compute(pf.ALL_VS_ALL, want_jac=True)
+    assert ctx.timings()["path"] == pf.PATH_MMA
+    monkeypatch.setenv("PFAAI_TEST_FAIL_MMA_PREP", "1")
+    got = ctx.compute(pf.ALL_VS_ALL, want_jac=True)
+    assert ctx.timings()["path"] == pf.PATH_LISTS
+    assert np.array_equal(got["matrix"], want["matrix"]) and np.array_equal(got["aji"], want["aji"])
+    ctx.set_path(pf.PATH_MMA)
+    with pytest.raises(pf.PfaaiError):
+        ctx.compute(pf.ALL_VS_ALL, want_jac=False)
+    monkeypatch.delenv("PFAAI_TEST_FAIL_MMA_PREP")
+    ctx.set_path(pf.PATH_AUTO)
+    assert np.array_equal(ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], want["matrix"])
+    ctx.close()
+
+
 def test_dense_path_refuses_what_it_cannot_serve(pf):
     from parfastaai_b200 import synth
     N, P = 900, 2
