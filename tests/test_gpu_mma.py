@@ -193,8 +193,8 @@ def test_auto_path_falls_back_to_lists_when_the_dense_path_cannot_be_prepared(pf
     """PATH_AUTO on the dense family picks K5; when its preparation fails (test hook) the call is served by the list path
     with identical results instead of failing; a forced PATH_MMA reports the error."""
     from parfastaai_b200 import synth
-    N, P = 700, 5
-    off, vals = synth.generate(N, P, seed=5, dense=True)
+    N, P = 1500, 6                     # the size at which test_auto_path_picks_by_density sees the cost model take K5
+    off, vals = synth.generate(N, P, seed=3, dense=True)
     Lc, F = synth.to_reference(N, P, off, vals)
     ctx = pf.PfaaiGpu(0)
     ctx.upload_index(P, N, F, Lc)
