@@ -70,9 +70,6 @@ struct TileParams {
     // (the tile's own 6 granules; in mirror mode also granule J, where the transposed cells land).  NULL = off.
     int *progress;
     int n_gran;
-    // 1: every T value is a true list length and 2 * max(T) < RCP_N over the whole index, so 0 <= c <= den < RCP_N holds for every
-    // cell and the epilogue needs no per-cell guard (the exact fast division applies everywhere; den = 0 only with c = 0 -> J = 0)
-    int all_fast;
     uint32_t piece;            // a stage blob travels as bulk copies of this many bytes (multiple of 16), all completing on the stage's
                                // mbarrier: one copy keeps only a few bytes per cycle in flight, many overlap their latencies
 };
@@ -503,12 +500,6 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                 }
                 const uint32_t ct32 = smem_u32(colT) + 4u * (uint32_t)((p & 3) * COLS_PER_TILE + cbase);
                 const uint32_t rcp32 = smem_u32(rcp);
-                // counts of 256 and more are rare (they need the planes 8 ..): skip their expansion when no lane of the warp has any
-                uint32_t hi_or = 0u;
-#pragma unroll
-                for (int kk = 8; kk <= NPL; kk++) hi_or |= R[kk];
-                const bool use_hi = __any_sync(0xffffffffu, hi_or != 0u);
-                const bool all_fast = prm.all_fast != 0;
                 __syncwarp();
                 // 8 columns at a time: fetch their sums from tensor memory, expand the bit-sliced counts
                 // (nibble -> one bit per byte: (n * 0x00204081) & 0x01010101) while the load is in flight, add J, store back
@@ -522,27 +513,19 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                         const int g4 = 2 * g8 + hf;
                         uint32_t lo = 0u, hi = 0u;
 #pragma unroll
-                        for (int kk = 0; kk < 8 && kk <= NPL; kk++)
-                            lo += ((((R[kk] >> (4 * g4)) & 15u) * 0x00204081u) & 0x01010101u) << kk;
-                        if (use_hi) {
-#pragma unroll
-                            for (int kk = 8; kk <= NPL; kk++)
-                                hi += ((((R[kk] >> (4 * g4)) & 15u) * 0x00204081u) & 0x01010101u) << (kk - 8);
+                        for (int kk = 0; kk <= NPL; kk++) {
+                            const uint32_t sp = (((R[kk] >> (4 * g4)) & 15u) * 0x00204081u) & 0x01010101u;
+                            if (kk < 8) lo += sp << kk; else hi += sp << (kk - 8);
                         }
 #pragma unroll
                         for (int u = 0; u < 4; u++)
                             cnt[4 * hf + u] = (int)(((lo >> (8 * u)) & 0xffu) | (((hi >> (8 * u)) & 0xffu) << 8));
                     }
                     bool slow = false;   // a denominator beyond the table or c > den (only the query-DB label quirk can do that)
-                    if (all_fast) {
 #pragma unroll
-                        for (int u = 0; u < 8; u++) den[u] = ta + lds_s32(ct32 + 4u * (uint32_t)(8 * g8 + u)) - cnt[u];
-                    } else {
-#pragma unroll
-                        for (int u = 0; u < 8; u++) {
-                            den[u] = max(ta + lds_s32(ct32 + 4u * (uint32_t)(8 * g8 + u)) - cnt[u], 1);
-                            slow |= (den[u] >= RCP_N) | (cnt[u] > den[u]);
-                        }
+                    for (int u = 0; u < 8; u++) {
+                        den[u] = max(ta + lds_s32(ct32 + 4u * (uint32_t)(8 * g8 + u)) - cnt[u], 1);
+                        slow |= (den[u] >= RCP_N) | (cnt[u] > den[u]);
                     }
                     if (prm.counts_out) {                                   // small-N hook, warp-uniform
 #pragma unroll
@@ -553,7 +536,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) aji_tile_kernel(const TilePar
                     }
                     tmem_wait_ld(sv);
                     // J = c / den, algorithm_impl.hpp:250-254 (c == 0 adds +0.0); one warp-uniform branch per 8 columns
-                    if (all_fast || !__any_sync(0xffffffffu, slow)) {
+                    if (!__any_sync(0xffffffffu, slow)) {
 #pragma unroll
                         for (int u = 0; u < 8; u++) {
                             const double sum = __hiloint2double((int)sv[2 * u + 1], (int)sv[2 * u]) + jaccard_fast(rcp32, cnt[u], den[u]);

@@ -1425,10 +1425,6 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     prm.T = ptr<int32_t>(c->T); prm.t_ld = c->G; prm.P = P;
     prm.out = direct_dev ? direct_dev : ptr<double>(c->out); prm.out_rs = m.rs; prm.out_cs = m.cs; prm.symmetric = m.symmetric; prm.mirror = (m.symmetric && !compact) ? 1 : 0;
     prm.k27 = 1u << 27; prm.k16 = 1u << 16;
-    // no per-cell division guard when every T is a true list length of THIS context's index (not host-supplied, not another
-    // shard's) and all denominators stay inside the reciprocal table
-    prm.all_fast = (!c->host_T && !c->partitioned && 2 * (int64_t)c->max_len < RCP_N &&
-                    !(mode == PFAAI_QUERY_DB && (flags & PFAAI_FLAG_REF_COMPAT_QT))) ? 1 : 0;
     {   // PFAAI_TILE_PIECE: bytes per bulk copy of a dictionary stage (A/B switch; default 0 = the whole blob in one copy.
         // Measured at config 4: 38.2 ms whole, 41.5 ms in 4 KB pieces, 49.5 ms in 1 KB pieces -- rejected, profiles/r2n_*)
         static const uint32_t piece = [] { const char *e = getenv("PFAAI_TILE_PIECE"); const long v = e ? atol(e) : 0; return (uint32_t)(v <= 0 ? (1 << 30) : ((v + 15) & ~15l)); }();
