@@ -271,6 +271,34 @@ int  pfaai_gpu_get_timings(const pfaai_gpu_ctx *ctx, pfaai_timings_t *out);
 typedef struct { double lookups_per_s; int64_t lookups; float ms; int32_t warps_per_sm; int32_t variant; int32_t reserved_; } pfaai_microbench_t;
 int  pfaai_gpu_microbench(pfaai_gpu_ctx *ctx, int variant, double hit_rate, int steps, pfaai_microbench_t *out);
 
+/* Exclusive prefix sum without any allocation.  NO COUNTERPART IN THE REFERENCE (its parallelPrefixSum, ds_helper.hpp:112-122,
+ * is what pfaai_gpu_build already replaces); this is the same device scan -- int32 inputs, 64-bit running sums -- offered to
+ * callers that cannot let this library allocate device memory:
+ *   - a plug-in inside a host application whose own memory pool has reserved the GPU (PyTorch's caching allocator, an RMM
+ *     arena, a serving process with a fixed budget): a cudaMalloc behind the pool's back fails or eats into that budget;
+ *   - a caller on a latency-critical path: cudaMalloc and cudaFree synchronise the whole device.
+ * The build path keeps the scan's per-tile partial sums in a cudaMalloc'ed context buffer.  Here they live in a fixed 8 KiB
+ * __device__ array inside the library image, so the call needs no context and performs no cudaMalloc / cudaFree / event or
+ * stream creation.  The price: every GPU this library is loaded on holds those 8 KiB until the process exits, and n is limited
+ * to PFAAI_GPU_STATIC_SCAN_MAX inputs (one partial sum per 4096 inputs; enough for Lc, 160000 entries, and for the segment
+ * histogram of up to 4,194,304 (SCP, genome) lists).  A larger n is refused with PFAAI_ERR_CONSTRUCT before anything is launched.
+ *   in_dev    [n]      device pointer, int32 counts
+ *   out_dev   [n + 1]  device pointer: out[i] = in[0] + ... + in[i-1], out[n] = the grand total
+ *   out32_dev [n]      optional (NULL to skip): the same sums truncated to int32 (the reference's Lp type)
+ * All three buffers belong to the caller.  The three kernels are enqueued on cuda_stream (a cudaStream_t; NULL = the default
+ * stream) of `device` and the call returns without waiting for them: synchronise the stream before reading the outputs.  The
+ * caller's current device is left as it was.
+ * Set-up: the FIRST call on each device looks the scratch array's device address up (cudaGetSymbolAddress, with that device
+ * current) and remembers it.  Make that first call before any stream capture begins.
+ * Sharing: all calls on one device, from every thread and stream of the process, use the same array.  It keeps whatever the
+ * previous call left there, which is harmless (each call overwrites the entries it reads before reading them).  But two calls
+ * whose kernels can run at the same time on one GPU -- different streams without an ordering between them -- overwrite each
+ * other's partial sums and give wrong results: keep such calls on one stream or order them with events.
+ * Errors: PFAAI_ERR_CONSTRUCT, text from pfaai_gpu_last_error(NULL). */
+#define PFAAI_GPU_STATIC_SCAN_MAX 4194304
+int  pfaai_gpu_prefix_sum_static(int device, void *cuda_stream, const int32_t *in_dev, int64_t n, int64_t *out_dev,
+                                 int32_t *out32_dev);
+
 #ifdef __cplusplus
 }
 #endif

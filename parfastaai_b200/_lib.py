@@ -33,6 +33,7 @@ EXPORTS = [
     "pfaai_gpu_upload_index_slice", "pfaai_gpu_index_slice_buffers", "pfaai_gpu_route_prepare", "pfaai_gpu_route_recv_buffer",
     "pfaai_gpu_build_routed", "pfaai_gpu_route_local", "pfaai_gpu_set_global_matrix", "pfaai_gpu_microbench", "pfaai_gpu_set_path", "pfaai_gpu_e_size",
     "pfaai_gpu_host_register", "pfaai_gpu_host_unregister", "pfaai_gpu_upload_triples", "pfaai_gpu_import_lists", "pfaai_gpu_set_progress", "pfaai_gpu_progress_poll",
+    "pfaai_gpu_prefix_sum_static",
 ]
 
 
@@ -119,6 +120,7 @@ def load():
     L.pfaai_gpu_set_progress.argtypes = [vp, i32]
     L.pfaai_gpu_progress_poll.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_int)]
     L.pfaai_gpu_microbench.argtypes = [vp, i32, C.c_double, i32, C.POINTER(Microbench)]
+    L.pfaai_gpu_prefix_sum_static.argtypes = [i32, vp, vp, i64, vp, vp]
     _lib = L
     return L
 
@@ -138,6 +140,20 @@ def host_register(ptr: int, nbytes: int) -> bool:
 
 def host_unregister(ptr: int, nbytes: int) -> bool:
     return load().pfaai_gpu_host_unregister(C.c_void_p(ptr), nbytes) == 0
+
+
+STATIC_SCAN_MAX = 4194304   # PFAAI_GPU_STATIC_SCAN_MAX
+
+
+def prefix_sum_static(device: int, stream_ptr: int, in_dev: int, n: int, out_dev: int, out32_dev: int = 0):
+    """pfaai_gpu_prefix_sum_static: exclusive scan of n int32 counts into n + 1 int64 sums, for callers that must not
+    allocate device memory (the scratch is a fixed array inside the library).  All pointers are DEVICE addresses of buffers
+    the caller owns; the kernels are only enqueued on the stream -- synchronise it before reading the outputs."""
+    L = load()
+    rc = L.pfaai_gpu_prefix_sum_static(int(device), C.c_void_p(stream_ptr or None), C.c_void_p(in_dev or None), int(n),
+                                       C.c_void_p(out_dev or None), C.c_void_p(out32_dev or None))
+    if rc != 0:
+        raise PfaaiError(f"prefix_sum_static rc={rc}: {L.pfaai_gpu_last_error(None).decode()}")
 
 
 class PfaaiGpu:

@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1717,3 +1718,73 @@ int pfaai_gpu_get_timings(const pfaai_gpu_ctx *h, pfaai_timings_t *out) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// pfaai_gpu_prefix_sum_static -- the exclusive scan of launch_scan() for callers that must not allocate.
+//
+// launch_scan() keeps its per-tile partial sums in a context buffer obtained with cudaMalloc.  Some users of this library
+// cannot afford that call: a plug-in that lives inside a host application whose own pool has already reserved the GPU's
+// memory (a raw cudaMalloc then fails, or steals from the pool's budget), and code on a latency-critical path, where
+// cudaMalloc / cudaFree synchronise the whole device.  For them the partial sums live in the array below, which is part of
+// the library image: every GPU on which this library is used holds these 8 KiB from module load until the process exits,
+// and the call itself allocates nothing -- no cudaMalloc / cudaFree, no context, no events, no library routine that could.
+//
+// g_static_scan_sums is a __device__ variable: inside host code its name is only the host-side handle of the symbol, not
+// an address a kernel can dereference.  The device address is looked up once per device, with that device current, with
+// cudaGetSymbolAddress and cached in g_static_scan_ptr; the kernels are then given that pointer like any other buffer.
+// ------------------------------------------------------------------------------------------------
+namespace pfaai {
+constexpr int64_t STATIC_SCAN_TILES = PFAAI_GPU_STATIC_SCAN_MAX / SCAN_TILE;      // 1024 partial sums = 8 KiB
+static_assert(PFAAI_GPU_STATIC_SCAN_MAX % SCAN_TILE == 0, "the limit is a whole number of scan tiles");
+static __device__ __align__(256) int64_t g_static_scan_sums[STATIC_SCAN_TILES];
+
+constexpr int STATIC_SCAN_MAX_DEVICES = 64;
+static int64_t *g_static_scan_ptr[STATIC_SCAN_MAX_DEVICES];                        // device address per ordinal, 0 = not looked up yet
+static std::mutex g_static_scan_mutex;                                             // guards the table and the error text
+
+static int static_scan_fail(const std::string &msg, int restore_device) {
+    set_error(nullptr, "prefix_sum_static: " + msg);
+    if (restore_device >= 0) cudaSetDevice(restore_device);
+    return PFAAI_ERR_CONSTRUCT;
+}
+}  // namespace pfaai
+
+extern "C" int pfaai_gpu_prefix_sum_static(int device, void *cuda_stream, const int32_t *in_dev, int64_t n, int64_t *out_dev,
+                                           int32_t *out32_dev) {
+    using namespace pfaai;
+    std::lock_guard<std::mutex> lock(g_static_scan_mutex);
+    // argument checks first: they need no GPU
+    if (n < 0 || !out_dev || (n > 0 && !in_dev)) return static_scan_fail("bad arguments (n >= 0, device pointers for input and output)", -1);
+    if (n > PFAAI_GPU_STATIC_SCAN_MAX)
+        return static_scan_fail("n = " + std::to_string(n) + " exceeds PFAAI_GPU_STATIC_SCAN_MAX = " + std::to_string((long long)PFAAI_GPU_STATIC_SCAN_MAX) +
+                                " (the fixed scratch array holds one partial sum per " + std::to_string(SCAN_TILE) +
+                                " inputs; larger inputs need the allocating path, pfaai_gpu_build)", -1);
+    if (device < 0 || device >= STATIC_SCAN_MAX_DEVICES) return static_scan_fail("device ordinal outside [0, 64)", -1);
+    int prev = -1;
+    if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); return static_scan_fail("no CUDA device (this library has no CPU fallback)", -1); }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) { cudaGetLastError(); return static_scan_fail(std::string("cudaSetDevice: ") + cudaGetErrorString(e), prev); }
+    if (!g_static_scan_ptr[device]) {
+        // set-up, once per device, with that device current (the FIRST call on a device: make it before any stream capture)
+        int64_t *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_static_scan_sums);
+        if (e != cudaSuccess || !p) { cudaGetLastError(); return static_scan_fail(std::string("cudaGetSymbolAddress: ") + cudaGetErrorString(e), prev); }
+        g_static_scan_ptr[device] = p;
+    }
+    int64_t *sums = g_static_scan_ptr[device];
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+    if (n == 0) {
+        e = cudaMemsetAsync(out_dev, 0, sizeof(int64_t), stream);                  // out[0] = grand total = 0
+    } else {
+        // Nothing in the array has to start at zero: k_scan_tile_sums overwrites sums[0, ntiles) before anything reads them, and
+        // entries beyond ntiles (left by an earlier, larger call) are never touched by this one.
+        const int64_t ntiles = ceil_div64(n, SCAN_TILE);
+        k_scan_tile_sums<<<(unsigned)ntiles, SCAN_THREADS, 0, stream>>>(in_dev, n, sums);
+        k_scan_small_i64<<<1, 1024, 0, stream>>>(sums, ntiles);
+        k_scan_final<<<(unsigned)ntiles, SCAN_THREADS, 0, stream>>>(in_dev, n, sums, out_dev, out32_dev);
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) return static_scan_fail(std::string("launch: ") + cudaGetErrorString(e), prev);
+    if (prev != device) cudaSetDevice(prev);
+    return PFAAI_OK;
+}
