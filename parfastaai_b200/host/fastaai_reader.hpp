@@ -221,6 +221,7 @@ class SQLiteSCPDataBase {
     virtual void preferLists(bool) const {}
     virtual bool wantsLists() const { return false; }
     virtual bool storeLists(const HostIndex &, const int64_t *, const uint32_t *) const { return false; }
+    virtual void dropLists() const {}     // the lists just served were refused by the device: forget them, serve F from now on
 
     int closeDB() {
         if (m_sqltDbPtr == nullptr) {
@@ -357,6 +358,8 @@ class QTSQLiteSCPDataBase {
 
     // targets keep ids 0..nT-1, queries become nT + id; per SCP only tetramers present in BOTH databases
     // are indexed (inner join, scp_db.hpp:408-414,459-466), T is unrestricted.
+    // the index as the reference's own route delivers it (ATTACH + joins), even when a subclass can serve it from a cache
+    virtual int loadIndexUncached(HostIndex &ix) const { return loadIndex(ix); }
     virtual int loadIndex(HostIndex &ix) const {
         const int P = (int)m_dbMeta.proteinSet.size();
         const int nT = (int)m_dbMeta.genomeSet.size(), nQ = (int)m_dbMeta.qyGenomeSet.size(), G = nT + nQ;

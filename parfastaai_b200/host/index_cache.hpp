@@ -43,6 +43,23 @@ inline uint64_t fnv1a(uint64_t h, const void *p, size_t n) {
     for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
     return h;
 }
+// Checksum of the tetramer postings of the lists sidecar (up to 7 GB at 50,000 genomes: byte-serial FNV would take longer than
+// reading the file).  The words are cut into fixed 2^18-word chunks; a chunk's sum is the FNV-1a recurrence taken over whole
+// 32-bit words, the chunks are independent (OpenMP) and their sums are folded with byte-wise FNV-1a in chunk order, so the
+// value does not depend on the number of threads.
+inline uint64_t words_checksum(const uint32_t *w, size_t n) {
+    constexpr size_t CHUNK = (size_t)1 << 18;
+    const size_t nchunks = (n + CHUNK - 1) / CHUNK;
+    std::vector<uint64_t> part(nchunks);
+#pragma omp parallel for schedule(static)
+    for (int64_t c = 0; c < (int64_t)nchunks; c++) {
+        uint64_t h = 1469598103934665603ull;
+        const size_t lo = (size_t)c * CHUNK, hi = lo + CHUNK < n ? lo + CHUNK : n;
+        for (size_t i = lo; i < hi; i++) { h ^= w[i]; h *= 1099511628211ull; }
+        part[(size_t)c] = h;
+    }
+    return fnv1a(1469598103934665603ull ^ (uint64_t)n, part.data(), part.size() * sizeof(uint64_t));
+}
 inline uint64_t cache_checksum(const DBMetaData &meta, const HostIndex &ix) {
     uint64_t h = 1469598103934665603ull;
     for (const auto &s : meta.proteinSet) h = fnv1a(h, s.data(), s.size() + 1);
@@ -120,7 +137,10 @@ inline bool read_index_cache(const std::string &path, const IndexCacheKey &key, 
 
 // ---- device-ready sidecar (<cache>.lists): the genome-major lists a device build produced (pfaai_gpu_get_arrays), so that the next
 // run hands them straight to pfaai_gpu_import_lists -- no F over PCIe (4 instead of 8 bytes per posting), no K1-K3, no sort.
-//   char[8] "PFLST001" | u64 db_size | i64 db_mtime_ns | i32 P | i32 G | u64 nF | u64 checksum(seg_off) | i64 seg_off[P*G+1] | u32 vals[nF]
+//   char[8] "PFLST002" | u64 db_size | i64 db_mtime_ns | i32 P | i32 G | u64 nF | u64 checksum(seg_off) | u64 checksum(vals) |
+//   i64 seg_off[P*G+1] | u32 vals[nF]
+// Both arrays are checksummed: a flipped bit in vals that keeps a segment ascending would pass the device's validation pass and
+// change counts silently.  (PFLST001 sidecars, which covered seg_off only, are treated as absent and rewritten.)
 inline bool write_lists_cache(const std::string &path, const IndexCacheKey &key, int32_t P, int32_t G, uint64_t nF, const int64_t *seg_off,
                               const uint32_t *vals) {
     const std::string tmp = path + ".tmp";
@@ -130,7 +150,8 @@ inline bool write_lists_cache(const std::string &path, const IndexCacheKey &key,
     auto put = [&](const void *p, size_t n) { if (ok && n) ok = std::fwrite(p, 1, n, f) == n; };
     const size_t nseg1 = (size_t)P * G + 1;
     const uint64_t sum = detail::fnv1a(1469598103934665603ull, seg_off, nseg1 * sizeof(int64_t));
-    put("PFLST001", 8); put(&key.size, 8); put(&key.mtime_ns, 8); put(&P, 4); put(&G, 4); put(&nF, 8); put(&sum, 8);
+    const uint64_t vsum = detail::words_checksum(vals, (size_t)nF);
+    put("PFLST002", 8); put(&key.size, 8); put(&key.mtime_ns, 8); put(&P, 4); put(&G, 4); put(&nF, 8); put(&sum, 8); put(&vsum, 8);
     put(seg_off, nseg1 * sizeof(int64_t));
     put(vals, (size_t)nF * sizeof(uint32_t));
     ok = (std::fclose(f) == 0) && ok;
@@ -145,7 +166,7 @@ inline bool lists_cache_header_ok(const std::string &path, const IndexCacheKey &
     if (!f) return false;
     char magic[8]; IndexCacheKey k;
     const bool ok = std::fread(magic, 1, 8, f) == 8 && std::fread(&k.size, 1, 8, f) == 8 && std::fread(&k.mtime_ns, 1, 8, f) == 8 &&
-                    std::memcmp(magic, "PFLST001", 8) == 0 && k.size == key.size && k.mtime_ns == key.mtime_ns;
+                    std::memcmp(magic, "PFLST002", 8) == 0 && k.size == key.size && k.mtime_ns == key.mtime_ns;
     std::fclose(f);
     return ok;
 }
@@ -156,9 +177,9 @@ inline bool read_lists_cache(const std::string &path, const IndexCacheKey &key, 
     if (!f) return false;
     bool ok = true;
     auto get = [&](void *p, size_t n) { if (ok && n) ok = std::fread(p, 1, n, f) == n; };
-    char magic[8]; IndexCacheKey k; int32_t p2 = 0, g2 = 0; uint64_t n2 = 0, sum = 0;
-    get(magic, 8); get(&k.size, 8); get(&k.mtime_ns, 8); get(&p2, 4); get(&g2, 4); get(&n2, 8); get(&sum, 8);
-    ok = ok && std::memcmp(magic, "PFLST001", 8) == 0 && k.size == key.size && k.mtime_ns == key.mtime_ns && p2 == P && g2 == G && n2 == nF;
+    char magic[8]; IndexCacheKey k; int32_t p2 = 0, g2 = 0; uint64_t n2 = 0, sum = 0, vsum = 0;
+    get(magic, 8); get(&k.size, 8); get(&k.mtime_ns, 8); get(&p2, 4); get(&g2, 4); get(&n2, 8); get(&sum, 8); get(&vsum, 8);
+    ok = ok && std::memcmp(magic, "PFLST002", 8) == 0 && k.size == key.size && k.mtime_ns == key.mtime_ns && p2 == P && g2 == G && n2 == nF;
     std::vector<int64_t> so; std::vector<uint32_t> v;
     if (ok) {
         so.resize((size_t)P * G + 1); get(so.data(), so.size() * sizeof(int64_t));
@@ -168,6 +189,7 @@ inline bool read_lists_cache(const std::string &path, const IndexCacheKey &key, 
         v.resize((size_t)nF); get(v.data(), v.size() * sizeof(uint32_t));
         char extra;
         ok = ok && std::fread(&extra, 1, 1, f) == 0;
+        ok = ok && detail::words_checksum(v.data(), v.size()) == vsum;
     }
     std::fclose(f);
     if (!ok) return false;
@@ -213,13 +235,29 @@ class CachedSCPDataBase : public SQLiteSCPDataBase {
         if (ok) std::printf("Index cache         : device-ready lists written to %s\n", listsPath().c_str());
         return ok;
     }
+    // the sidecar turned out to be unusable (the device refused its lists): remove it so that later runs do not trip over it
+    // again; the next loadIndex() serves F and the driver rewrites the sidecar from its fresh device build
+    void dropLists() const override {
+        std::remove(listsPath().c_str());
+        m_preferLists = false;
+    }
     pfaai_status validate() const override { return m_cached ? PFAAI_OK : SQLiteSCPDataBase::validate(); }
+    // the cache file became unreadable after the constructor accepted it: read the database itself and rewrite the cache
+    int loadFromSQLite(HostIndex &ix) const {
+        std::cerr << "Warning: index cache " << m_cachePath << " unreadable; reading the database from SQLite" << std::endl;
+        SQLiteSCPDataBase fresh(m_pathToDb);
+        if (fresh.getDBErrorCode() != SQLITE_OK) return fresh.getDBErrorCode();
+        const int rc = fresh.loadIndex(ix);
+        if (rc == SQLITE_OK && m_haveKey && write_index_cache(m_cachePath, m_key, fresh.getMeta(), ix))
+            std::printf("Index cache         : written to %s\n", m_cachePath.c_str());
+        return rc;
+    }
     int loadIndex(HostIndex &ix) const override {
         if (m_cached) {
             if (m_cachedIxValid) { ix = std::move(m_cachedIx); m_cachedIxValid = false; }
             else {
                 DBMetaData meta;
-                if (!read_index_cache(m_cachePath, m_key, meta, ix)) return SQLITE_ERROR;
+                if (!read_index_cache(m_cachePath, m_key, meta, ix)) return loadFromSQLite(ix);
             }
             uint64_t nF = 0;
             for (int32_t v : ix.Lc) nF += (uint64_t)v;
@@ -229,7 +267,7 @@ class CachedSCPDataBase : public SQLiteSCPDataBase {
             }
             if (ix.F.size() != nF) {            // F was skipped for a sidecar that cannot be used after all: read the full cache
                 DBMetaData meta;
-                if (!read_index_cache(m_cachePath, m_key, meta, ix)) return SQLITE_ERROR;
+                if (!read_index_cache(m_cachePath, m_key, meta, ix)) return loadFromSQLite(ix);
             }
             return SQLITE_OK;
         }
@@ -294,6 +332,12 @@ class CachedQTDataBase : public QTSQLiteSCPDataBase {
     bool fromCache() const { return m_cached; }
     pfaai_status validate() const override { return m_cached ? m_qdb->validate() : QTSQLiteSCPDataBase::validate(); }
 
+    // the reference's route (ATTACH + joins over both databases), whatever the cache says
+    int loadIndexUncached(HostIndex &ix) const override {
+        if (!m_cached) return QTSQLiteSCPDataBase::loadIndex(ix);
+        QTSQLiteSCPDataBase fresh(m_pathToTgtDb, m_pathToQryDb);
+        return fresh.getDBErrorCode() == SQLITE_OK ? fresh.loadIndex(ix) : fresh.getDBErrorCode();
+    }
     int loadIndex(HostIndex &ix) const override {
         if (!m_cached) return QTSQLiteSCPDataBase::loadIndex(ix);
         const int Pm = m_mainIx.nProteins, nT = m_mainIx.nGenomes, Pc = (int)m_pm.size();
@@ -304,8 +348,7 @@ class CachedQTDataBase : public QTSQLiteSCPDataBase {
         if (!read_lists_cache(m_cachePath + ".lists", m_key, Pm, nT, nFm, so_m, sv_m) || m_qdb->loadIndex(q) != SQLITE_OK) {
             // cannot happen after the constructor's checks unless the files changed underneath us: take the reference's route
             std::cerr << "Warning: index cache unusable for the query-DB run; reading both databases from SQLite" << std::endl;
-            QTSQLiteSCPDataBase fresh(m_pathToTgtDb, m_pathToQryDb);
-            return fresh.getDBErrorCode() == SQLITE_OK ? fresh.loadIndex(ix) : fresh.getDBErrorCode();
+            return loadIndexUncached(ix);
         }
         const int Pq = q.nProteins, nQ = q.nGenomes, G = nT + nQ;
         // the query database's own lists, genome-major: a stable counting sort of its (tetramer, protein, genome) postings

@@ -12,6 +12,7 @@
 // run() executes the tile kernel and brings back the dense AJI matrix (plus JAC/AJI lists for small inputs).
 // All CUDA work happens behind the C-ABI; this header contains no CUDA.  No CPU fallback.
 #pragma once
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdio>
@@ -90,6 +91,14 @@ class DataStructBase {
 
     virtual int loadHostIndex(HostIndex &ix) = 0;   // SQLite rc
     virtual const SQLiteSCPDataBase *cacheDb() const { return nullptr; }   // single-DB modes: the database object (index cache hooks)
+    // The device refused the cached device-ready lists: forget them (the sidecar is deleted) and load F the ordinary way -- from
+    // the .pfidx cache or, failing that, from SQLite.
+    virtual int reloadHostIndexWithoutLists(HostIndex &ix) {
+        const SQLiteSCPDataBase *db = cacheDb();
+        if (!db) return SQLITE_ERROR;
+        db->dropLists();
+        return loadHostIndex(ix);
+    }
 
   public:
     explicit DataStructBase(const DBMetaData &meta) : m_dbMeta(meta) {}
@@ -185,6 +194,32 @@ class DataStructBase {
             std::vector<std::thread> th;
             for (int k = 1; k < n; k++) th.emplace_back(work, k);
             work(0);
+            for (auto &t : th) t.join();
+        }
+        if (m_ix.haveLists() && std::any_of(rcs.begin(), rcs.end(), [](int r) { return r != PFAAI_OK; }) &&
+            std::all_of(m_ctxs.begin(), m_ctxs.end(), [](pfaai_gpu_ctx *c) { return c != nullptr; })) {
+            // The cache contract is "anything wrong with a cache -> fall back and rewrite it", and that includes lists that pass
+            // the sidecar's own checks but not the device's validation: drop the sidecar, load F, build the ordinary way.  The
+            // fresh build's lists are written back further down, so the next run is served from the cache again.
+            std::string msg;
+            for (int k = 0; k < n; k++) if (rcs[k] != PFAAI_OK) { msg = errs[k]; break; }
+            std::cerr << "Warning: the device refused the cached device-ready lists (" << msg << "); loading F and rebuilding the index" << std::endl;
+            m_ix = HostIndex();
+            if (reloadHostIndexWithoutLists(m_ix) != SQLITE_OK || m_ix.haveLists()) {
+                std::cerr << "Error in Lc, F, T host load ; Error code : " << PFAAI_ERR_SQLITE_DB << std::endl;
+                return m_errorCode = PFAAI_ERR_SQLITE_DB;
+            }
+            nF_all = (int64_t)m_ix.F.size();
+            auto rebuild = [&](int k) {
+                int r = pfaai_gpu_upload_index(m_ctxs[k], m_ix.nProteins, m_ix.nGenomes, m_ix.F.data(), m_ix.Lc.data(), (int64_t)m_ix.F.size(),
+                                               m_hostT ? m_ix.T.data() : nullptr);
+                if (r == PFAAI_OK) r = pfaai_gpu_build(m_ctxs[k]);
+                rcs[k] = r;
+                if (r != PFAAI_OK) errs[k] = pfaai_gpu_last_error(m_ctxs[k]);
+            };
+            std::vector<std::thread> th;
+            for (int k = 1; k < n; k++) th.emplace_back(rebuild, k);
+            rebuild(0);
             for (auto &t : th) t.join();
         }
         for (int k = 0; k < n; k++)
@@ -349,6 +384,7 @@ class ParFAAIQryTgtData : public DataStructBase {
     int m_nT, m_nQ;
     bool m_refCompat;
     int loadHostIndex(HostIndex &ix) override { return m_qtDBIf.loadIndex(ix); }
+    int reloadHostIndexWithoutLists(HostIndex &ix) override { return m_qtDBIf.loadIndexUncached(ix); }
 
   public:
     // refCompat = reproduce the reference's T-lookup labels (q, nQ+t) (ds_impl.hpp:434-436);

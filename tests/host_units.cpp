@@ -42,6 +42,12 @@ int main(int argc, char **argv) {
         std::string blob = slurp(path);
         { std::string b = blob; b[60] ^= 0x55; std::ofstream(path, std::ios::binary) << b; }
         CHECK(!read_lists_cache(path, key, P, G, v.size(), so2, v2));            // damaged offsets: checksum
+        { std::string b = blob; b[b.size() - 5] ^= 0x01; std::ofstream(path, std::ios::binary) << b; }
+        CHECK(!read_lists_cache(path, key, P, G, v.size(), so2, v2));            // one bit of a tetramer flipped (the segment stays ascending): checksum of vals
+        { std::string b = blob; b[56 + 8 * (P * G + 1) + 1] ^= 0x40; std::ofstream(path, std::ios::binary) << b; }
+        CHECK(!read_lists_cache(path, key, P, G, v.size(), so2, v2));            // first posting damaged
+        { std::string b = blob; b[7] = '1'; std::ofstream(path, std::ios::binary) << b; }
+        CHECK(!lists_cache_header_ok(path, key) && !read_lists_cache(path, key, P, G, v.size(), so2, v2));   // the older PFLST001 layout is not trusted
         { std::ofstream(path, std::ios::binary) << blob.substr(0, blob.size() - 3); }
         CHECK(!read_lists_cache(path, key, P, G, v.size(), so2, v2));            // truncated
         { std::ofstream(path, std::ios::binary) << blob + "x"; }

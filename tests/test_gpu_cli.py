@@ -181,6 +181,69 @@ def test_index_cache_gives_identical_csv(cli, tmp_path):
     assert open(plain, "rb").read() != b""
 
 
+def _sidecar_sums(seg_off_bytes, vals):
+    """The two checksums of a PFLST002 sidecar (parfastaai_b200/host/index_cache.hpp: fnv1a / words_checksum)."""
+    M, FNV0, FNVP = (1 << 64) - 1, 1469598103934665603, 1099511628211
+
+    def fnv(h, data):
+        for b in data:
+            h = ((h ^ b) * FNVP) & M
+        return h
+    parts = []
+    for lo in range(0, len(vals), 1 << 18):
+        h = FNV0
+        for w in vals[lo:lo + (1 << 18)].tolist():
+            h = ((h ^ w) * FNVP) & M
+        parts.append(h)
+    return fnv(FNV0, seg_off_bytes), fnv(FNV0 ^ len(vals), np.array(parts, np.uint64).tobytes())
+
+
+def test_index_cache_sidecar_the_device_refuses(cli, tmp_path):
+    """A sidecar whose own checks pass (size, key, both checksums) but whose lists the device refuses -- two tetramers of one
+    segment out of order -- must not fail the run, nor every later one: the driver drops it, loads F from the .pfidx cache,
+    builds the ordinary way, writes the same CSV bytes and leaves a fresh, valid sidecar behind.  And a flipped bit inside the
+    tetramer postings (segment still ascending) is caught by the sidecar's checksum before anything reaches the device."""
+    import shutil
+    import struct
+    db = str(tmp_path / "s1.db")
+    shutil.copy(gu.db_path("xdb_subset1.db"), db)
+    cache = str(tmp_path / "s1.pfidx")
+    plain, first = str(tmp_path / "plain.csv"), str(tmp_path / "first.csv")
+    run(cli, db, plain)
+    run(cli, db, first, "--index-cache", cache)
+    good = open(cache + ".lists", "rb").read()
+    assert good[:8] == b"PFLST002"
+    P, G, nF = struct.unpack_from("<iiQ", good, 24)
+    off_bytes = 8 * (P * G + 1)
+    seg_off = np.frombuffer(good, np.int64, P * G + 1, 56)
+    vals = np.frombuffer(good, np.uint32, nF, 56 + off_bytes).copy()
+    assert _sidecar_sums(good[56:56 + off_bytes], vals) == struct.unpack_from("<QQ", good, 40)   # the Python restatement is right
+    s = int(np.argmax(np.diff(seg_off) >= 2))
+    a = int(seg_off[s])
+    vals[a], vals[a + 1] = vals[a + 1], vals[a]                                  # descending pair inside one segment
+    sums = _sidecar_sums(good[56:56 + off_bytes], vals)
+    open(cache + ".lists", "wb").write(good[:40] + struct.pack("<QQ", *sums) + good[56:56 + off_bytes] + vals.tobytes())
+    out = str(tmp_path / "refused.csv")
+    r = run(cli, db, out, "--index-cache", cache)
+    assert "device refused the cached device-ready lists" in r.stderr
+    assert "device-ready lists written" in r.stdout                              # a fresh sidecar replaces the refused one
+    assert open(out, "rb").read() == open(plain, "rb").read()
+    assert open(cache + ".lists", "rb").read() == good
+    again = str(tmp_path / "again.csv")
+    r = run(cli, db, again, "--index-cache", cache)
+    assert "device-ready lists loaded" in r.stdout and "refused" not in r.stderr
+    assert open(again, "rb").read() == open(plain, "rb").read()
+    # one flipped bit in the postings, the segment still ascending: read_lists_cache rejects it (checksum of vals), the run takes F
+    flip = bytearray(good)
+    flip[56 + off_bytes + 4 * int(seg_off[s + 1]) - 4] ^= 0x01
+    open(cache + ".lists", "wb").write(bytes(flip))
+    out = str(tmp_path / "flipped.csv")
+    r = run(cli, db, out, "--index-cache", cache)
+    assert "device-ready lists loaded" not in r.stdout and "refused" not in r.stderr
+    assert open(out, "rb").read() == open(plain, "rb").read()
+    assert open(cache + ".lists", "rb").read() == good
+
+
 def test_multi_gpu_sharded_cli_matches_single_gpu(cli, tmp_path):
     """--gpus N: output row blocks sharded over N contexts, host scatter + mirror; bytes must equal the 1-GPU CSV.
     On a single-GPU box the N contexts share the device (--same-device); with >= 2 GPUs both layouts are run."""
