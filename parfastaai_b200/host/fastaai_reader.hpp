@@ -304,17 +304,19 @@ class QTSQLiteSCPDataBase {
     struct DeferOpen {};
     QTSQLiteSCPDataBase(const std::string &tgtDBPath, const std::string &qryDBPath, DeferOpen)   // a subclass decides whether the pair is opened
         : m_pathToTgtDb(tgtDBPath), m_pathToQryDb(qryDBPath) {}
+    // SCPs present in BOTH databases, same statement as db_helper.hpp:139-146.  The ORDER of its rows is whatever SQLite's
+    // planner makes of the two-table join, and that order is the fp64 summation order of S: anything that wants the
+    // reference's bytes takes the order from this statement, not from either database alone.
+    std::string commonScpStatement() const {
+        const std::string acc = m_dbNames.SCPDTAB_COLUMN_ACC;
+        return "SELECT DISTINCT target_table." + acc + " \n  FROM `main`." + m_dbNames.SCPDTAB + " as target_table, `QueryDB`." +
+               m_dbNames.SCPDTAB + " as query_table \n  WHERE target_table." + acc + " = query_table." + acc + ";";
+    }
     void openPairAndReadNames() {
         m_dbMeta = DBMetaData();
         m_sqltDbPtr = open_pair(&m_dbErrorCode, true);
         if (m_dbErrorCode != SQLITE_OK) return;
-        // SCPs present in BOTH databases, same statement as db_helper.hpp:139-146
-        const std::string acc = m_dbNames.SCPDTAB_COLUMN_ACC;
-        m_dbErrorCode = detail::query_strings(m_sqltDbPtr,
-                                              "SELECT DISTINCT target_table." + acc + " \n  FROM `main`." + m_dbNames.SCPDTAB +
-                                                  " as target_table, `QueryDB`." + m_dbNames.SCPDTAB + " as query_table \n  WHERE target_table." +
-                                                  acc + " = query_table." + acc + ";",
-                                              m_dbMeta.proteinSet);
+        m_dbErrorCode = detail::query_strings(m_sqltDbPtr, commonScpStatement(), m_dbMeta.proteinSet);
         if (m_dbErrorCode == SQLITE_OK)
             m_dbErrorCode = detail::query_strings(
                 m_sqltDbPtr, "SELECT " + m_dbNames.GMTTAB_COLUMN_GNAME + " FROM `main`." + m_dbNames.GMTTAB, m_dbMeta.genomeSet);

@@ -284,8 +284,9 @@ class CachedSCPDataBase : public SQLiteSCPDataBase {
 // re-reads the whole main database for every query database (main.cpp:302-335 -> scp_db.hpp:402-589, ATTACH + per-SCP inner
 // joins); here a valid `.pfidx` + `.lists` pair of the main database serves the targets' device-ready lists, name tables and T,
 // only the (small) query database is read from SQLite, and the query genomes' lists are appended behind the targets':
-//   proteins : those of the main database that the query database also has, in the main database's order (what the reference's
-//              join statement returns, db_helper.hpp:139-146);
+//   proteins : those of the main database that the query database also has, in the order the reference's own join statement
+//              returns them (db_helper.hpp:139-146, run here over the two SCP-description tables: SQLite decides which table
+//              drives the join, and that order is the summation order of S);
 //   genomes  : targets keep ids 0..nT-1, queries become nT + id;
 //   lists    : every tetramer of every genome, not only those present in both databases -- a tetramer that one side lacks never
 //              co-occurs in a (target, query) pair, so counts, S, N and AJI equal the inner-join index's (scp_db.hpp:408-414);
@@ -309,21 +310,36 @@ class CachedQTDataBase : public QTSQLiteSCPDataBase {
             read_index_cache(m_cachePath, m_key, m_mainMeta, m_mainIx, /*skip_F=*/true)) {
             m_qdb.reset(new SQLiteSCPDataBase(qryDBPath));
             if (m_qdb->getDBErrorCode() == SQLITE_OK) {
+                // The common SCPs IN THE REFERENCE'S ORDER: its own join statement over the two SCP-description tables (an ATTACH
+                // that reads two tiny tables, no tetramer table).  Every name must be known to the cached main database and to
+                // the query database, and nothing common may be missing, else the ATTACH path answers.
                 const DBMetaData &qm = m_qdb->getMeta();
-                std::unordered_map<std::string, int> qidx;
+                std::vector<std::string> common;
+                int rc = SQLITE_OK;
+                sqlite3 *pair = open_pair(&rc, false);
+                if (rc == SQLITE_OK) rc = detail::query_strings(pair, commonScpStatement(), common);
+                if (pair) sqlite3_close(pair);
+                std::unordered_map<std::string, int> qidx, midx;
                 for (size_t i = 0; i < qm.proteinSet.size(); i++) qidx.emplace(qm.proteinSet[i], (int)i);
-                for (size_t i = 0; i < m_mainMeta.proteinSet.size(); i++) {
-                    auto it = qidx.find(m_mainMeta.proteinSet[i]);
-                    if (it == qidx.end()) continue;
-                    m_dbMeta.proteinSet.push_back(m_mainMeta.proteinSet[i]);
-                    m_pm.push_back((int)i); m_pq.push_back(it->second);
+                for (size_t i = 0; i < m_mainMeta.proteinSet.size(); i++) midx.emplace(m_mainMeta.proteinSet[i], (int)i);
+                size_t n_common = 0;
+                for (const auto &kv : midx) n_common += qidx.count(kv.first);
+                bool ok = rc == SQLITE_OK && common.size() == n_common;
+                for (size_t i = 0; ok && i < common.size(); i++) {
+                    auto im = midx.find(common[i]); auto iq = qidx.find(common[i]);
+                    ok = im != midx.end() && iq != qidx.end();
+                    if (ok) { m_pm.push_back(im->second); m_pq.push_back(iq->second); }
                 }
-                m_dbMeta.genomeSet = m_mainMeta.genomeSet;
-                m_dbMeta.qyGenomeSet = qm.genomeSet;
-                m_cached = true;
-                std::printf("Index cache         : main database served from %s (+ .lists); only the query database is read from SQLite\n",
-                            m_cachePath.c_str());
-                return;
+                if (ok) {
+                    m_dbMeta.proteinSet = std::move(common);
+                    m_dbMeta.genomeSet = m_mainMeta.genomeSet;
+                    m_dbMeta.qyGenomeSet = qm.genomeSet;
+                    m_cached = true;
+                    std::printf("Index cache         : main database served from %s (+ .lists); only the query database is read from SQLite\n",
+                                m_cachePath.c_str());
+                    return;
+                }
+                m_pm.clear(); m_pq.clear();
             }
             m_qdb.reset();
         }
