@@ -61,7 +61,7 @@ typedef struct {
     float h2d_ms;        /* pfaai_gpu_upload_index                                       */
     float build_ms;      /* pfaai_gpu_build total                                        */
     float sort_ms;       /*   of which: radix sort passes                                */
-    float pack_ms;       /* row-slab packing inside compute                              */
+    float pack_ms;       /* row-slab packing inside compute (list path; excludes plan_ms) */
     float tile_ms;       /* the core tile kernel (aji_tile_kernel)                       */
     float d2h_ms;        /* result download                                              */
     int32_t n_launches;  /* kernels launched by the last build + compute                 */
@@ -75,7 +75,7 @@ typedef struct {
     int64_t sparse_items; /* dense path: postings on non-dense tetramers (walked in-kernel as sparse row items)  */
     int64_t e_size;      /* |E| = sum over posting lists of n(n-1)/2 (the reference's E array, all-vs-all), when known, else -1 */
     float prep_ms;       /* dense path: list lengths, dense ids, operand images, sparse items + dictionaries */
-    int32_t reserved2_;
+    float plan_ms;       /* choosing the tile path (list-length histogram + cost model; host clock); ~0 once cached for this build */
 } pfaai_timings_t;
 
 /* ---- life cycle ------------------------------------------------------------------------------ */

@@ -42,7 +42,7 @@ class Timings(C.Structure):
                 ("tile_ms", C.c_float), ("d2h_ms", C.c_float), ("n_launches", C.c_int32), ("n_tiles", C.c_int32),
                 ("tile_alg_bytes", C.c_int64), ("dict_ms", C.c_float), ("reserved_", C.c_int32),
                 ("path", C.c_int32), ("dense_tau", C.c_int32), ("dense_k_sum", C.c_int64), ("sparse_items", C.c_int64),
-                ("e_size", C.c_int64), ("prep_ms", C.c_float), ("reserved2_", C.c_int32)]
+                ("e_size", C.c_int64), ("prep_ms", C.c_float), ("plan_ms", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -70,12 +70,17 @@ _lib = None
 def load():
     """dlopen the C-ABI library; raises (never falls back) when it has not been built."""
     global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
-        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+    if _lib is None:
+        _lib = load_path(LIB_PATH)
+    return _lib
+
+
+def load_path(path):
+    """dlopen one build of the C-ABI library and declare its argument types (tests: the -DPFAAI_TEST_HOOKS build)."""
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                            "(nvcc, sm_100a). There is no CPU fallback.")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
     vp, i32, i64, u32 = C.c_void_p, C.c_int, C.c_int64, C.c_uint
     L.pfaai_gpu_create.argtypes = [C.POINTER(vp), i32, u32]
     L.pfaai_gpu_destroy.argtypes = [vp]
@@ -121,7 +126,6 @@ def load():
     L.pfaai_gpu_progress_poll.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_int)]
     L.pfaai_gpu_microbench.argtypes = [vp, i32, C.c_double, i32, C.POINTER(Microbench)]
     L.pfaai_gpu_prefix_sum_static.argtypes = [i32, vp, vp, i64, vp, vp]
-    _lib = L
     return L
 
 
@@ -159,8 +163,8 @@ def prefix_sum_static(device: int, stream_ptr: int, in_dev: int, n: int, out_dev
 class PfaaiGpu:
     """Thin object wrapper over one pfaai_gpu_ctx (one CUDA device)."""
 
-    def __init__(self, device=0):
-        self._L = load()
+    def __init__(self, device=0, lib=None):
+        self._L = lib if lib is not None else load()
         h = C.c_void_p()
         rc = self._L.pfaai_gpu_create(C.byref(h), device, 0)
         if rc != 0:

@@ -2,6 +2,7 @@
 // No CPU fallback: every entry point either runs the CUDA kernels or returns PFAAI_ERR_CONSTRUCT.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -56,6 +57,8 @@ struct Ctx {
     bool lists_only = false;                  // pfaai_gpu_import_lists: no F on the device (no partitioned / routed build possible)
     bool prog_enabled = false;
     std::atomic<int> prog_state{0};          // 0 = no compute under way / not armed, 1 = armed (counters valid), 2 = compute finished
+    std::mutex prog_mutex;                   // a poll holds it from its state re-check to its last read of prog_need / prog_host; the computing
+                                             // thread takes it to leave state 1, so it never frees or replaces them under a poller
     std::vector<int32_t> prog_need;
     int prog_gran = 0;                        // output rows per granule
     int64_t prog_rows = 0;                    // output rows of the armed compute
@@ -66,6 +69,11 @@ struct Ctx {
     int path_pref = PFAAI_PATH_AUTO, tau_pref = 0;
     DevBuf mm_len, mm_hist, mm_did, mm_kcnt, mm_kpad, mm_koff, mm_img_rows, mm_img_cols, mm_colT, mm_rowmax, mm_colmax,
            mm_owned, sp_cnt, sp_nch, sp_tot, sp_off, sp_items, sp_nsub, sp_sub, sp_blob;
+    // planning inputs that depend on the built index only, kept per build (reset wherever e_size is): the posting-list length
+    // histograms of mma_length_hist, slot 0 = exact (every genome), slot 1 = the planning sample, and what mm_len holds on the device
+    std::vector<unsigned long long> plan_hist[2];
+    int plan_hist_stride[2] = {0, 0};        // stride the slot was computed with, 0 = empty
+    int mm_len_stride = 0;                   // stride of the lengths in mm_len (the dense path needs 1), 0 = none
     int64_t e_size = -1;                  // |E| of the built index (exact length histogram), -1 = not computed for this build
     // routed build: this context holds postings [slice_begin, slice_begin + n_slice) of F only
     bool sliced = false;
@@ -208,7 +216,7 @@ static int build_internal(Ctx *c, bool partitioned) {
     const int P = c->P, G = c->G;
     const int64_t nF = c->nF, nseg = (int64_t)P * G;
     c->launches = 0;
-    c->built = false; c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr; c->e_size = -1;
+    c->built = false; c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr; c->e_size = -1; c->plan_hist_stride[0] = c->plan_hist_stride[1] = 0; c->mm_len_stride = 0;
     PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
     PF_TRY(ensure(c, c->Lp32, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->seg_len, sizeof(uint32_t) * (size_t)nseg));
@@ -456,7 +464,7 @@ int pfaai_gpu_import_lists(pfaai_gpu_ctx *h, int P, int G, int64_t nF, const int
     PF_CUDA(c, cudaSetDevice(c->device));
     const int64_t nseg = (int64_t)P * G;
     c->P = P; c->G = G; c->nF = nF; c->nF_owned = nF; c->host_T = (T != nullptr); c->built = false; c->uploaded = false; c->sliced = false; c->lists_only = false;
-    c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr; c->e_size = -1; c->launches = 0;
+    c->partitioned = false; c->dict_ready = false; c->exch_event = nullptr; c->e_size = -1; c->plan_hist_stride[0] = c->plan_hist_stride[1] = 0; c->mm_len_stride = 0; c->launches = 0;
     c->lists_only = true;
     PF_TRY(ensure(c, c->Lc, sizeof(int32_t) * NTETRA));
     PF_TRY(ensure(c, c->Lp64, sizeof(int64_t) * (NTETRA + 1)));
@@ -1003,8 +1011,15 @@ struct MmaPlan {
 };
 
 // length histogram of the posting lists; stride > 1: every stride-th genome only (the planning estimate, ~|F|/stride work)
-static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl) {
+static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl, bool need_device_lengths = false) {
     const int P = c->P, G = c->G;
+    const int slot = stride == 1 ? 0 : 1;
+    if (c->plan_hist_stride[slot] == stride && (!need_device_lengths || c->mm_len_stride == stride)) {
+        // same build, same sample: the histogram (and |E|) cannot have changed -- no memset, no pass over the postings, no host sync
+        pl.hist = c->plan_hist[slot];
+        pl.stride = stride; pl.exact = (stride == 1);
+        return PFAAI_OK;
+    }
     const int64_t nlen = (int64_t)P * NTETRA;
     PF_TRY(ensure(c, c->mm_len, sizeof(uint32_t) * (size_t)nlen));
     PF_TRY(ensure(c, c->mm_hist, sizeof(unsigned long long) * (MM_HMAX + 2)));
@@ -1024,6 +1039,7 @@ static int mma_length_hist(Ctx *c, int stride, MmaPlan &pl) {
     PF_CUDA(c, cudaStreamSynchronize(c->stream));
     pl.stride = stride; pl.exact = (stride == 1);
     if (pl.exact) c->e_size = (int64_t)pl.hist[MM_HMAX + 1];
+    c->plan_hist[slot] = pl.hist; c->plan_hist_stride[slot] = stride; c->mm_len_stride = stride;
     return PFAAI_OK;
 }
 
@@ -1243,13 +1259,13 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
     if (lane_lookups > 4095) { set_error(c, "compute: a (SCP, genome) tetramer list exceeds 8158 entries"); return PFAAI_ERR_CONSTRUCT; }
     if (P > 1023) { set_error(c, "compute: more than 1023 SCPs"); return PFAAI_ERR_CONSTRUCT; }
 
-    PF_CUDA(c, cudaEventRecord(c->ev[EV_P0], c->stream));
     PF_TRY(upload_i32(c, c->rows, m.rows)); PF_TRY(upload_i32(c, c->row_t, m.row_t));
     PF_TRY(upload_i32(c, c->cols, m.cols)); PF_TRY(upload_i32(c, c->col_t, m.col_t));
     // ---- which tile path (include/pfaai_gpu.h, pfaai_gpu_set_path) ----
     const bool sharded = c->n_shards > 1;
     bool use_mma = false;
     MmaPlan pl;
+    const auto plan_t0 = std::chrono::steady_clock::now();   // host clock: a planning pass that runs ends in a stream synchronise
     {
         const bool mma_possible = !c->partitioned && P <= 255 && c->nF > 0 && n_rows > 0 && n_cols > 0;
         if (c->path_pref == PFAAI_PATH_MMA && !mma_possible) {
@@ -1263,14 +1279,16 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
             // planning on a genome sample first (~|F| / stride work); the exact lengths only when the dense path is taken
             PF_TRY(mma_length_hist(c, force ? 1 : std::max(1, c->G / 2048), pl));
             mma_choose(c, pl, cells, img_blocks, force);
-            if (pl.use && !pl.exact) {
-                PF_TRY(mma_length_hist(c, 1, pl));
+            if (pl.use && (!pl.exact || c->mm_len_stride != 1)) {
+                PF_TRY(mma_length_hist(c, 1, pl, /*need_device_lengths=*/true));   // k_dense_ids reads the exact lengths from mm_len
                 mma_choose(c, pl, cells, img_blocks, force);
             }
             if (force && !pl.use) { set_error(c, "compute: the dense path does not fit this input (operand images too large)"); return PFAAI_ERR_CONSTRUCT; }
             use_mma = pl.use;
         }
     }
+    c->tm.plan_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - plan_t0).count();
+    PF_CUDA(c, cudaEventRecord(c->ev[EV_P0], c->stream));    // pack_ms = row-slab packing only; the planning has its own timer
     const int TR = use_mma ? MM_ROWS : TILE_ROWS, TC = use_mma ? MM_COLS : COLS_PER_TILE;      // tile geometry of the path
     const int nrb = (n_rows + TR - 1) / TR, ncb = (n_cols + TC - 1) / TC;
     if (!use_mma) {
@@ -1390,7 +1408,7 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         PF_CUDA(c, cudaMemsetAsync(c->counts_out.p, 0, sizeof(int32_t) * nk * P, c->stream));
     }
     // ---- streaming output: arm the per-granule progress counters (unsharded all-vs-all into a pinned host matrix only) ----
-    c->prog_state.store(0, std::memory_order_release);
+    { std::lock_guard<std::mutex> lk(c->prog_mutex); c->prog_state.store(0, std::memory_order_release); }
     int *prog_dev = nullptr;
     int n_gran = 0;
     if (c->prog_enabled && direct_dev && m.symmetric && !sharded && !tiles.empty() && c->nF > 0) {
@@ -1458,14 +1476,18 @@ static int compute_internal(Ctx *c, int mode, const int32_t *qry_ids, int nQ, un
         PF_CUDA(c, cudaEventRecord(c->ev[EV_K0], c->stream));
         {
             // (PFAAI_TEST_FAIL_MMA_PREP: test hook for the fall-back below)
+#ifdef PFAAI_TEST_HOOKS   // only in libpfaai_gpu_hooks.so, which the tests build next to the product library
             const int prc = getenv("PFAAI_TEST_FAIL_MMA_PREP") ? (set_error(c, "dense path: preparation failed (test hook)"), (int)PFAAI_ERR_CONSTRUCT)
                                                                : mma_prepare(c, m, pl, n_rows, n_cols, rb_owned, kpad_host, mp);
+#else
+            const int prc = mma_prepare(c, m, pl, n_rows, n_cols, rb_owned, kpad_host, mp);
+#endif
             if (prc != PFAAI_OK) {
                 // the cost model picked the dense path but it cannot be prepared for this input (a sparse dictionary that does not
                 // fit a stage, no memory for the operand images, ...): when the choice was ours, serve the call on the list path
                 // instead of failing it; a caller who forced PFAAI_PATH_MMA gets the error
                 if (c->path_pref != PFAAI_PATH_AUTO) return prc;
-                c->prog_state.store(0, std::memory_order_release);
+                { std::lock_guard<std::mutex> lk(c->prog_mutex); c->prog_state.store(0, std::memory_order_release); }
                 c->path_pref = PFAAI_PATH_LISTS;
                 ModePlan m2;
                 const int rc2 = compute_internal(c, mode, qry_ids, nQ, flags, want_sn, want_counts, m2, direct_dev);
@@ -1649,7 +1671,7 @@ int pfaai_gpu_set_progress(pfaai_gpu_ctx *h, int enable) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     if (!c) return PFAAI_ERR_CONSTRUCT;
     c->prog_enabled = enable != 0;
-    c->prog_state.store(0, std::memory_order_release);
+    { std::lock_guard<std::mutex> lk(c->prog_mutex); c->prog_state.store(0, std::memory_order_release); }
     return PFAAI_OK;
 }
 
@@ -1663,6 +1685,16 @@ int pfaai_gpu_progress_poll(pfaai_gpu_ctx *h, int64_t *rows_final, int *finished
     if (st == 0) { *rows_final = 0; return PFAAI_OK; }
     if (st == 2) { *rows_final = c->prog_rows; return PFAAI_OK; }
     if (cudaSetDevice(c->device) != cudaSuccess) return PFAAI_ERR_CONSTRUCT;
+    // The computing thread may leave state 1 at any moment (a dense-path preparation that falls back to the list path re-arms
+    // with new counters; the next compute may free prog_host): it does so under prog_mutex, so re-check the state with the lock
+    // held and keep it until the last read of the shared arrays.
+    std::lock_guard<std::mutex> lk(c->prog_mutex);
+    const int st2 = c->prog_state.load(std::memory_order_acquire);
+    if (st2 != 1) {
+        if (finished) *finished = (st2 == 2) ? 1 : 0;
+        *rows_final = (st2 == 2) ? c->prog_rows : 0;
+        return PFAAI_OK;
+    }
     const int n = (int)c->prog_need.size();
     if (cudaMemcpyAsync(c->prog_host, c->prog.p, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, c->prog_stream) != cudaSuccess ||
         cudaStreamSynchronize(c->prog_stream) != cudaSuccess)

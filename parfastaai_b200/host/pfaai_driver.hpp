@@ -231,8 +231,12 @@ class DataStructBase {
         int rc;
         if (partitioned) {
             // (PFAAI_TEST_FAIL_ROUTED: test hook for the fall-back below)
+#ifdef PFAAI_TEST_HOOKS   // only in par_fastaai_hooks.x, which the tests build next to the product binary
             rc = std::getenv("PFAAI_TEST_FAIL_ROUTED") ? (int)PFAAI_ERR_CONSTRUCT
                                                        : pfaai_gpu_route_local(m_ctxs.data(), n);   // group by owner, peer copies, sort + own dictionaries
+#else
+            rc = pfaai_gpu_route_local(m_ctxs.data(), n);   // group by owner, peer copies, sort + own dictionaries
+#endif
             if (rc == PFAAI_OK) rc = pfaai_gpu_exchange_local(m_ctxs.data(), n);  // dictionaries to every GPU
             if (rc != PFAAI_OK) {
                 // e.g. a skewed database whose heaviest shard overflows the agreed dictionary chunk: do not fail the run, fall

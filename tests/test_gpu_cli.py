@@ -269,8 +269,12 @@ def test_multi_gpu_sharded_cli_matches_single_gpu(cli, tmp_path):
             assert f"{v[1]} GPU(s)" in r.stdout
     # a routed build that cannot be done (skewed input: chunk overflow) must fall back to the replicated build, not fail the run
     many = str(tmp_path / "fallback.csv")
-    r = subprocess.run([cli, db, many, "--gpus", "2", "--same-device"], capture_output=True, text=True,
+    # (the failure switch exists only in the -DPFAAI_TEST_HOOKS build of the binary; the product binary ignores it)
+    r = subprocess.run([ge.CLI_HOOKS, db, many, "--gpus", "2", "--same-device"], capture_output=True, text=True,
                        env=dict(os.environ, OMP_NUM_THREADS="4", PFAAI_TEST_FAIL_ROUTED="1"))
     assert r.returncode == 0 and "falling back to the replicated build" in r.stderr, r.stderr
     run(cli, db, one)
     assert open(one, "rb").read() == open(many, "rb").read()
+    r = subprocess.run([cli, db, many, "--gpus", "2", "--same-device"], capture_output=True, text=True,
+                       env=dict(os.environ, OMP_NUM_THREADS="4", PFAAI_TEST_FAIL_ROUTED="1"))
+    assert r.returncode == 0 and "falling back" not in r.stderr

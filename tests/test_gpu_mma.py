@@ -189,6 +189,47 @@ def test_auto_path_picks_by_density_and_agrees(pf, orc):
     assert picked[False] in (pf.PATH_LISTS, pf.PATH_MMA)
 
 
+def test_path_plan_is_kept_per_build_and_dropped_with_it(pf):
+    """The list-length histogram, |E| and the chosen plan depend on the built index only: the second compute on a build does not
+    recompute them (plan_ms ~ 0, same path / tau / |E| / matrix); a new index on the same context does (its own path and |E|);
+    a query-subset compute between two all-vs-all ones (sampled vs exact lengths on the device) leaves the dense path intact."""
+    from parfastaai_b200 import synth
+    N, P = 1500, 6
+    ctx = pf.PfaaiGpu(0)
+    seen = {}
+    for dense in (True, False, True):
+        off, vals = synth.generate(N, P, seed=3, dense=dense)
+        Lc, F = synth.to_reference(N, P, off, vals)
+        ctx.upload_index(P, N, F, Lc)
+        ctx.build()
+        n0 = ctx.timings()["n_launches"]             # the counter runs on from the build
+        m1 = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"].copy()
+        t1 = ctx.timings()
+        sub = ctx.compute(pf.QUERY_SUBSET, qry_ids=np.arange(5, 45, dtype=np.int32), want_jac=False)["matrix"]
+        assert np.array_equal(sub, m1[5:45])
+        n_sub = ctx.timings()["n_launches"]
+        m2 = ctx.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"]
+        t2 = ctx.timings()
+        assert np.array_equal(m1, m2)
+        assert (t2["path"], t2["dense_tau"], t2["e_size"]) == (t1["path"], t1["dense_tau"], t1["e_size"])
+        assert t1["e_size"] == ctx.e_size() > 0
+        # the repeat launches no planning kernels (list lengths + histogram): at least two launches fewer than the first call
+        assert (t1["n_launches"] - n0) - (t2["n_launches"] - n_sub) >= 2, (n0, t1["n_launches"], n_sub, t2["n_launches"])
+        assert t1["plan_ms"] > 0 and t2["plan_ms"] >= 0
+        fresh = pf.PfaaiGpu(0)                       # the same index on a context without history
+        fresh.upload_index(P, N, F, Lc)
+        fresh.build()
+        assert np.array_equal(fresh.compute(pf.ALL_VS_ALL, want_jac=False)["matrix"], m1)
+        tf = fresh.timings()
+        assert (tf["path"], tf["dense_tau"], tf["e_size"]) == (t1["path"], t1["dense_tau"], t1["e_size"])
+        fresh.close()
+        if dense in seen:
+            assert seen[dense] == (t1["path"], t1["e_size"])
+        seen[dense] = (t1["path"], t1["e_size"])
+    assert seen[True][0] == pf.PATH_MMA and seen[True][1] != seen[False][1]
+    ctx.close()
+
+
 def test_auto_path_falls_back_to_lists_when_the_dense_path_cannot_be_prepared(pf, orc, monkeypatch):
     """PATH_AUTO on the dense family picks K5; when its preparation fails (test hook) the call is served by the list path
     with identical results instead of failing; a forced PATH_MMA reports the error."""
@@ -196,12 +237,21 @@ def test_auto_path_falls_back_to_lists_when_the_dense_path_cannot_be_prepared(pf
     N, P = 1500, 6                     # the size at which test_auto_path_picks_by_density sees the cost model take K5
     off, vals = synth.generate(N, P, seed=3, dense=True)
     Lc, F = synth.to_reference(N, P, off, vals)
-    ctx = pf.PfaaiGpu(0)
+    # the failure switch exists only in the -DPFAAI_TEST_HOOKS build of the library (same sources; the product has no such getenv)
+    import __graft_entry__ as ge
+    from parfastaai_b200 import _lib
+    ctx = pf.PfaaiGpu(0, lib=_lib.load_path(ge.LIB_HOOKS))
     ctx.upload_index(P, N, F, Lc)
     ctx.build()
     want = ctx.compute(pf.ALL_VS_ALL, want_jac=True)
     assert ctx.timings()["path"] == pf.PATH_MMA
+    prod = pf.PfaaiGpu(0)                       # the product library gives the same matrix and ignores the switch
+    prod.upload_index(P, N, F, Lc)
+    prod.build()
     monkeypatch.setenv("PFAAI_TEST_FAIL_MMA_PREP", "1")
+    got = prod.compute(pf.ALL_VS_ALL, want_jac=True)
+    assert prod.timings()["path"] == pf.PATH_MMA and np.array_equal(got["matrix"], want["matrix"])
+    prod.close()
     got = ctx.compute(pf.ALL_VS_ALL, want_jac=True)
     assert ctx.timings()["path"] == pf.PATH_LISTS
     assert np.array_equal(got["matrix"], want["matrix"]) and np.array_equal(got["aji"], want["aji"])
