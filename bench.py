@@ -821,12 +821,14 @@ def main():
                             "ceiling": ceiling,
                             "frac": ((float(tm["n_tiles"]) * 384 * (nF / G) / (tile_avg_ms / 1e3)) / ceiling["lookups_per_s"]
                                      if ceiling and ceiling.get("lookups_per_s") and tm["path"] == pf.PATH_LISTS else None),
+                            "frac_of": "the walk loop's own ceiling (the same loop on the same data structure, no bulk copies / epilogue / output); "
+                                       "it bounds the overhead around the walk -- it is NOT a roofline fraction (that is roofline.frac)",
                             "mma": ({"macs_per_s": float(tm["n_tiles"]) * 128 * 128 * tm["dense_k_sum"] / (tile_avg_ms / 1e3),
                                      "operand_bytes_per_s": float(tm["n_tiles"]) * 256 * tm["dense_k_sum"] / (tile_avg_ms / 1e3),
                                      "note": "u8 x u8 -> s32 multiply-accumulates on tcgen05 (0/1 operands: exact counts) and the bulk-copied operand bytes they consume"}
                                     if tm["path"] == pf.PATH_MMA else None),
                             "ncu": onchip},
-        "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
+        "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "plan": tm["plan_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
                       "exchange": exchange_ms, "exchange_bytes_per_rank": exchange_bytes,
                       "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"],
                       # the same tile kernel inside the e2e step, where its stores go to page-locked HOST memory (rank 0's last step):

@@ -524,10 +524,13 @@ __global__ void __launch_bounds__(256) k_lc_run_ends(const int32_t *__restrict__
 // Import of device-ready lists (pfaai_gpu_import_lists: the index cache's fast path): validates what K1-K3 + the sort would
 // have guaranteed -- offsets ascending from 0 to nF, tetramers strictly ascending inside a segment and below NTETRA, T(p, g)
 // == the segment's length unless the caller supplies its own T -- and returns the longest segment.  One pass, HBM-bound.
-// flags[0] = 1 on a violation, flags[1] = max segment length (atomicMax).
+// flags[0] = 1 on a violation, flags[1] = max segment length (atomicMax).  With a caller-supplied T (row-major P x G) every
+// T(p, g) must be at least the length of segment (g, p): the Jaccard denominator ta + tb - c indexes the epilogue's reciprocal
+// table and would wrap around for a T smaller than the lists it describes; flags[2] = 1 when one is.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_check_lists(const int64_t *__restrict__ seg_off, const uint32_t *__restrict__ vals, int64_t nseg,
-                                                      int64_t nF, int *__restrict__ flags) {
+                                                      int64_t nF, int *__restrict__ flags, const int32_t *__restrict__ T_or_null, int P,
+                                                      int G) {
     const int lane = threadIdx.x & 31;
     const int64_t nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
     int mx = 0;
@@ -536,6 +539,7 @@ __global__ void __launch_bounds__(256) k_check_lists(const int64_t *__restrict__
         const int64_t b = seg_off[sg], e = seg_off[sg + 1];
         if (b < 0 || e < b || e > nF || e - b > (1 << 20) || (sg == 0 && b != 0) || (sg == nseg - 1 && e != nF)) { bad = true; continue; }
         mx = max(mx, (int)(e - b));
+        if (T_or_null && lane == 0 && (int64_t)T_or_null[(int64_t)(sg % P) * G + sg / P] < e - b) flags[2] = 1;
         for (int64_t k = b + lane; k < e; k += 32) {
             const uint32_t v = vals[k];
             if (v >= (uint32_t)NTETRA || (k > b && vals[k - 1] >= v)) bad = true;

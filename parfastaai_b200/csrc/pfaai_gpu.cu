@@ -482,7 +482,7 @@ int pfaai_gpu_import_lists(pfaai_gpu_ctx *h, int P, int G, int64_t nF, const int
     PF_CUDA(c, cudaMemsetAsync(c->flags.p, 0, 64, c->stream));
     PF_TRY(launch_scan(c, ptr<int32_t>(c->Lc), NTETRA, ptr<int64_t>(c->Lp64), ptr<int32_t>(c->Lp32)));   // Lp parity hook
     k_check_lists<<<(unsigned)std::min<int64_t>(ceil_div64(nseg, 8), (int64_t)c->sm_count * 16), 256, 0, c->stream>>>(
-        ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), nseg, nF, ptr<int>(c->flags));
+        ptr<int64_t>(c->seg_off), ptr<uint32_t>(c->vals), nseg, nF, ptr<int>(c->flags), T ? ptr<int32_t>(c->T) : nullptr, P, G);
     PF_LAUNCH_CHECK(c);
     if (!T) {
         k_t_from_offsets<<<(unsigned)ceil_div64(nseg, 256), 256, 0, c->stream>>>(ptr<int64_t>(c->seg_off), P, G, ptr<int32_t>(c->T));
@@ -492,6 +492,7 @@ int pfaai_gpu_import_lists(pfaai_gpu_ctx *h, int P, int G, int64_t nF, const int
     int fl[4];
     PF_TRY(read_flags(c, fl));
     if (fl[0]) { set_error(c, "import_lists: offsets must ascend from 0 to nF and tetramers must ascend strictly inside a segment, below 160000"); return PFAAI_ERR_CONSTRUCT; }
+    if (fl[2]) { set_error(c, "import_lists: a supplied T(p, g) is smaller than the tetramer list of (SCP p, genome g) it describes"); return PFAAI_ERR_CONSTRUCT; }
     c->max_len = fl[1];
     c->tm.h2d_ms = ev_ms(c, EV_H2D0, EV_H2D1);
     c->tm.build_ms = ev_ms(c, EV_B0, EV_B1);

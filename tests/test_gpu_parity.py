@@ -171,6 +171,14 @@ def test_device_ready_lists_import_equals_the_built_index(pf, orc):
     bad_off = a["seg_off"].copy(); bad_off[-1] -= 1
     with pytest.raises(pf.PfaaiError):
         c2.import_lists(P, G, a["Lc"], bad_off, a["seg_vals"])
+    # a supplied T that is smaller than the list it describes would wrap the Jaccard denominator ta + tb - c: refused up front;
+    # a larger one (query-DB mode: T counts tetramers the inner join dropped) is legitimate
+    p_, g_ = np.argwhere(a["T"] > 0)[-1]
+    small = a["T"].copy(); small[p_, g_] -= 1
+    with pytest.raises(pf.PfaaiError, match="smaller than the tetramer list"):
+        c2.import_lists(P, G, a["Lc"], a["seg_off"], a["seg_vals"], T=small)
+    large = a["T"].copy(); large[p_, g_] += 3
+    c2.import_lists(P, G, a["Lc"], a["seg_off"], a["seg_vals"], T=large)
     c2.close()
 
 
