@@ -254,6 +254,44 @@ def verify_against_oracle(G, P, dense, rects, read_cells, lower_valid):
     return out
 
 
+def dense_family_record(pf, synth, device, P, genomes=10000, reps=3):
+    """Untimed side record of the N = 1 line: the real-like (dense) synthetic family at BASELINE config-4 size, all-vs-all, on the
+    list path and on the path the cost model picks (the tensor-core contraction, aji_mma_kernel).  Tile-kernel time of both
+    (CUDA events inside the C-ABI, best of `reps` after one warm-up), the plan, and an oracle check of the picked path's cells.
+    Never part of `value` / `e2e`; it exists so that the driver's own run exercises and checks the dense path."""
+    t0 = time.perf_counter()
+    off, vals = synth.generate(genomes, P, seed=SEED, dense=True)
+    Lc, F = synth.to_reference(genomes, P, off, vals)
+    ctx = pf.PfaaiGpu(device)
+    rec = {"workload": f"all-vs-all {genomes} x {P}, real-like (dense) synthetic family, |F| = {int(off[-1])}", "reps": reps}
+    try:
+        ctx.upload_index(P, genomes, F, Lc)
+        ctx.build()
+        for name, path in (("lists", pf.PATH_LISTS), ("auto", pf.PATH_AUTO)):
+            ctx.set_path(path, 0)
+            ms = []
+            for _ in range(reps + 1):
+                ctx.compute_device(pf.ALL_VS_ALL)
+                ms.append(ctx.timings()["tile_ms"])
+            tm = ctx.timings()
+            r = {"tile_ms": float(min(ms[1:])), "prep_or_pack_ms": float(tm["prep_ms"] + tm["pack_ms"] + tm["dict_ms"]),
+                 "kernel": "aji_mma_kernel" if tm["path"] == pf.PATH_MMA else "aji_tile_kernel"}
+            if tm["path"] == pf.PATH_MMA:
+                r.update({"dense_tau": tm["dense_tau"], "dense_k_sum": tm["dense_k_sum"], "sparse_items": tm["sparse_items"],
+                          "macs_per_s": float(tm["n_tiles"]) * 128 * 128 * tm["dense_k_sum"] / (r["tile_ms"] / 1e3)})
+            rec[name] = r
+        M = ctx.download_matrix()                                    # the picked path's matrix (last compute)
+        v = verify_against_oracle(genomes, P, True, verify_rectangles(genomes, 0, 1), lambda rows, cols: M[np.ix_(rows, cols)], True)
+        v.pop("hit_rate", None)
+        rec["verify"] = v
+        rec["symmetric_zero_diagonal"] = bool(np.array_equal(M, M.T) and not np.any(np.diag(M)))
+        rec["speedup_picked_over_lists"] = rec["lists"]["tile_ms"] / rec["auto"]["tile_ms"]
+    finally:
+        ctx.close()
+    rec["wall_s"] = time.perf_counter() - t0
+    return rec
+
+
 def reference_baseline(P, n_genomes, threads, tmpdir):
     db = make_ref_db(n_genomes, P, tmpdir)
     phases, wall = run_ref_once(db, threads, tmpdir)
@@ -337,6 +375,7 @@ def main():
     ap.add_argument("--ref-genomes", type=int, default=64, help="size of the reference arm's bounded sample")
     ap.add_argument("--cpu-baseline-genomes", type=int, default=96)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dense-family", action="store_true", help="N=1: skip the untimed dense-family side record (both tile paths at config-4 size)")
     ap.add_argument("--no-ceiling", action="store_true", help="skip the on-chip ceiling micro-benchmark (pfaai_gpu_microbench)")
     ap.add_argument("--replicated-build", action="store_true",
                     help="N>1: every rank builds the whole index (the pre-partitioning path) instead of pfaai_gpu_build_partitioned")
@@ -859,6 +898,12 @@ def main():
         line["config"]["zero_share_pairs"] = zero_share // 2
 
     ctx.close()
+    if rank == 0 and world == 1 and not args.dense and not args.no_dense_family:
+        try:
+            del M
+            line["dense_family"] = dense_family_record(pf, synth, local_rank, P)
+        except Exception as e:  # noqa: BLE001  (a side record must not take the bench line down)
+            line["dense_family"] = {"error": str(e)}
     if world > 1:
         dist.barrier()
         if shared_matrix:
