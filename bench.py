@@ -581,15 +581,21 @@ def main():
         if world == 1:
             ctx.upload_index(P, G, F, Lc)
             return
+        cur = torch.cuda.current_stream(dev)               # the copies are torch's: timed here (the C-ABI's h2d_ms sees only its own)
+        h_ev[0].record(cur)
         if sliced:                                         # only the rank's own slice, over its own PCIe link
             Fs_dev[:8 * (hi - lo)].copy_(F_slice_pin[:8 * (hi - lo)], non_blocking=True)
             Lcs_dev.copy_(Lc_pin_r, non_blocking=True)
+            h_ev[1].record(cur); h_ev[2].record(cur)
             return
         mine = F_all[8 * per * rank:8 * per * (rank + 1)]
         mine.copy_(F_slice_pin, non_blocking=True)
         Lc_dev.copy_(Lc_pin_r, non_blocking=True)
+        h_ev[1].record(cur)
         dist.all_gather_into_tensor(F_all, mine)           # in place, straight into the context's F buffer
+        h_ev[2].record(cur)
 
+    h_ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]   # N > 1: slice upload begin / end, index all-gather end
     partitioned = world > 1 and not args.replicated_build and args.path != "mma"   # the dense path needs every genome's lists on the GPU
     xviews = {}
     xstream = torch.cuda.Stream(device=dev) if world > 1 else None
@@ -703,6 +709,10 @@ def main():
         with torch.cuda.stream(stream):
             step_e2e()
     ms_e2e, _, _, _, tm_e2e = timed(step_e2e, args.steps)
+    # N > 1: what the e2e step adds in front of the device-resident step, from the LAST e2e step, max over ranks: the rank's own
+    # slice of F over its PCIe link (all N links at once) and, for the builds that hold all of F, the NVLink all-gather of the slices
+    e2e_h2d_n = max_over_ranks(h_ev[0].elapsed_time(h_ev[1])) if world > 1 else None
+    e2e_index_allgather = max_over_ranks(h_ev[1].elapsed_time(h_ev[2])) if world > 1 else None
     e2e_value = pairs_total * args.steps / (ms_e2e / 1e3)
     h2d = 8 * nF + 4 * pf.NTETRA * world              # all ranks together (N > 1: every rank uploads 1/N of F)
     # bytes the tile kernels actually store into host memory per step, all ranks together: N = 1 and the shared matrix hold
@@ -869,7 +879,9 @@ def main():
                             "ncu": onchip},
         "phases_ms": {"build": tm["build_ms"], "sort": tm["sort_ms"], "plan": tm["plan_ms"], "pack": tm["pack_ms"], "dict": tm["dict_ms"], "tile": tile_avg_ms,
                       "exchange": exchange_ms, "exchange_bytes_per_rank": exchange_bytes,
-                      "e2e_h2d": tm_e2e["h2d_ms"], "e2e_d2h": tm_e2e["d2h_ms"],
+                      "e2e_h2d": tm_e2e["h2d_ms"] if world == 1 else e2e_h2d_n, "e2e_d2h": tm_e2e["d2h_ms"],
+                      "e2e_h2d_gbs_per_rank": (8.0 * (nF / world) / (e2e_h2d_n / 1e3) / 1e9) if world > 1 and e2e_h2d_n else None,
+                      "e2e_index_allgather": e2e_index_allgather,
                       # the same tile kernel inside the e2e step, where its stores go to page-locked HOST memory (rank 0's last step):
                       # the difference to "tile" is what the host-side write bandwidth costs when N GPUs store 8*G*G bytes at once
                       "e2e_tile": tm_e2e["tile_ms"], "e2e_build": tm_e2e["build_ms"]},
